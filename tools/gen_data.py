@@ -1,0 +1,203 @@
+#!/usr/bin/env python
+"""Seeded synthetic workload generator.
+
+Writes a FASTA reference (iid uniform ACGT + injected repeat families) and a
+FASTQ read set (mutated substrings, both strands).  Everything is a pure
+function of the arguments, so the GPU arm, the CPU reference arm and the tests
+all see the same bytes.  numpy only (PCG64 streams are stable across versions).
+"""
+import argparse
+import os
+
+import numpy as np
+
+ACGT = np.frombuffer(b"ACGT", dtype=np.uint8)
+COMP = np.zeros(256, dtype=np.uint8)
+for a, b in zip(b"ACGTN", b"TGCAN"):
+    COMP[a] = b
+
+
+def _mutate_copy(rng, block, div):
+    """Return a copy of block with substitution divergence div."""
+    out = block.copy()
+    n = len(out)
+    m = rng.random(n) < div
+    k = int(m.sum())
+    if k:
+        # substitute by a different base
+        cur = np.searchsorted(ACGT, out[m])
+        out[m] = ACGT[(cur + rng.integers(1, 4, k)) % 4]
+    return out
+
+
+def gen_reference(total_bp, seed, n_seqs=1, profile="auto"):
+    """Return (names, list of uint8 arrays)."""
+    rng = np.random.default_rng(seed)
+    g = ACGT[rng.integers(0, 4, total_bp)]
+    scale = total_bp / 3.1e9
+
+    def inject(unit_len, copies, dlo, dhi, trunc_min=None):
+        copies = int(copies)
+        if copies <= 0 or unit_len >= total_bp // 4:
+            return
+        master = ACGT[rng.integers(0, 4, unit_len)]
+        for _ in range(copies):
+            blk = master
+            if trunc_min is not None and unit_len > trunc_min:
+                cut = int(rng.integers(0, unit_len - trunc_min))
+                blk = master[cut:]
+            d = rng.uniform(dlo, dhi)
+            c = _mutate_copy(rng, blk, d)
+            p = int(rng.integers(0, total_bp - len(c)))
+            g[p:p + len(c)] = c
+
+    if profile == "auto":
+        profile = "ecoli" if total_bp < 20_000_000 else "human"
+    if profile == "ecoli":
+        f = total_bp / 4.6e6
+        inject(5000, max(2, round(7 * f)), 0.005, 0.005)
+        inject(1300, max(3, round(30 * f)), 0.01, 0.03)
+    elif profile == "human":
+        # SINE-like, LINE-like, 1 kbp family, segmental dups, microsatellites,
+        # 171-bp tandem arrays -- counts scaled by genome size
+        inject(300, max(50, 1_000_000 * scale), 0.05, 0.15)
+        inject(6000, max(8, 80_000 * scale), 0.02, 0.12, trunc_min=900)
+        inject(1000, max(10, 100_000 * scale), 0.01, 0.10)
+        nseg = max(2, int(200 * scale))
+        for _ in range(nseg):
+            ln = min(40_000, total_bp // 50)
+            src = int(rng.integers(0, total_bp - ln))
+            dst = int(rng.integers(0, total_bp - ln))
+            g[dst:dst + ln] = _mutate_copy(rng, g[src:src + ln].copy(),
+                                           rng.uniform(0.005, 0.02))
+        for _ in range(max(10, int(100_000 * scale))):
+            u = int(rng.integers(1, 7))
+            tot = int(rng.integers(60, 201))
+            unit = ACGT[rng.integers(0, 4, u)]
+            blk = np.tile(unit, tot // u + 1)[:tot]
+            p = int(rng.integers(0, total_bp - tot))
+            g[p:p + tot] = blk
+        for _ in range(max(1, int(200 * scale))):
+            units = min(2000, max(20, total_bp // (171 * 400)))
+            unit = ACGT[rng.integers(0, 4, 171)]
+            arr = np.concatenate([_mutate_copy(rng, unit, rng.uniform(0.01, 0.03))
+                                  for _ in range(units)])
+            p = int(rng.integers(0, total_bp - len(arr)))
+            g[p:p + len(arr)] = arr
+    elif profile == "dense":
+        # repeat-dense test profile (a few big families, 1-10 % divergence):
+        # makes most reads start real FM-index searches
+        mb = total_bp / 1e6
+        inject(300, max(20, 1000 * mb), 0.01, 0.10)
+        inject(1000, max(6, 100 * mb), 0.01, 0.10)
+        inject(3000, max(3, 20 * mb), 0.005, 0.05)
+        for _ in range(max(4, int(30 * mb))):
+            u = int(rng.integers(1, 7))
+            tot = int(rng.integers(60, 201))
+            unit = ACGT[rng.integers(0, 4, u)]
+            blk = np.tile(unit, tot // u + 1)[:tot]
+            p = int(rng.integers(0, total_bp - tot))
+            g[p:p + tot] = blk
+    elif profile == "none":
+        pass
+    else:
+        raise ValueError(profile)
+
+    # split into n_seqs sequences with GRCh38-like (decreasing) proportions
+    if n_seqs == 1:
+        return ["seq1_syn"], [g]
+    w = np.array([1.0 / (1 + 0.12 * i) for i in range(n_seqs)])
+    cuts = np.concatenate([[0], np.round(np.cumsum(w / w.sum()) * total_bp).astype(np.int64)])
+    cuts[-1] = total_bp
+    names = ["chr%d_syn" % (i + 1) for i in range(n_seqs)]
+    return names, [g[cuts[i]:cuts[i + 1]] for i in range(n_seqs)]
+
+
+def write_fasta(path, names, seqs, width=80):
+    with open(path, "wb") as f:
+        for nm, s in zip(names, seqs):
+            f.write(b">" + nm.encode() + b" synthetic\n")
+            n = len(s)
+            full = (n // width) * width
+            if full:
+                body = np.empty((full // width, width + 1), dtype=np.uint8)
+                body[:, :width] = s[:full].reshape(-1, width)
+                body[:, width] = 10
+                f.write(body.tobytes())
+            if n > full:
+                f.write(s[full:].tobytes() + b"\n")
+
+
+def gen_reads(seqs, n_reads, read_len, seed, metric="edit", max_e=4,
+              frac_over=0.05, frac_exact=0.05, over_e=6, n_frac=0.0):
+    """Return list of (name, bytes).  Reads never cross a sequence end."""
+    rng = np.random.default_rng(seed)
+    lens = np.array([len(s) for s in seqs], dtype=np.int64)
+    ok = lens > read_len + 16
+    prob = np.where(ok, lens, 0).astype(np.float64)
+    prob /= prob.sum()
+    sid = rng.choice(len(seqs), size=n_reads, p=prob)
+    u = rng.random(n_reads)
+    strand = rng.integers(0, 2, n_reads)
+    cls = rng.random(n_reads)
+    ne = rng.integers(0, max_e + 1, n_reads)
+    ne = np.where(cls < frac_over, over_e, ne)
+    ne = np.where(cls > 1.0 - frac_exact, 0, ne)
+    out = []
+    for r in range(n_reads):
+        s = seqs[sid[r]]
+        span = read_len + 8
+        p = int(u[r] * (len(s) - span))
+        frag = bytearray(s[p:p + span].tobytes())
+        for _ in range(int(ne[r])):
+            q = int(rng.integers(0, read_len))
+            t = rng.random() if metric == "edit" else 0.0
+            if t < 0.70:
+                cur = b"ACGT".index(frag[q]) if frag[q] in b"ACGT" else 0
+                frag[q] = b"ACGT"[(cur + int(rng.integers(1, 4))) % 4]
+            elif t < 0.85:
+                frag.insert(q, b"ACGT"[int(rng.integers(0, 4))])
+            else:
+                del frag[q]
+        rd = np.frombuffer(bytes(frag[:read_len]), dtype=np.uint8)
+        if n_frac > 0 and rng.random() < n_frac:
+            rd = rd.copy()
+            rd[int(rng.integers(0, read_len))] = ord("N")
+        if strand[r]:
+            rd = COMP[rd[::-1]]
+        out.append(("r%d" % r, rd.tobytes()))
+    return out
+
+
+def write_fastq(path, reads):
+    with open(path, "wb") as f:
+        for nm, s in reads:
+            f.write(b"@" + nm.encode() + b"\n" + s + b"\n+\n" + b"I" * len(s) + b"\n")
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--ref-bp", type=int, required=True)
+    ap.add_argument("--ref-seed", type=int, default=4600)
+    ap.add_argument("--n-seqs", type=int, default=1)
+    ap.add_argument("--profile", default="auto")
+    ap.add_argument("--reads", type=int, default=0)
+    ap.add_argument("--read-len", type=int, default=150)
+    ap.add_argument("--read-seed", type=int, default=150)
+    ap.add_argument("--metric", default="edit")
+    ap.add_argument("--max-e", type=int, default=4)
+    ap.add_argument("--n-frac", type=float, default=0.0)
+    ap.add_argument("--out", required=True, help="output prefix")
+    a = ap.parse_args()
+    names, seqs = gen_reference(a.ref_bp, a.ref_seed, a.n_seqs, a.profile)
+    os.makedirs(os.path.dirname(os.path.abspath(a.out)), exist_ok=True)
+    write_fasta(a.out + ".fa", names, seqs)
+    if a.reads:
+        reads = gen_reads(seqs, a.reads, a.read_len, a.read_seed, a.metric,
+                          a.max_e, n_frac=a.n_frac,
+                          over_e=(a.max_e + 2))
+        write_fastq(a.out + ".fq", reads)
+
+
+if __name__ == "__main__":
+    main()
