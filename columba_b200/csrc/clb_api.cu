@@ -1,0 +1,232 @@
+// columba_b200 -- the product library: CUDA backend (sm_100a) + C ABI.
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -shared ...
+// (see __graft_entry__.build()).  There is no CPU execution path in this
+// translation unit: every task functor of clb_kernels.h runs inside
+// clb_kernel<K> on the device.
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "clb_pipeline.h"
+
+namespace clb {
+
+#define CLB_CUDA(x)                                                                                  \
+    do {                                                                                             \
+        cudaError_t e_ = (x);                                                                        \
+        if (e_ != cudaSuccess)                                                                       \
+            throw BackendError(std::string("CUDA error: ") + cudaGetErrorString(e_) + " at " #x);   \
+    } while (0)
+
+// One thread = one worker.  Static striding for uniform tasks; for tasks of
+// very different cost (searches, verifications, per-read filters) each warp
+// claims 32 tasks at a time from a global counter.
+template <class K>
+__global__ void __launch_bounds__(128) clb_kernel(const K k, u32 nMax, const u32* __restrict__ nDev, u32* workCtr) {
+    u32 n = nMax;
+    if (nDev) {
+        u32 v = *nDev;
+        n = v < nMax ? v : nMax;
+    }
+    const u32 worker = blockIdx.x * blockDim.x + threadIdx.x;
+    const u32 nWorkers = gridDim.x * blockDim.x;
+    typename K::State st;
+    k.begin(st, worker);
+    if (workCtr == nullptr) {
+        for (u32 i = worker; i < n; i += nWorkers)
+            k.run(st, i);
+    } else {
+        const u32 lane = threadIdx.x & 31;
+        for (;;) {
+            u32 base = 0;
+            if (lane == 0)
+                base = atomicAdd(workCtr, 32u);
+            base = __shfl_sync(0xFFFFFFFFu, base, 0);
+            if (base >= n)
+                break;
+            u32 i = base + lane;
+            if (i < n)
+                k.run(st, i);
+            __syncwarp();
+        }
+    }
+    k.end(st);
+}
+
+// exclusive scan of n u32 values by one block (out[n] = total)
+__global__ void __launch_bounds__(1024) clb_scan_kernel(const u32* __restrict__ in, u32* __restrict__ out, u32 n) {
+    __shared__ u32 part[1024];
+    const u32 tid = threadIdx.x, nt = blockDim.x;
+    const u32 per = (n + nt - 1) / nt;
+    const u32 b = tid * per, e = (b + per < n) ? b + per : n;
+    u32 sum = 0;
+    for (u32 i = b; i < e; i++)
+        sum += in[i];
+    part[tid] = sum;
+    __syncthreads();
+    for (u32 off = 1; off < nt; off <<= 1) {
+        u32 v = (tid >= off) ? part[tid - off] : 0;
+        __syncthreads();
+        part[tid] += v;
+        __syncthreads();
+    }
+    u32 run = part[tid] - sum;
+    for (u32 i = b; i < e; i++) {
+        u32 v = in[i];
+        out[i] = run;
+        run += v;
+    }
+    if (tid == nt - 1)
+        out[n] = part[nt - 1];
+}
+
+struct CudaBackend {
+    int device;
+    int numSMs = 0;
+    cudaStream_t stream = nullptr;
+    u32* workCtrs = nullptr; // pool of work counters, one per dynamic launch
+    u32 nextCtr = 0;
+    static const u32 N_CTRS = 64;
+    cudaEvent_t evBegin = nullptr, evEnd = nullptr, evStage[N_STAGES + 1];
+    int lastStage = -1;
+    u32 launches = 0;
+    bool timed = false;
+
+    static int deviceCount() {
+        int n = 0;
+        if (cudaGetDeviceCount(&n) != cudaSuccess)
+            return 0;
+        return n;
+    }
+    explicit CudaBackend(int dev) : device(dev) {
+        int n = 0;
+        cudaError_t e = cudaGetDeviceCount(&n);
+        if (e != cudaSuccess || n == 0)
+            throw BackendError(std::string("no CUDA device available (") +
+                               (e != cudaSuccess ? cudaGetErrorString(e) : "device count 0") +
+                               "); columba_b200 has no CPU fallback");
+        if (dev < 0 || dev >= n)
+            throw BackendError("invalid CUDA device ordinal " + std::to_string(dev));
+        CLB_CUDA(cudaSetDevice(dev));
+        CLB_CUDA(cudaDeviceGetAttribute(&numSMs, cudaDevAttrMultiProcessorCount, dev));
+        CLB_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+        CLB_CUDA(cudaMalloc(&workCtrs, N_CTRS * sizeof(u32)));
+        CLB_CUDA(cudaEventCreate(&evBegin));
+        CLB_CUDA(cudaEventCreate(&evEnd));
+        for (auto& ev : evStage)
+            CLB_CUDA(cudaEventCreate(&ev));
+    }
+    ~CudaBackend() {
+        cudaSetDevice(device);
+        if (stream)
+            cudaStreamSynchronize(stream);
+        if (workCtrs)
+            cudaFree(workCtrs);
+        if (evBegin)
+            cudaEventDestroy(evBegin);
+        if (evEnd)
+            cudaEventDestroy(evEnd);
+        for (auto& ev : evStage)
+            if (ev)
+                cudaEventDestroy(ev);
+        if (stream)
+            cudaStreamDestroy(stream);
+    }
+    void* alloc(size_t n) {
+        void* p = nullptr;
+        CLB_CUDA(cudaSetDevice(device));
+        CLB_CUDA(cudaMalloc(&p, n ? n : 16));
+        return p;
+    }
+    void free(void* p) {
+        cudaSetDevice(device);
+        cudaStreamSynchronize(stream);
+        cudaFree(p);
+    }
+    void zero(void* p, size_t n) { CLB_CUDA(cudaMemsetAsync(p, 0, n, stream)); }
+    void h2d(void* d, const void* s, size_t n) { CLB_CUDA(cudaMemcpyAsync(d, s, n, cudaMemcpyHostToDevice, stream)); }
+    void d2h(void* d, const void* s, size_t n) {
+        CLB_CUDA(cudaMemcpyAsync(d, s, n, cudaMemcpyDeviceToHost, stream));
+        CLB_CUDA(cudaStreamSynchronize(stream));
+    }
+    void sync() { CLB_CUDA(cudaStreamSynchronize(stream)); }
+    u32 blocksFor(int kind) const {
+        switch (kind) {
+        case WK_SEARCH: return (u32)numSMs * 2;   // x128 threads: 256 workers per SM (large slabs)
+        case WK_VERIFY: return (u32)numSMs * 8;
+        case WK_FILTER: return (u32)numSMs * 4;
+        default: return (u32)numSMs * 16;
+        }
+    }
+    u32 workers(int kind) { return blocksFor(kind) * 128; }
+    template <class K> void launch(const K& k, u32 nMax, const u32* nDev, int kind) {
+        if (nMax == 0)
+            return;
+        u32 blocks = blocksFor(kind);
+        u32* ctr = nullptr;
+        if (kind != WK_LIGHT) {
+            if (nextCtr >= N_CTRS)
+                throw BackendError("work counter pool exhausted");
+            ctr = workCtrs + nextCtr++;
+        } else if (!nDev) {
+            u32 need = (nMax + 127) / 128;
+            if (need < blocks)
+                blocks = need;
+        }
+        clb_kernel<K><<<blocks, 128, 0, stream>>>(k, nMax, nDev, ctr);
+        CLB_CUDA(cudaGetLastError());
+        launches++;
+    }
+    void exclusiveScan(const u32* in, u32* out, u32 n) {
+        clb_scan_kernel<<<1, 1024, 0, stream>>>(in, out, n);
+        CLB_CUDA(cudaGetLastError());
+        launches++;
+    }
+    void mark(int stage) {
+        if (stage >= 0 && stage < N_STAGES) {
+            CLB_CUDA(cudaEventRecord(evStage[stage + 1], stream));
+            lastStage = stage;
+        }
+    }
+    void beginBatch() {
+        CLB_CUDA(cudaSetDevice(device));
+        launches = 0;
+        nextCtr = 0;
+        lastStage = -1;
+        CLB_CUDA(cudaMemsetAsync(workCtrs, 0, N_CTRS * sizeof(u32), stream));
+        CLB_CUDA(cudaEventRecord(evBegin, stream));
+        CLB_CUDA(cudaEventRecord(evStage[0], stream));
+        timed = true;
+    }
+    void endBatch() {
+        CLB_CUDA(cudaEventRecord(evEnd, stream));
+        CLB_CUDA(cudaEventSynchronize(evEnd));
+    }
+    void fillTimings(float* stage, float* total, uint32_t* nl) {
+        for (int i = 0; i < N_STAGES; i++)
+            stage[i] = 0;
+        *total = 0;
+        *nl = launches;
+        if (!timed)
+            return;
+        // a batch that was re-run after a list overflow records the events of
+        // its last run; stage i spans evStage[i] .. evStage[i+1]
+        for (int i = 0; i <= lastStage; i++) {
+            float ms = 0;
+            if (cudaEventElapsedTime(&ms, evStage[i], evStage[i + 1]) == cudaSuccess)
+                stage[i] = ms;
+        }
+        float ms = 0;
+        if (cudaEventElapsedTime(&ms, evBegin, evEnd) == cudaSuccess)
+            *total = ms;
+    }
+};
+
+} // namespace clb
+
+#define CLB_BE clb::CudaBackend
+#include "clb_api_impl.h"
+#include "clb_index_build.h"

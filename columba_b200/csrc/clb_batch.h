@@ -1,0 +1,153 @@
+// columba_b200 -- per-batch buffers in HBM shared by all stages of the path.
+//
+// One batch = R reads mapped at one maximal distance k.  t = 2*read + strand
+// indexes a (read, strand) "sequence" (strand 1 = reverse complement), which is
+// the unit the reference maps with one matchWithSearches call
+// (src/searchstrategy.cpp:425-493).  Stages append variable-length records to
+// global lists with one atomic per record; capacities are set by the host and
+// an overflow raises an error bit so the host can re-run with larger lists.
+#pragma once
+#include "clb_index.h"
+#include "clb_scheme.h"
+
+namespace clb {
+
+// per (read,strand) partitioning result: parts + exact ranges + chosen scheme
+struct PartInfo {
+    u16 begin[MAXP];
+    u16 end[MAXP];
+    RangePair emr[MAXP];
+    u8 scheme; // index into DevStrategy::sc
+    u8 valid;  // 0: read too short for partitioning
+    u16 len;
+};
+
+// one search of the chosen scheme for one (read,strand)
+struct SearchTask {
+    u32 t;
+    u32 search;
+};
+
+// candidate for in-text verification: one SA row + how to turn its text
+// position into the start of the verification window
+struct Cand {
+    u32 t;
+    u32 row;      // SA row
+    u32 add;      // shift added to SA[row] (u32 wrap like the reference's length_t)
+    u32 sub;      // startDiff / lengthBefore: start = sum >= sub ? sum - sub : 0
+    u32 order;    // reference emission order within t (tie-break of the filter)
+    u8 fixedStart;
+    u8 maxED, minED;
+    u8 pad;
+};
+
+// occurrence in the index (an SA range), indexhelpers.h:1353-1535
+struct FMOccRec {
+    u32 t;
+    Range sa;
+    u32 depth;
+    u16 dist;
+    u16 shift;
+    u32 order;
+};
+
+// occurrence in the text before the per-read filter, indexhelpers.h:289-930
+struct TextOccRec {
+    u32 t;
+    u32 b, e;
+    u32 order;  // emission order of the candidate / index of the FM occurrence
+    u32 order2; // cluster centre within the candidate / row within the SA range
+    u8 dist;
+    u8 ncig;    // number of CIGAR runs (0 = none yet)
+    u8 cls;     // 0: found by in-text verification, 1: expanded from an FM occurrence
+    u8 pad;
+};
+
+// final occurrence handed back to the host
+struct OutOcc {
+    u32 read;
+    u32 seqID;
+    u32 pos;        // 0-based begin within the sequence
+    u32 end;        // end within the sequence
+    u32 indexBegin; // begin in the concatenated text
+    u8 strand;
+    u8 dist;
+    u8 ncig;
+    u8 trimmed;     // FOUND_WITH_TRIMMING
+};
+
+template <typename T> struct DevList {
+    T* data;
+    u32* count; // device counter
+    u32 cap;
+    CLB_HD u32 push(const T& v, u32* err, u32 errBit) const {
+        u32 i = atomAdd<u32>(count, 1u);
+        if (i >= cap) {
+            atomOr(err, errBit);
+            return 0xFFFFFFFFu;
+        }
+        data[i] = v;
+        return i;
+    }
+    // reserve n consecutive slots; returns first index or 0xFFFFFFFF
+    CLB_HD u32 reserve(u32 n, u32* err, u32 errBit) const {
+        u32 i = atomAdd<u32>(count, n);
+        if (i + n > cap || i + n < i) {
+            atomOr(err, errBit);
+            return 0xFFFFFFFFu;
+        }
+        return i;
+    }
+};
+
+struct Batch {
+    // inputs
+    const u8* readsAscii;  // concatenated reads
+    const u32* readOff;    // R+1 offsets
+    u32 R;
+    u32 maxLen;            // longest read of the batch
+    u32 k;                 // maximal distance
+    u32 minD;              // minimal distance (BEST mode strata)
+    u32 metric;            // METRIC_*
+    u32 partStrategy;      // PART_*
+    u32 cigW;              // CIGAR slots per occurrence (2k+2)
+    u32 noCigarFlag;       // -nC: do not keep CIGAR strings
+    // derived per (read,strand)
+    u8* codes;             // 2R x seqStride codes (0..3 ACGT, 4 other)
+    u32 seqStride;
+    u64* planes;           // 2R x 2 dirs x 4 chars x nw words
+    u32 nw;
+    PartInfo* parts;
+    // lists
+    DevList<SearchTask> tasks;
+    DevList<Cand> cands;
+    DevList<FMOccRec> fmOccs;
+    DevList<TextOccRec> textOccs;
+    u16* textCig;          // textOccs.cap x cigW
+    // per-read grouping
+    u32* fmCount;   // R+1
+    u32* fmStart;   // R+1 (exclusive scan)
+    u32* fmFill;    // R
+    u32* fmIdx;     // fmOccs.cap : indices grouped by read
+    u32* fmUnique;  // R : unique FM occurrences per read (after sort+unique)
+    u32* txCount;   // R+1
+    u32* txStart;   // R+1
+    u32* txFill;    // R
+    u32* txIdx;     // textOccs.cap
+    u32* txTmp;     // textOccs.cap : merge-sort scratch
+    u32* outCount;  // R+1 : surviving occurrences per read
+    u32* outStart;  // R+1
+    DevList<OutOcc> out;
+    u16* outCig;    // out.cap x cigW
+    // statistics
+    u64* counters;  // N_COUNTERS
+    u64* stats;     // N_STATS
+    u32* err;
+};
+
+CLB_HD const u8* seqCodes(const Batch& B, u32 t) { return B.codes + (size_t)t * B.seqStride; }
+CLB_HD u32 seqLen(const Batch& B, u32 t) { return B.readOff[(t >> 1) + 1] - B.readOff[t >> 1]; }
+// planes of sequence t in direction d (DIR_FWD: as is, DIR_BWD: reversed)
+CLB_HD const u64* seqPlanes(const Batch& B, u32 t, u32 d) { return B.planes + ((size_t)t * 2 + d) * 4 * B.nw; }
+
+} // namespace clb

@@ -1,0 +1,354 @@
+// columba_b200 -- stages 4-6: per-read dedup of index occurrences, SA-range ->
+// text positions, sort + unique + redundancy filter of the text occurrences,
+// CIGAR strings for index hits, assignment to a reference sequence (with
+// trimming at sequence boundaries).  One task per read.
+//
+// Replaces (reference): Occurrences::eraseDoublesFM src/indexhelpers.h:2135-2143,
+// eraseDoublesAndSortText :2149-2157, FMOcc::operator< :1506-1522 / == :1529-1533,
+// TextOcc::operator< :779-798 / == :811-813,
+// IndexInterface::getUniqueTextOccurrences src/indexinterface.cpp:1373-1491,
+// getTextOccHamming :1331-1371, generateCIGAR src/indexinterface.h:959-997,
+// findSeqName src/indexinterface.cpp:799-897, and the assignment loop of
+// SearchStrategy::generateOutputSingleEnd src/searchstrategy.cpp:1824-1856.
+//
+// The reference relies on stable sorts (DEVELOPER_MODE) and insertion order to
+// pick one of several equal occurrences; here the insertion order is an
+// explicit part of the sort key (strand, emission order), so any sorting
+// algorithm yields the reference's survivor.
+#pragma once
+#include "clb_verify.h"
+
+namespace clb {
+
+template <typename Less> CLB_HD void heapSortIdx(u32* a, u32 n, Less less) {
+    if (n < 2)
+        return;
+    // small segments: insertion sort
+    if (n <= 16) {
+        for (u32 i = 1; i < n; i++) {
+            u32 v = a[i];
+            u32 j = i;
+            while (j > 0 && less(v, a[j - 1])) {
+                a[j] = a[j - 1];
+                j--;
+            }
+            a[j] = v;
+        }
+        return;
+    }
+    for (u32 start = n / 2; start-- > 0;) {
+        u32 root = start;
+        for (;;) {
+            u32 child = 2 * root + 1;
+            if (child >= n)
+                break;
+            if (child + 1 < n && less(a[child], a[child + 1]))
+                child++;
+            if (!less(a[root], a[child]))
+                break;
+            u32 t = a[root];
+            a[root] = a[child];
+            a[child] = t;
+            root = child;
+        }
+    }
+    for (u32 end = n - 1; end > 0; end--) {
+        u32 t = a[0];
+        a[0] = a[end];
+        a[end] = t;
+        u32 root = 0;
+        for (;;) {
+            u32 child = 2 * root + 1;
+            if (child >= end)
+                break;
+            if (child + 1 < end && less(a[child], a[child + 1]))
+                child++;
+            if (!less(a[root], a[child]))
+                break;
+            u32 t2 = a[root];
+            a[root] = a[child];
+            a[child] = t2;
+            root = child;
+        }
+    }
+}
+
+struct FMLess {
+    const FMOccRec* d;
+    CLB_HD bool operator()(u32 x, u32 y) const {
+        const FMOccRec &a = d[x], &b = d[y];
+        if (a.sa.b != b.sa.b) return a.sa.b < b.sa.b;
+        if (a.dist != b.dist) return a.dist < b.dist;
+        u32 wa = a.sa.width(), wb = b.sa.width();
+        if (wa != wb) return wa < wb;
+        if (a.shift != b.shift) return a.shift < b.shift;
+        // insertion order of the reference: forward strand first, then
+        // search by search in emission order
+        if ((a.t & 1) != (b.t & 1)) return (a.t & 1) < (b.t & 1);
+        return a.order < b.order;
+    }
+};
+struct TxLess {
+    const TextOccRec* d;
+    CLB_HD bool operator()(u32 x, u32 y) const {
+        const TextOccRec &a = d[x], &b = d[y];
+        if (a.b != b.b) return a.b < b.b;
+        if (a.dist != b.dist) return a.dist < b.dist;
+        u32 wa = a.e <= a.b ? 0 : a.e - a.b, wb = b.e <= b.b ? 0 : b.e - b.b;
+        if (wa != wb) return wa < wb;
+        bool ca = a.ncig != 0, cb = b.ncig != 0;
+        if (ca != cb) return ca;
+        if (a.cls != b.cls) return a.cls < b.cls;
+        if (a.cls == 0 && (a.t & 1) != (b.t & 1)) return (a.t & 1) < (b.t & 1);
+        if (a.order != b.order) return a.order < b.order;
+        return a.order2 < b.order2;
+    }
+};
+
+struct FilterScratch {
+    void* rows;  // rowsCap rows of Row<u128>
+    u16* ops;    // 2 x cigW
+    u32 rowsCap;
+};
+
+// generateCIGAR, indexinterface.h:959-997: re-align the read against text[b,e)
+CLB_HD u32 cigarForOcc(const IndexView& ix, const Batch& B, u32 t, u32 b, u32 e, u32 dist, FilterScratch& fs,
+                       u16* ops, LocalCtr& lc) {
+    PartSeq ps = fullSeq(B, t);
+    TextRef ref;
+    ref.ix = &ix;
+    ref.start = b;
+    u32 ee = tmin(e, ix.textLength);
+    u32 refLen = ee <= b ? 0u : ee - b;
+    lc.c[CIGARS_IN_INDEX]++;
+    if (refLen + 1 > fs.rowsCap) {
+        atomOr(B.err, ERR_ROWS_OVERFLOW);
+        return 0;
+    }
+    u32 n;
+    if (BPC<u64>::MAX_ED >= dist)
+        n = bpFindCigar<u64>((Row<u64>*)fs.rows, ps, ref, refLen, dist, ops, B.cigW);
+    else
+        n = bpFindCigar<u128>((Row<u128>*)fs.rows, ps, ref, refLen, dist, ops, B.cigW);
+    if (n == 0xFFFFFFFFu) {
+        atomOr(B.err, ERR_INTERNAL);
+        return 0;
+    }
+    return n;
+}
+
+// stage 4 task: dedup the FM occurrences of read r and expand them to text
+// occurrences.
+CLB_HD void fmPerReadTask(const IndexView& ix, const Batch& B, u32 r, FilterScratch& fs, LocalCtr& lc) {
+    const u32 s0 = B.fmStart[r], s1 = B.fmStart[r + 1];
+    if (s1 == s0)
+        return;
+    u32* idx = B.fmIdx + s0;
+    const u32 n = s1 - s0;
+    const FMOccRec* d = B.fmOccs.data;
+    FMLess less;
+    less.d = d;
+    heapSortIdx(idx, n, less);
+    // unique (adjacent)
+    u32 m = 0;
+    for (u32 i = 0; i < n; i++) {
+        if (m > 0) {
+            const FMOccRec &a = d[idx[m - 1]], &b = d[idx[i]];
+            if (a.sa.b == b.sa.b && a.sa.e == b.sa.e && a.dist == b.dist && a.depth == b.depth &&
+                a.shift == b.shift && (a.t & 1) == (b.t & 1))
+                continue;
+        }
+        idx[m++] = idx[i];
+    }
+    const u32 hamSize = d[idx[0]].depth;
+    for (u32 j = 0; j < m; j++) {
+        const FMOccRec f = d[idx[j]];
+        const u32 w = f.sa.width();
+        lc.c[TOTAL_REPORTED_POSITIONS] += w;
+        u32 at = B.textOccs.reserve(w, B.err, ERR_TEXTOCC_OVERFLOW);
+        if (at == 0xFFFFFFFFu)
+            return;
+        const bool edit = B.metric == METRIC_EDIT;
+        const bool calc = edit && !B.noCigarFlag && w > 10; // CIGAR_THRESHOLD
+        u32 ncig = 0;
+        for (u32 i = 0; i < w; i++) {
+            u32 pos = findSA(ix, f.sa.b + i, lc.s[ST_LF_STEPS]);
+            TextOccRec o;
+            o.t = f.t;
+            o.b = edit ? pos + f.shift : pos;
+            o.e = o.b + (edit ? f.depth : hamSize);
+            o.order = j;
+            o.order2 = i;
+            o.dist = (u8)f.dist;
+            o.cls = 1;
+            o.pad = 0;
+            o.ncig = 0;
+            u16* dst = B.textCig + (size_t)(at + i) * B.cigW;
+            if (!edit) {
+                if (!B.noCigarFlag) {
+                    o.ncig = 1;
+                    dst[0] = (u16)((hamSize << 2) | CIG_M);
+                }
+            } else if (calc) {
+                if (i == 0) {
+                    ncig = cigarForOcc(ix, B, f.t, o.b, o.e, f.dist, fs, fs.ops, lc);
+                }
+                o.ncig = (u8)ncig;
+                for (u32 q = 0; q < ncig; q++)
+                    dst[q] = fs.ops[q];
+            }
+            B.textOccs.data[at + i] = o;
+        }
+        lc.s[ST_TEXT_OCCS] += w;
+    }
+}
+
+struct TrimSink {
+    VerifyHit best;
+    bool any;
+    u16* bestOps;
+    CLB_HD void operator()(const VerifyHit& h, const u16* ops) {
+        bool better = !any;
+        if (any) { // TextOcc::operator<
+            u32 wa = h.e - h.b, wb = best.e - best.b;
+            if (h.b != best.b) better = h.b < best.b;
+            else if (h.dist != best.dist) better = h.dist < best.dist;
+            else if (wa != wb) better = wa < wb;
+            else better = false;
+        }
+        if (better) {
+            best = h;
+            any = true;
+            for (u32 i = 0; i < h.ncig && h.ncig != 0xFFFFFFFFu; i++)
+                bestOps[i] = ops[i];
+        }
+    }
+};
+
+// stage 6 task: filter the text occurrences of read r and write the output
+CLB_HD void txPerReadTask(const IndexView& ix, const Batch& B, u32 r, FilterScratch& fs, LocalCtr& lc) {
+    const u32 s0 = B.txStart[r], s1 = B.txStart[r + 1];
+    B.outStart[r] = 0;
+    B.outCount[r] = 0;
+    if (s1 == s0)
+        return;
+    u32* idx = B.txIdx + s0;
+    const u32 n = s1 - s0;
+    TextOccRec* d = B.textOccs.data;
+    TxLess less;
+    less.d = d;
+    heapSortIdx(idx, n, less);
+    u32 m = 0;
+    for (u32 i = 0; i < n; i++) {
+        if (m > 0) {
+            const TextOccRec &a = d[idx[m - 1]], &b = d[idx[i]];
+            if (a.b == b.b && a.e == b.e && a.dist == b.dist)
+                continue;
+        }
+        idx[m++] = idx[i];
+    }
+    const bool edit = B.metric == METRIC_EDIT;
+    u32 nOut = m;
+    if (edit) { // redundancy filter, indexinterface.cpp:1451-1485
+        const u32 maxDiff = 2 * B.k;
+        u32 prevBegin = 0xFFFFFFFFu, prevDepth = 0xFFFFFFFFu, prevED = B.k + 1;
+        nOut = 0;
+        for (u32 i = 0; i < m; i++) {
+            const TextOccRec& o = d[idx[i]];
+            u32 diff = o.b > prevBegin ? o.b - prevBegin : prevBegin - o.b;
+            if (diff == 0)
+                continue;
+            u32 width = o.e <= o.b ? 0 : o.e - o.b;
+            if (diff <= maxDiff) {
+                if (o.dist > prevED || (o.dist == prevED && width >= prevDepth))
+                    continue;
+                nOut--;
+            }
+            prevBegin = o.b;
+            prevED = o.dist;
+            prevDepth = width;
+            idx[nOut++] = idx[i];
+        }
+    }
+    u32 at = B.out.reserve(nOut, B.err, ERR_OUT_OVERFLOW);
+    if (at == 0xFFFFFFFFu)
+        return;
+    u32 w = 0;
+    for (u32 i = 0; i < nOut; i++) {
+        TextOccRec o = d[idx[i]];
+        u16* cig = B.textCig + (size_t)idx[i] * B.cigW;
+        if (edit && !B.noCigarFlag && o.ncig == 0) {
+            o.ncig = (u8)cigarForOcc(ix, B, o.t, o.b, o.e, o.dist, fs, cig, lc);
+        }
+        // findSeqName, indexinterface.cpp:799-897
+        u32 lo = 0, hi = ix.numSeq + 1; // upper_bound over seqStart[0..numSeq]
+        while (lo < hi) {
+            u32 mid = (lo + hi) >> 1;
+            if (ix.seqStart[mid] <= o.b)
+                lo = mid + 1;
+            else
+                hi = mid;
+        }
+        u32 index = lo - 1;
+        OutOcc out;
+        out.read = r;
+        out.strand = (u8)(o.t & 1);
+        u32 ncig = o.ncig;
+        const u16* src = cig;
+        if (o.e <= ix.seqStart[index + 1]) {
+            out.trimmed = 0;
+            out.indexBegin = o.b;
+            out.pos = o.b - ix.seqStart[index];
+            out.end = o.e - ix.seqStart[index];
+            out.dist = o.dist;
+        } else {
+            if (!edit)
+                continue;
+            u32 nb, ne;
+            const u32 largest = B.k;
+            if ((ix.seqStart[index + 1] - o.b) <= largest) {
+                index++;
+                nb = ix.seqStart[index];
+                ne = tmin(o.e, ix.seqStart[index + 1]);
+            } else if ((o.e - ix.seqStart[index + 1]) <= largest) {
+                nb = o.b;
+                ne = ix.seqStart[index + 1];
+            } else
+                continue;
+            // inTextVerificationOneString, fmindex.cpp:312-342
+            TrimSink sink;
+            sink.any = false;
+            sink.bestOps = fs.ops + B.cigW;
+            bool considered = true, ok;
+            lc.c[IN_TEXT_STARTED]++;
+            if (use64(1, largest))
+                ok = verifyWindow<u64>(ix, B, o.t, (Row<u64>*)fs.rows, nb, ne, 1, largest, 0, fs.ops, B.cigW, lc,
+                                       considered, sink);
+            else
+                ok = verifyWindow<u128>(ix, B, o.t, (Row<u128>*)fs.rows, nb, ne, 1, largest, 0, fs.ops, B.cigW, lc,
+                                        considered, sink);
+            if (!ok && considered)
+                lc.c[ABORTED_IN_TEXT_VERIF]++;
+            if (!sink.any)
+                continue;
+            out.trimmed = 1;
+            out.indexBegin = sink.best.b;
+            out.pos = sink.best.b - ix.seqStart[index];
+            out.end = sink.best.e - ix.seqStart[index];
+            out.dist = (u8)sink.best.dist;
+            ncig = B.noCigarFlag ? 0 : sink.best.ncig;
+            src = sink.bestOps;
+        }
+        out.seqID = index;
+        out.ncig = (u8)ncig;
+        B.out.data[at + w] = out;
+        u16* dst = B.outCig + (size_t)(at + w) * B.cigW;
+        for (u32 q = 0; q < ncig; q++)
+            dst[q] = src[q];
+        w++;
+    }
+    B.outStart[r] = at;
+    B.outCount[r] = w;
+}
+
+} // namespace clb

@@ -1,0 +1,187 @@
+// columba_b200 -- HBM layout of the bidirectional FM-index and the rank /
+// extend / locate primitives on it.
+//
+// Replaces (reference, Vanilla flavour):
+//   BitvecIntl<4>::rank            src/bitvec.h:356-372
+//   BWTRepresentation::occ/cumOcc  src/fmindex/bwtrepr.h:80-107
+//   FMIndex::findRangesWithExtraChar{Backward,Forward}, findRangeWithExtraChar
+//   BackwardUniDirectional         src/fmindex/fmindex.cpp:137-243
+//   FMIndex::findLF / findSA       src/fmindex/fmindex.cpp:47-60
+//   SparseSuffixArray::operator[] / get   src/fmindex/suffixArray.h:131-148
+//
+// Layout (one record = one 32-byte DRAM sector = one rank lookup):
+//   BwtRec  : occ counts of A,C,G,T before the 64-position block (4 x u32) and
+//             the 64 symbols as two bit planes (lo,hi) of the 2-bit code.
+//             The sentinel '$' is stored as code 0 and corrected by position.
+//   SsaRec  : 64 marker bits + number of sampled rows before the block.
+//   text    : 2 bits per character, 16 characters per u32.
+#pragma once
+#include "clb_common.h"
+
+namespace clb {
+
+struct alignas(32) BwtRec {
+    u32 cnt[4];
+    u64 lo, hi;
+};
+struct alignas(16) SsaRec {
+    u64 bits;
+    u32 rank;
+    u32 pad;
+};
+
+struct BwtView {
+    const BwtRec* rec;
+    u32 dollarPos;
+};
+
+struct IndexView {
+    BwtView fwd, rev;
+    u32 C[5];        // C[c] = number of characters smaller than c ($ACGT order)
+    u32 textLength;  // including the final '$'
+    const u32* text; // 2-bit packed
+    const SsaRec* ssaRec;
+    const u32* ssa;
+    const RangePair* kmer; // dense 4^K table (indexinterface.cpp:294-335)
+    u32 K;
+    const u32* seqStart; // numSeq+1 entries (.pos)
+    u32 numSeq;
+    u32 switchPoint; // in-text verification switch point
+    u32 noCigar;
+};
+
+CLB_HD BwtRec loadRec(const BwtRec* p) {
+#if defined(__CUDA_ARCH__)
+    // one 32-byte sector, read through the non-coherent path as two 16-byte
+    // vector loads
+    const uint4* q = reinterpret_cast<const uint4*>(p);
+    uint4 a = __ldg(q), b = __ldg(q + 1);
+    BwtRec r;
+    r.cnt[0] = a.x; r.cnt[1] = a.y; r.cnt[2] = a.z; r.cnt[3] = a.w;
+    r.lo = ((u64)b.y << 32) | b.x;
+    r.hi = ((u64)b.w << 32) | b.z;
+    return r;
+#else
+    return *p;
+#endif
+}
+
+// occ of A,C,G,T in BWT[0,p)
+CLB_HD void occ4(const BwtView& v, u32 p, u32 o[4]) {
+    BwtRec r = loadRec(v.rec + (p >> 6));
+    u32 off = p & 63;
+    u64 m = (1ull << off) - 1ull;
+    u64 lo = r.lo & m, hi = r.hi & m;
+    u32 nT = popc64(hi & lo), nG = popc64(hi) - nT, nC = popc64(lo) - nT;
+    u32 nA = off - nT - nG - nC;
+    // '$' is stored as an 'A'
+    if ((v.dollarPos >> 6) == (p >> 6) && v.dollarPos < p)
+        nA--;
+    o[0] = r.cnt[0] + nA;
+    o[1] = r.cnt[1] + nC;
+    o[2] = r.cnt[2] + nG;
+    o[3] = r.cnt[3] + nT;
+}
+// symbol (0..3) of BWT[p]; caller handles p == dollarPos
+CLB_HD u32 bwtSym(const BwtRec& r, u32 off) {
+    return (u32)((r.lo >> off) & 1) | ((u32)((r.hi >> off) & 1) << 1);
+}
+
+// Extend a range pair by every character at once.  mode: DIR_FWD uses the BWT
+// of the reversed text and the rev range as the driving range; DIR_BWD uses
+// the forward BWT and the SA range.  Children with an empty range have
+// width 0.  Two rank lookups.
+CLB_HD void extendAll(const IndexView& ix, int dir, bool uniBack, const RangePair& p, RangePair ch[4]) {
+    const BwtView& bw = (dir == DIR_BWD) ? ix.fwd : ix.rev;
+    const Range t = (dir == DIR_BWD) ? p.sa : p.rev;
+    u32 ob[4], oe[4];
+    occ4(bw, t.b, ob);
+    occ4(bw, t.e, oe);
+    u32 s = (dir == DIR_BWD) ? p.rev.b : p.sa.b;
+    u32 x = (t.b <= bw.dollarPos && bw.dollarPos < t.e) ? 1u : 0u;
+    for (int c = 0; c < 4; c++) {
+        Range r1;
+        r1.b = ob[c] + ix.C[c + 1];
+        r1.e = oe[c] + ix.C[c + 1];
+        u32 w = r1.width();
+        Range r2;
+        r2.b = s + x;
+        r2.e = s + x + w;
+        x += oe[c] - ob[c];
+        if (uniBack) {
+            ch[c].sa = r1;
+            ch[c].rev.b = 0;
+            ch[c].rev.e = 0;
+        } else if (dir == DIR_BWD) {
+            ch[c].sa = r1;
+            ch[c].rev = r2;
+        } else {
+            ch[c].sa = r2;
+            ch[c].rev = r1;
+        }
+    }
+}
+// single character (code 0..3) -- indexinterface.cpp:1034-1049 (addChar)
+CLB_HD bool extendOne(const IndexView& ix, int dir, bool uniBack, u32 c, RangePair& r) {
+    const BwtView& bw = (dir == DIR_BWD) ? ix.fwd : ix.rev;
+    const Range t = (dir == DIR_BWD) ? r.sa : r.rev;
+    u32 ob[4], oe[4];
+    occ4(bw, t.b, ob);
+    occ4(bw, t.e, oe);
+    u32 s = (dir == DIR_BWD) ? r.rev.b : r.sa.b;
+    u32 x = (t.b <= bw.dollarPos && bw.dollarPos < t.e) ? 1u : 0u;
+    for (u32 i = 0; i < c; i++)
+        x += oe[i] - ob[i];
+    Range r1;
+    r1.b = ob[c] + ix.C[c + 1];
+    r1.e = oe[c] + ix.C[c + 1];
+    u32 w = r1.width();
+    Range r2;
+    r2.b = s + x;
+    r2.e = s + x + w;
+    if (uniBack) {
+        r.sa = r1;
+        r.rev.b = r.rev.e = 0;
+    } else if (dir == DIR_BWD) {
+        r.sa = r1;
+        r.rev = r2;
+    } else {
+        r.sa = r2;
+        r.rev = r1;
+    }
+    return !r1.empty();
+}
+
+CLB_HD RangePair completeRange(const IndexView& ix) { return mkPair(0, ix.textLength, 0, ix.textLength); }
+// fmindex.cpp:434-445
+CLB_HD RangePair rangeOfSingleChar(const IndexView& ix, u32 code) {
+    if (code > 3)
+        return emptyPair();
+    u32 b = ix.C[code + 1], e = (code < 3) ? ix.C[code + 2] : ix.textLength;
+    return mkPair(b, e, b, e);
+}
+
+// locate one SA row: LF-walk to a sampled row (fmindex.cpp:47-60)
+CLB_HD u32 findSA(const IndexView& ix, u32 i, u64& lfSteps) {
+    u32 l = 0;
+    for (;;) {
+        SsaRec s = ix.ssaRec[i >> 6];
+        u32 off = i & 63;
+        if ((s.bits >> off) & 1)
+            return ix.ssa[s.rank + popc64(s.bits & ((1ull << off) - 1ull))] + l;
+        BwtRec r = loadRec(ix.fwd.rec + (i >> 6));
+        u32 c = bwtSym(r, off);
+        u64 m = (1ull << off) - 1ull;
+        u64 plane = ((c & 1) ? r.lo : ~r.lo) & ((c & 2) ? r.hi : ~r.hi) & m;
+        u32 occ = r.cnt[c] + popc64(plane);
+        if (c == 0 && (ix.fwd.dollarPos >> 6) == (i >> 6) && ix.fwd.dollarPos < i)
+            occ--;
+        i = ix.C[c + 1] + occ;
+        l++;
+        lfSteps++;
+    }
+}
+
+CLB_HD u32 textAt(const IndexView& ix, u32 p) { return (ix.text[p >> 4] >> ((p & 15) * 2)) & 3u; }
+
+} // namespace clb

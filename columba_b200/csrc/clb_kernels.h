@@ -1,0 +1,232 @@
+// columba_b200 -- the kernels of the path as task functors.  A backend runs
+// functor K over n tasks with W workers: worker w calls begin(), then run(i)
+// for its share of the tasks, then end().  The CUDA backend (clb_cuda.cuh)
+// launches `clb_kernel<K>` with one thread per worker; tests/hostemu runs the
+// same functors in a loop on the CPU to unit-test the kernel logic.
+#pragma once
+#include "clb_filter.h"
+#include "clb_search.h"
+
+namespace clb {
+
+struct WorkerCtr {
+    LocalCtr lc;
+};
+
+// stage 0
+struct PrepKernel {
+    Batch B;
+    struct State {};
+    CLB_HD void begin(State&, u32) const {}
+    CLB_HD void run(State&, u32 i) const { prepTask(B, i); }
+    CLB_HD void end(State&) const {}
+};
+
+// stage 1
+struct PartitionKernel {
+    IndexView ix;
+    const DevStrategy* st;
+    Batch B;
+    typedef WorkerCtr State;
+    CLB_HD void begin(State& s, u32) const { s.lc.clear(); }
+    CLB_HD void run(State& s, u32 t) const { partitionTask(ix, *st, B, t, s.lc); }
+    CLB_HD void end(State& s) const { s.lc.flush(B.counters, B.stats); }
+};
+
+// stage 2
+template <typename W> struct SearchKernel {
+    IndexView ix;
+    const DevStrategy* st;
+    Batch B;
+    u8* slabs;
+    size_t slabBytes;
+    u32 stackCap, rowsCap, nFrames;
+    struct State {
+        LocalCtr lc;
+        SearchScratch<W> sc;
+    };
+    CLB_HD void begin(State& s, u32 worker) const {
+        s.lc.clear();
+        s.sc = carveSearchScratch<W>(slabs + (size_t)worker * slabBytes, stackCap, rowsCap, nFrames);
+    }
+    CLB_HD void run(State& s, u32 i) const {
+        const SearchTask task = B.tasks.data[i];
+        const PartInfo& pi = B.parts[task.t];
+        const DevSearch& se = st->sc[pi.scheme].s[task.search];
+        SearchCtx<W> X(ix, B, se, pi, s.sc, s.lc, task.t, task.search);
+        s.lc.s[ST_SEARCH_TASKS]++;
+        if (B.metric == METRIC_EDIT)
+            editSearchTask<W>(X);
+        else
+            hammingSearchTask<W>(X);
+        if (X.err)
+            atomOr(B.err, X.err);
+    }
+    CLB_HD void end(State& s) const { s.lc.flush(B.counters, B.stats); }
+};
+
+// stage 3
+struct VerifyKernel {
+    IndexView ix;
+    Batch B;
+    u8* slabs;
+    size_t slabBytes;
+    u32 rowsCap;
+    struct State {
+        LocalCtr lc;
+        VerifyScratch vs;
+    };
+    CLB_HD void begin(State& s, u32 worker) const {
+        s.lc.clear();
+        u8* p = slabs + (size_t)worker * slabBytes;
+        s.vs.ops = (u16*)p;
+        s.vs.rows = p + (((size_t)B.cigW * 2 * sizeof(u16) + 63) & ~(size_t)63);
+        s.vs.rowsCap = rowsCap;
+    }
+    CLB_HD void run(State& s, u32 i) const {
+        s.lc.s[ST_CANDIDATES]++;
+        if (B.metric == METRIC_EDIT)
+            verifyEditTask(ix, B, i, s.vs, s.lc);
+        else
+            verifyHammingTask(ix, B, i, s.lc);
+    }
+    CLB_HD void end(State& s) const { s.lc.flush(B.counters, B.stats); }
+};
+
+// grouping by read: count / scatter
+struct FmCountKernel {
+    Batch B;
+    struct State {};
+    CLB_HD void begin(State&, u32) const {}
+    CLB_HD void run(State&, u32 i) const { atomAdd<u32>(B.fmCount + (B.fmOccs.data[i].t >> 1), 1u); }
+    CLB_HD void end(State&) const {}
+};
+struct FmScatterKernel {
+    Batch B;
+    struct State {};
+    CLB_HD void begin(State&, u32) const {}
+    CLB_HD void run(State&, u32 i) const {
+        u32 r = B.fmOccs.data[i].t >> 1;
+        B.fmIdx[B.fmStart[r] + atomAdd<u32>(B.fmFill + r, 1u)] = i;
+    }
+    CLB_HD void end(State&) const {}
+};
+struct TxCountKernel {
+    Batch B;
+    struct State {};
+    CLB_HD void begin(State&, u32) const {}
+    CLB_HD void run(State&, u32 i) const { atomAdd<u32>(B.txCount + (B.textOccs.data[i].t >> 1), 1u); }
+    CLB_HD void end(State&) const {}
+};
+struct TxScatterKernel {
+    Batch B;
+    struct State {};
+    CLB_HD void begin(State&, u32) const {}
+    CLB_HD void run(State&, u32 i) const {
+        u32 r = B.textOccs.data[i].t >> 1;
+        B.txIdx[B.txStart[r] + atomAdd<u32>(B.txFill + r, 1u)] = i;
+    }
+    CLB_HD void end(State&) const {}
+};
+
+// stages 4 and 6
+struct FilterState {
+    LocalCtr lc;
+    FilterScratch fs;
+};
+CLB_HD void carveFilter(FilterState& s, u8* p, u32 cigW, u32 rowsCap) {
+    s.lc.clear();
+    s.fs.ops = (u16*)p;
+    s.fs.rows = p + (((size_t)cigW * 2 * sizeof(u16) + 63) & ~(size_t)63);
+    s.fs.rowsCap = rowsCap;
+}
+struct FmPerReadKernel {
+    IndexView ix;
+    Batch B;
+    u8* slabs;
+    size_t slabBytes;
+    u32 rowsCap;
+    typedef FilterState State;
+    CLB_HD void begin(State& s, u32 worker) const { carveFilter(s, slabs + (size_t)worker * slabBytes, B.cigW, rowsCap); }
+    CLB_HD void run(State& s, u32 r) const { fmPerReadTask(ix, B, r, s.fs, s.lc); }
+    CLB_HD void end(State& s) const { s.lc.flush(B.counters, B.stats); }
+};
+struct TxPerReadKernel {
+    IndexView ix;
+    Batch B;
+    u8* slabs;
+    size_t slabBytes;
+    u32 rowsCap;
+    typedef FilterState State;
+    CLB_HD void begin(State& s, u32 worker) const { carveFilter(s, slabs + (size_t)worker * slabBytes, B.cigW, rowsCap); }
+    CLB_HD void run(State& s, u32 r) const {
+        txPerReadTask(ix, B, r, s.fs, s.lc);
+        u32 n = B.outCount[r];
+        if (n) {
+            s.lc.c[MAPPED_READS]++;
+            s.lc.c[TOTAL_UNIQUE_MATCHES] += n;
+        }
+        s.lc.c[NUMBER_OF_READS]++;
+    }
+    CLB_HD void end(State& s) const { s.lc.flush(B.counters, B.stats); }
+};
+
+// k-mer table construction (indexinterface.cpp:294-335), level by level:
+// entry `code` of level d extends entry code>>2 of level d-1 by one character
+// in the forward direction.
+struct KmerLevelKernel {
+    IndexView ix;
+    const RangePair* prev;
+    RangePair* cur;
+    struct State {};
+    CLB_HD void begin(State&, u32) const {}
+    CLB_HD void run(State&, u32 code) const {
+        RangePair r = prev[code >> 2];
+        if (r.empty()) {
+            cur[code] = emptyPair();
+            return;
+        }
+        if (!extendOne(ix, DIR_FWD, false, code & 3, r))
+            r = emptyPair();
+        cur[code] = r;
+    }
+    CLB_HD void end(State&) const {}
+};
+
+// index parity micro-kernels (exposed through the C ABI for unit tests)
+struct Occ4Kernel {
+    IndexView ix;
+    u32 reverse;
+    const u32* pos;
+    u32* out; // 4 per position
+    struct State {};
+    CLB_HD void begin(State&, u32) const {}
+    CLB_HD void run(State&, u32 i) const { occ4(reverse ? ix.rev : ix.fwd, pos[i], out + 4 * (size_t)i); }
+    CLB_HD void end(State&) const {}
+};
+struct ExtendKernel {
+    IndexView ix;
+    u32 mode; // 0 fwd, 1 bwd, 2 uni-directional bwd
+    const RangePair* parents;
+    RangePair* out; // 4 per parent
+    struct State {};
+    CLB_HD void begin(State&, u32) const {}
+    CLB_HD void run(State&, u32 i) const {
+        extendAll(ix, mode == 0 ? DIR_FWD : DIR_BWD, mode == 2, parents[i], out + 4 * (size_t)i);
+    }
+    CLB_HD void end(State&) const {}
+};
+struct FindSAKernel {
+    IndexView ix;
+    const u32* rows;
+    u32* out;
+    struct State {};
+    CLB_HD void begin(State&, u32) const {}
+    CLB_HD void run(State&, u32 i) const {
+        u64 lf = 0;
+        out[i] = findSA(ix, rows[i], lf);
+    }
+    CLB_HD void end(State&) const {}
+};
+
+} // namespace clb

@@ -1,0 +1,281 @@
+// columba_b200 -- stage 0/1: sequence preparation, read partitioning, scheme
+// selection, task generation.  One task per (read,strand).
+//
+// Replaces (reference): SearchStrategy::partition src/searchstrategy.cpp:141-156,
+// seed :381-419, partitionDynamic :299-379 (+ seedIfNoKmers :255-271,
+// extendParts :283-297), partitionUniform :194-209, partitionOptimalStatic /
+// setParts :212-238, calculateExactMatchRanges :158-190,
+// MultipleSchemes::createSearches src/searchstrategy.h:2505-2537, and the head
+// of matchWithSearches src/searchstrategy.cpp:425-476 (immediate switch to
+// in-text verification for narrow parts) and of doRecSearch :1181-1254 (which
+// searches start at all).
+#pragma once
+#include "clb_batch.h"
+
+namespace clb {
+
+CLB_HD u32 asciiCode(u8 c) {
+    switch (c) {
+    case 'A': case 'a': return 0;
+    case 'C': case 'c': return 1;
+    case 'G': case 'g': return 2;
+    case 'T': case 't': return 3;
+    default: return 4;
+    }
+}
+
+// stage 0: codes of the sequence (strand 1 = reverse complement, nucleotide.h)
+// and its "equals A/C/G/T" bit planes, forward and reversed.
+CLB_HD void prepTask(const Batch& B, u32 t) {
+    const u32 r = t >> 1, strand = t & 1;
+    const u32 off = B.readOff[r], len = B.readOff[r + 1] - off;
+    u8* codes = B.codes + (size_t)t * B.seqStride;
+    u64* pf = B.planes + ((size_t)t * 2 + DIR_FWD) * 4 * B.nw;
+    u64* pb = B.planes + ((size_t)t * 2 + DIR_BWD) * 4 * B.nw;
+    for (u32 i = 0; i < 4 * B.nw; i++) {
+        pf[i] = 0;
+        pb[i] = 0;
+    }
+    for (u32 i = 0; i < len; i++) {
+        u32 c;
+        if (strand == 0) {
+            c = asciiCode(B.readsAscii[off + i]);
+        } else {
+            c = asciiCode(B.readsAscii[off + len - 1 - i]);
+            if (c < 4)
+                c = 3 - c;
+        }
+        codes[i] = (u8)c;
+        if (c < 4) {
+            pf[c * B.nw + (i >> 6)] |= 1ull << (i & 63);
+            u32 ri = len - 1 - i;
+            pb[c * B.nw + (ri >> 6)] |= 1ull << (ri & 63);
+        }
+    }
+}
+
+// indexinterface.h:590-595
+CLB_HD RangePair lookUpKmer(const IndexView& ix, const u8* p) {
+    u32 code = 0;
+    for (u32 i = 0; i < ix.K; i++) {
+        if (p[i] > 3)
+            return emptyPair();
+        code = (code << 2) | p[i];
+    }
+    return ix.kmer[code];
+}
+CLB_HD bool addChar(const IndexView& ix, int dir, bool uni, u32 c, RangePair& r, LocalCtr& lc) {
+    if (c < 4) {
+        lc.s[ST_RANK_LOOKUPS] += 2;
+        if (extendOne(ix, dir, uni, c, r)) {
+            lc.c[NODE_COUNTER]++;
+            return true;
+        }
+    }
+    r = emptyPair();
+    return false;
+}
+// indexinterface.cpp:1016-1032; chars pat[b..e) read in direction dir
+CLB_HD RangePair matchString(const IndexView& ix, int dir, bool uni, const u8* pat, u32 b, u32 e, int readDir,
+                             RangePair r, LocalCtr& lc) {
+    u32 n = e <= b ? 0 : e - b;
+    for (u32 i = 0; i < n; i++) {
+        u32 c = (readDir == DIR_FWD) ? pat[b + i] : pat[e - 1 - i];
+        if (!addChar(ix, dir, uni, c, r, lc))
+            break;
+    }
+    return r;
+}
+
+struct PartScratch {
+    u32 b[MAXP], e[MAXP];
+    RangePair emr[MAXP];
+};
+
+CLB_HD void calcExactRanges(const IndexView& ix, const u8* pat, u32 P, PartScratch& ps, LocalCtr& lc) {
+    const u32 ws = ix.K;
+    for (u32 i = 0; i < P; ++i) {
+        u32 size = ps.e[i] <= ps.b[i] ? 0 : ps.e[i] - ps.b[i];
+        u32 start = ps.b[i] + ((size >= ws) ? ws : 0);
+        RangePair init = (size >= ws) ? lookUpKmer(ix, pat + ps.b[i]) : completeRange(ix);
+        ps.emr[i] = matchString(ix, DIR_FWD, false, pat, start, ps.e[i], DIR_FWD, init, lc);
+    }
+    u32 lb = ps.b[P - 1], le = ps.e[P - 1];
+    u32 size = le <= lb ? 0 : le - lb;
+    u32 end = (size >= ws) ? le - ws : le;
+    RangePair init = (size >= ws) ? lookUpKmer(ix, pat + end) : completeRange(ix);
+    ps.emr[P - 1] = matchString(ix, DIR_BWD, true, pat, lb, end, DIR_BWD, init, lc);
+}
+
+CLB_HD void partitionDynamic(const IndexView& ix, const DevStrategy& st, const u8* pat, u32 pSize, u32 P,
+                             PartScratch& ps, LocalCtr& lc) {
+    // seed(), searchstrategy.cpp:381-419
+    const bool useK = ((u64)P * ix.K < ((u64)pSize * 2) / 3) && pSize >= st.useKmerCutOff;
+    const int wSize = useK ? (int)ix.K : 1;
+    ps.b[0] = 0;
+    for (u32 i = 1; i + 1 < P; i++)
+        ps.b[i] = (u32)(int)dsub(dmul(st.seeds[i - 1], (double)pSize), (double)(wSize / 2));
+    for (u32 i = 0; i + 1 < P; i++)
+        ps.e[i] = ps.b[i] + wSize;
+    ps.b[P - 1] = pSize - wSize;
+    ps.e[P - 1] = pSize;
+    for (u32 i = 0; i < P; i++)
+        ps.emr[i] = useK ? lookUpKmer(ix, pat + ps.b[i]) : rangeOfSingleChar(ix, pat[ps.b[i]]);
+    u32 matched = P * (u32)wSize;
+    if (matched == 0) { // seedIfNoKmers, :255-271
+        u32 size = (pSize >= 4 * P) ? 4 : 1;
+        for (u32 i = 0; i + 1 < P; i++) {
+            ps.e[i] = tmin(ps.e[i] + size, pSize);
+            for (u32 j = ps.b[i]; j < ps.e[i]; j++) {
+                addChar(ix, DIR_FWD, false, pat[j], ps.emr[i], lc);
+                matched++;
+            }
+        }
+    }
+    int dir = DIR_FWD;
+    u32 partToExtend = 0;
+    for (u32 j = matched; j < pSize; j++) {
+        u64 maxW = 0;
+        for (u32 i = 0; i < P; i++) {
+            bool noL = (i == 0) || ps.b[i] == ps.e[i - 1];
+            bool noR = (i == P - 1) || ps.e[i] == ps.b[i + 1];
+            if (noL && noR)
+                continue;
+            u64 w = (u64)ps.emr[i].width() * st.weights[i];
+            if (w > maxW) {
+                maxW = w;
+                partToExtend = i;
+                if (noL)
+                    dir = DIR_FWD;
+                else if (noR)
+                    dir = DIR_BWD;
+                else
+                    dir = (ps.emr[i - 1].width() < ps.emr[i + 1].width()) ? DIR_BWD : DIR_FWD;
+            }
+        }
+        if (maxW == 0) { // extendParts, :283-297
+            for (u32 i = 0; i < P; i++) {
+                if ((i != P - 1) && (ps.e[i] != ps.b[i + 1]))
+                    ps.e[i] = ps.b[i + 1];
+                if ((i != 0) && (ps.b[i] != ps.e[i - 1]))
+                    ps.b[i] = ps.e[i - 1];
+            }
+            return;
+        }
+        u32 c;
+        if (dir == DIR_FWD) {
+            ps.e[partToExtend]++;
+            c = pat[ps.e[partToExtend] - 1];
+        } else {
+            ps.b[partToExtend]--;
+            c = pat[ps.b[partToExtend]];
+        }
+        addChar(ix, dir, partToExtend == P - 1, c, ps.emr[partToExtend], lc);
+    }
+}
+
+// stage 1 task.  Emits the immediate-switch candidates (order slot 0) and the
+// search tasks of the selected scheme.
+CLB_HD void partitionTask(const IndexView& ix, const DevStrategy& st, const Batch& B, u32 t, LocalCtr& lc) {
+    const u8* pat = seqCodes(B, t);
+    const u32 pSize = seqLen(B, t);
+    const u32 P = st.P;
+    PartInfo& pi = B.parts[t];
+    pi.len = (u16)pSize;
+    pi.valid = 0;
+    pi.scheme = 0;
+    if (P >= pSize || P == 1) { // searchstrategy.cpp:141-156: no partitioning possible
+        atomOr(B.err, ERR_SHORT_READ);
+        return;
+    }
+    PartScratch ps;
+    if (B.partStrategy == PART_DYNAMIC) {
+        partitionDynamic(ix, st, pat, pSize, P, ps, lc);
+    } else {
+        if (B.partStrategy == PART_UNIFORM) { // :194-209
+            for (u32 i = 0; i < P; i++) {
+                ps.b[i] = (u32)dmul(ddiv(dmul((double)(int)i, 1.0), (double)P), (double)pSize);
+                ps.e[i] = (u32)dmul(ddiv(dmul((double)(int)(i + 1), 1.0), (double)P), (double)pSize);
+            }
+            ps.e[P - 1] = pSize;
+        } else { // :212-238
+            ps.b[0] = 0;
+            ps.e[0] = (u32)dmul(st.begins[0], (double)(int)pSize);
+            for (u32 i = 0; i + 2 < P; i++) {
+                ps.b[i + 1] = (u32)dmul(st.begins[i], (double)(int)pSize);
+                ps.e[i + 1] = (u32)dmul(st.begins[i + 1], (double)(int)pSize);
+            }
+            ps.b[P - 1] = (u32)dmul(st.begins[P - 2], (double)(int)pSize);
+            ps.e[P - 1] = pSize;
+        }
+        calcExactRanges(ix, pat, P, ps, lc);
+    }
+    for (u32 i = 0; i < P; i++) {
+        pi.begin[i] = (u16)ps.b[i];
+        pi.end[i] = (u16)ps.e[i];
+        pi.emr[i] = ps.emr[i];
+    }
+    pi.valid = 1;
+    // A) immediate switch, searchstrategy.cpp:464-476 -> fmindex.cpp:245-265 /
+    //    :344-356
+    u32 emit = 0;
+    for (u32 i = 0; i < P; i++) {
+        u32 width = ps.emr[i].width();
+        if (width != 0 && width <= ix.switchPoint) {
+            Cand c;
+            c.t = t;
+            c.maxED = (u8)B.k;
+            c.minED = (u8)B.minD;
+            c.pad = 0;
+            c.add = 0;
+            if (B.metric == METRIC_EDIT) {
+                lc.c[IMMEDIATE_SWITCH]++;
+                u32 startDiff = (ps.b[i] == 0) ? 0 : ps.b[i] + B.k;
+                c.sub = startDiff;
+                c.fixedStart = (ps.b[i] == 0);
+            } else {
+                c.sub = ps.b[i];
+                c.fixedStart = 1;
+            }
+            u32 at = B.cands.reserve(width, B.err, ERR_CAND_OVERFLOW);
+            for (u32 row = 0; row < width; row++) {
+                c.row = ps.emr[i].sa.b + row;
+                c.order = emit++;
+                if (at != 0xFFFFFFFFu)
+                    B.cands.data[at + row] = c;
+            }
+        }
+    }
+    // B) scheme selection, searchstrategy.h:2505-2537
+    u32 sel = 0;
+    if (st.nSchemes > 1) {
+        u32 total = 0;
+        for (u32 i = 0; i < P; i++)
+            total += ps.emr[i].width();
+        if (total > P) {
+            u32 minValue = ps.emr[st.sc[0].criticalPart].width();
+            for (u32 i = 1; i < st.nSchemes; i++) {
+                u32 w = ps.emr[st.sc[i].criticalPart].width();
+                if (w < minValue) {
+                    minValue = w;
+                    sel = i;
+                }
+            }
+        }
+    }
+    pi.scheme = (u8)sel;
+    // which searches start (doRecSearch, searchstrategy.cpp:1181-1254)
+    const DevScheme& sc = st.sc[sel];
+    for (u32 s = 0; s < sc.nSearches; s++) {
+        const DevSearch& se = sc.s[s];
+        bool start = se.U[0] > 0 || ps.emr[se.order[0]].width() > ix.switchPoint;
+        if (start) {
+            SearchTask task;
+            task.t = t;
+            task.search = s;
+            B.tasks.push(task, B.err, ERR_TASK_OVERFLOW);
+        }
+    }
+}
+
+} // namespace clb

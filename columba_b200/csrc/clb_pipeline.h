@@ -1,0 +1,300 @@
+// columba_b200 -- host-side orchestration of one batch: buffer management and
+// the sequence of kernel launches.  Templated on the backend (BE) that owns
+// device memory and launches the task functors of clb_kernels.h.
+//
+// BE must provide:
+//   void* alloc(size_t), void free(void*), void zero(void*, size_t),
+//   void h2d(void* dst, const void* src, size_t), void d2h(void* dst, const void* src, size_t),
+//   void sync(), u32 workers(int kind) (number of workers for scratch slabs),
+//   template<class K> void launch(const K&, u32 nMax, const u32* nDev, int kind),
+//   void exclusiveScan(const u32* in, u32* out, u32 n)   (out[n] = total),
+//   void mark(int stage) (timing hook)
+#pragma once
+#include "clb_kernels.h"
+#include <string.h>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+namespace clb {
+
+struct BackendError : public std::runtime_error {
+    explicit BackendError(const std::string& m) : std::runtime_error(m) {}
+};
+
+enum { WK_LIGHT = 0, WK_SEARCH = 1, WK_VERIFY = 2, WK_FILTER = 3 };
+enum { STG_PREP, STG_PARTITION, STG_SEARCH, STG_VERIFY, STG_FM, STG_TEXT, N_STAGES };
+
+template <typename BE> struct DevBuf {
+    void* p = nullptr;
+    size_t bytes = 0;
+    void ensure(BE& be, size_t n) {
+        if (n <= bytes)
+            return;
+        if (p)
+            be.free(p);
+        size_t want = n + n / 4 + 256;
+        p = be.alloc(want);
+        bytes = want;
+    }
+    void release(BE& be) {
+        if (p)
+            be.free(p);
+        p = nullptr;
+        bytes = 0;
+    }
+};
+
+struct MapOptions {
+    u32 k = 0;
+    u32 minD = 0;
+    u32 metric = METRIC_EDIT;
+    u32 partStrategy = PART_DYNAMIC;
+    u32 noCigar = 0;
+};
+
+struct MapResult {
+    // host copies
+    std::vector<OutOcc> occ;
+    std::vector<u16> cig; // occ.size() x cigW
+    std::vector<u32> outStart, outCount; // per read
+    u32 cigW = 0;
+    u64 counters[N_COUNTERS];
+    u64 stats[N_STATS];
+    u32 err = 0;
+};
+
+template <typename BE> struct Pipeline {
+    BE& be;
+    IndexView ix;
+    DevBuf<BE> bReads, bOff, bCodes, bPlanes, bParts, bTasks, bCands, bFm, bTx, bTxCig, bOut, bOutCig, bPerRead, bIdx,
+        bMisc, bSlabSearch, bSlabVerify, bSlabFilter, bStrategy;
+    // list capacities (per read multipliers, grown after an overflow)
+    double candPerRead = 24, fmPerRead = 4, txPerRead = 24, outPerRead = 8;
+    u32 minCap = 1 << 16;
+    std::string lastError;
+
+    Pipeline(BE& b) : be(b) {}
+    ~Pipeline() {
+        DevBuf<BE>* all[] = {&bReads, &bOff, &bCodes, &bPlanes, &bParts, &bTasks, &bCands, &bFm, &bTx, &bTxCig, &bOut,
+                             &bOutCig, &bPerRead, &bIdx, &bMisc, &bSlabSearch, &bSlabVerify, &bSlabFilter, &bStrategy};
+        for (auto* d : all)
+            d->release(be);
+    }
+
+    // misc block layout: counters[N_COUNTERS] stats[N_STATS] (u64) then u32s
+    struct Misc {
+        u64 counters[N_COUNTERS];
+        u64 stats[N_STATS];
+        u32 err;
+        u32 nTasks, nCands, nFm, nTx, nOut;
+        u32 nT, nR; // 2R and R as device-side task counts
+    };
+
+    void uploadStrategy(const DevStrategy& st) {
+        bStrategy.ensure(be, sizeof(DevStrategy));
+        be.h2d(bStrategy.p, &st, sizeof(DevStrategy));
+    }
+
+    // reads: device pointers when readsOnDevice, else host pointers that are
+    // copied in.  Returns 0 or an error bit mask (after growing the lists the
+    // caller may simply call again).
+    u32 runOnce(const DevStrategy& st, const u8* reads, const u32* off, u32 R, u32 maxLen, size_t totalBytes,
+                bool readsOnDevice, const MapOptions& opt, MapResult* res, bool fetch) {
+        Batch B;
+        B.R = R;
+        B.maxLen = maxLen;
+        B.k = opt.k;
+        B.minD = opt.minD;
+        B.metric = opt.metric;
+        B.partStrategy = opt.partStrategy;
+        B.cigW = 2 * opt.k + 2;
+        B.noCigarFlag = opt.noCigar;
+        const u32 T = 2 * R;
+        if (readsOnDevice) {
+            B.readsAscii = reads;
+            B.readOff = off;
+        } else {
+            bReads.ensure(be, totalBytes + 16);
+            bOff.ensure(be, (size_t)(R + 1) * 4);
+            be.h2d(bReads.p, reads, totalBytes);
+            be.h2d(bOff.p, off, (size_t)(R + 1) * 4);
+            B.readsAscii = (const u8*)bReads.p;
+            B.readOff = (const u32*)bOff.p;
+        }
+        B.seqStride = (maxLen + 15) & ~15u;
+        B.nw = (maxLen + 63) / 64 + 1;
+        bCodes.ensure(be, (size_t)T * B.seqStride);
+        bPlanes.ensure(be, (size_t)T * 2 * 4 * B.nw * 8);
+        bParts.ensure(be, (size_t)T * sizeof(PartInfo));
+        B.codes = (u8*)bCodes.p;
+        B.planes = (u64*)bPlanes.p;
+        B.parts = (PartInfo*)bParts.p;
+        const u32 P = st.P;
+        u32 maxSearches = 0;
+        for (u32 i = 0; i < st.nSchemes; i++)
+            maxSearches = tmax<u32>(maxSearches, st.sc[i].nSearches);
+        auto capOf = [&](double perRead) {
+            double c = perRead * R;
+            if (c < minCap)
+                c = minCap;
+            if (c > 4.0e9)
+                c = 4.0e9;
+            return (u32)c;
+        };
+        const u32 capTasks = T * maxSearches + 16;
+        const u32 capCands = capOf(candPerRead), capFm = capOf(fmPerRead), capTx = capOf(txPerRead),
+                  capOut = capOf(outPerRead);
+        bTasks.ensure(be, (size_t)capTasks * sizeof(SearchTask));
+        bCands.ensure(be, (size_t)capCands * sizeof(Cand));
+        bFm.ensure(be, (size_t)capFm * sizeof(FMOccRec));
+        bTx.ensure(be, (size_t)capTx * sizeof(TextOccRec));
+        bTxCig.ensure(be, (size_t)capTx * B.cigW * 2);
+        bOut.ensure(be, (size_t)capOut * sizeof(OutOcc));
+        bOutCig.ensure(be, (size_t)capOut * B.cigW * 2);
+        bMisc.ensure(be, sizeof(Misc));
+        be.zero(bMisc.p, sizeof(Misc));
+        Misc* M = (Misc*)bMisc.p;
+        Misc hm;
+        memset(&hm, 0, sizeof(hm));
+        hm.nT = T;
+        hm.nR = R;
+        be.h2d(bMisc.p, &hm, sizeof(hm));
+        B.tasks.data = (SearchTask*)bTasks.p; B.tasks.count = &M->nTasks; B.tasks.cap = capTasks;
+        B.cands.data = (Cand*)bCands.p; B.cands.count = &M->nCands; B.cands.cap = capCands;
+        B.fmOccs.data = (FMOccRec*)bFm.p; B.fmOccs.count = &M->nFm; B.fmOccs.cap = capFm;
+        B.textOccs.data = (TextOccRec*)bTx.p; B.textOccs.count = &M->nTx; B.textOccs.cap = capTx;
+        B.textCig = (u16*)bTxCig.p;
+        B.out.data = (OutOcc*)bOut.p; B.out.count = &M->nOut; B.out.cap = capOut;
+        B.outCig = (u16*)bOutCig.p;
+        B.counters = M->counters;
+        B.stats = M->stats;
+        B.err = &M->err;
+        // per-read arrays: 9 x (R+1)
+        const size_t pr = (size_t)(R + 1);
+        bPerRead.ensure(be, pr * 9 * 4);
+        be.zero(bPerRead.p, pr * 9 * 4);
+        u32* q = (u32*)bPerRead.p;
+        B.fmCount = q; B.fmStart = q + pr; B.fmFill = q + 2 * pr; B.fmUnique = q + 3 * pr;
+        B.txCount = q + 4 * pr; B.txStart = q + 5 * pr; B.txFill = q + 6 * pr;
+        B.outCount = q + 7 * pr; B.outStart = q + 8 * pr;
+        bIdx.ensure(be, ((size_t)capFm + 2 * (size_t)capTx) * 4);
+        B.fmIdx = (u32*)bIdx.p;
+        B.txIdx = B.fmIdx + capFm;
+        B.txTmp = B.txIdx + capTx;
+        const DevStrategy* dst = (const DevStrategy*)bStrategy.p;
+
+        // ---- stage 0/1
+        {
+            PrepKernel k0{B};
+            be.launch(k0, T, nullptr, WK_LIGHT);
+            be.mark(STG_PREP);
+            PartitionKernel k1{ix, dst, B};
+            be.launch(k1, T, nullptr, WK_LIGHT);
+            be.mark(STG_PARTITION);
+        }
+        // ---- stage 2
+        {
+            const bool wide = opt.k > BPC<u64>::MAX_ED;
+            const u32 rowsCap = maxLen + P * (2 * opt.k + (wide ? 70 : 40)) + 8;
+            const u32 stackCap = 3 * rowsCap + 8;
+            const u32 nw = be.workers(WK_SEARCH);
+            if (wide) {
+                size_t sb = searchScratchBytes<u128>(stackCap, rowsCap, P);
+                bSlabSearch.ensure(be, sb * nw);
+                SearchKernel<u128> k2{ix, dst, B, (u8*)bSlabSearch.p, sb, stackCap, rowsCap, P};
+                be.launch(k2, capTasks, &M->nTasks, WK_SEARCH);
+            } else {
+                size_t sb = searchScratchBytes<u64>(stackCap, rowsCap, P);
+                bSlabSearch.ensure(be, sb * nw);
+                SearchKernel<u64> k2{ix, dst, B, (u8*)bSlabSearch.p, sb, stackCap, rowsCap, P};
+                be.launch(k2, capTasks, &M->nTasks, WK_SEARCH);
+            }
+            be.mark(STG_SEARCH);
+        }
+        // ---- stage 3
+        const u32 vRows = maxLen + 3 * opt.k + 8;
+        {
+            const bool wide = !use64(2 * opt.k + 1, opt.k);
+            size_t sb = (((size_t)B.cigW * 2 * 2 + 63) & ~(size_t)63) +
+                        (size_t)vRows * (wide ? sizeof(Row<u128>) : sizeof(Row<u64>));
+            sb = (sb + 63) & ~(size_t)63;
+            const u32 nw = be.workers(WK_VERIFY);
+            bSlabVerify.ensure(be, sb * nw);
+            VerifyKernel k3{ix, B, (u8*)bSlabVerify.p, sb, vRows};
+            be.launch(k3, capCands, &M->nCands, WK_VERIFY);
+            be.mark(STG_VERIFY);
+        }
+        // ---- stages 4-6
+        {
+            size_t sb = (((size_t)B.cigW * 2 * 2 + 63) & ~(size_t)63) + (size_t)vRows * sizeof(Row<u128>);
+            sb = (sb + 63) & ~(size_t)63;
+            const u32 nw = be.workers(WK_FILTER);
+            bSlabFilter.ensure(be, sb * nw);
+            FmCountKernel c1{B};
+            be.launch(c1, capFm, &M->nFm, WK_LIGHT);
+            be.exclusiveScan(B.fmCount, B.fmStart, R);
+            FmScatterKernel c2{B};
+            be.launch(c2, capFm, &M->nFm, WK_LIGHT);
+            FmPerReadKernel c3{ix, B, (u8*)bSlabFilter.p, sb, vRows};
+            be.launch(c3, R, nullptr, WK_FILTER);
+            be.mark(STG_FM);
+            TxCountKernel d1{B};
+            be.launch(d1, capTx, &M->nTx, WK_LIGHT);
+            be.exclusiveScan(B.txCount, B.txStart, R);
+            TxScatterKernel d2{B};
+            be.launch(d2, capTx, &M->nTx, WK_LIGHT);
+            TxPerReadKernel d3{ix, B, (u8*)bSlabFilter.p, sb, vRows};
+            be.launch(d3, R, nullptr, WK_FILTER);
+            be.mark(STG_TEXT);
+        }
+        // ---- results
+        be.d2h(&hm, bMisc.p, sizeof(hm));
+        u32 err = hm.err;
+        if (err & ERR_CAND_OVERFLOW)
+            candPerRead = tmax(candPerRead * 2, (double)hm.nCands / R * 1.25);
+        if (err & ERR_FMOCC_OVERFLOW)
+            fmPerRead = tmax(fmPerRead * 2, (double)hm.nFm / R * 1.25);
+        if (err & ERR_TEXTOCC_OVERFLOW)
+            txPerRead = tmax(txPerRead * 2, (double)hm.nTx / R * 1.25 + 1);
+        if (err & ERR_OUT_OVERFLOW)
+            outPerRead = tmax(outPerRead * 2, (double)hm.nOut / R * 1.25);
+        if (minCap < (1u << 22) && (err & (ERR_CAND_OVERFLOW | ERR_FMOCC_OVERFLOW | ERR_TEXTOCC_OVERFLOW | ERR_OUT_OVERFLOW)))
+            minCap *= 4;
+        if (res) {
+            res->err = err;
+            memcpy(res->counters, hm.counters, sizeof(hm.counters));
+            memcpy(res->stats, hm.stats, sizeof(hm.stats));
+            res->cigW = B.cigW;
+            if (fetch && !(err & ~(u32)ERR_SHORT_READ)) {
+                u32 n = hm.nOut;
+                res->occ.resize(n);
+                res->cig.resize((size_t)n * B.cigW);
+                res->outStart.resize(R);
+                res->outCount.resize(R);
+                if (n) {
+                    be.d2h(res->occ.data(), bOut.p, (size_t)n * sizeof(OutOcc));
+                    be.d2h(res->cig.data(), bOutCig.p, (size_t)n * B.cigW * 2);
+                }
+                be.d2h(res->outStart.data(), B.outStart, (size_t)R * 4);
+                be.d2h(res->outCount.data(), B.outCount, (size_t)R * 4);
+            }
+        }
+        return err;
+    }
+
+    // run with automatic re-run after list overflows
+    u32 run(const DevStrategy& st, const u8* reads, const u32* off, u32 R, u32 maxLen, size_t totalBytes,
+            bool readsOnDevice, const MapOptions& opt, MapResult* res, bool fetch) {
+        const u32 retry = ERR_CAND_OVERFLOW | ERR_FMOCC_OVERFLOW | ERR_TEXTOCC_OVERFLOW | ERR_OUT_OVERFLOW;
+        u32 err = 0;
+        for (int attempt = 0; attempt < 8; attempt++) {
+            err = runOnce(st, reads, off, R, maxLen, totalBytes, readsOnDevice, opt, res, fetch);
+            if (!(err & retry))
+                break;
+        }
+        return err;
+    }
+};
+
+} // namespace clb

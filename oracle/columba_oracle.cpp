@@ -97,6 +97,7 @@ void orc_extend(void* h, int mode, const uint32_t* parent4, uint32_t* out16) {
 }
 uint32_t orc_find_sa(void* h, uint32_t row) { return ((OracleCtx*)h)->ix.findSA(row); }
 uint32_t orc_text_length(void* h) { return ((OracleCtx*)h)->ix.textLength; }
+const char* orc_seq_name(void* h, uint32_t i) { return ((OracleCtx*)h)->ix.seqNames[i].c_str(); }
 
 // Map one read (ALL mode).  Output records are appended to a malloc'ed text
 // buffer "strand\tseqID\tpos1\tdist\tcigar\tindexBegin\n"; counters[17] are

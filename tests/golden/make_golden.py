@@ -76,8 +76,8 @@ CASES = {
     "edit_k4_columba": ("edit", ["-e", "4"], dict(k=4)),
     "edit_k6_columba": ("edit", ["-e", "6"], dict(k=6)),
     "edit_k4_kuch1": ("edit", ["-e", "4", "-S", "kuch1"], dict(k=4, scheme=("named", "kuch1"))),
-    "edit_k3_kuch2": ("edit", ["-e", "3", "-S", "kuch2"], dict(k=3, scheme=("named", "kuch2"))),
-    "edit_k2_01star0": ("edit", ["-e", "2", "-S", "01*0"], dict(k=2, scheme=("named", "01*0"))),
+    "edit_k3_kuch2": ("edit", ["-e", "3", "-S", "kuch2"], dict(k=3, scheme=("named", "kuch2"), kmer=4)),  # -K is capped at 4 for kuch2/01*0 (alignparameters.cpp:1272-1279)
+    "edit_k2_01star0": ("edit", ["-e", "2", "-S", "01*0"], dict(k=2, scheme=("named", "01*0"), kmer=4)),
     "edit_k4_minU": ("edit", ["-e", "4", "-S", "minU"], dict(k=4, scheme=("named", "minU"))),
     "edit_k4_pigeon_custom": ("edit", ["-e", "4", "-c", "@pigeon5", "-nD"], dict(k=4, scheme=("custom", "pigeon5"))),
     "edit_k3_pigeon_custom_dyn": ("edit", ["-e", "3", "-c", "@pigeon5"], dict(k=3, scheme=("custom_dynamic", "pigeon5"))),
