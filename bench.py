@@ -1,0 +1,362 @@
+#!/usr/bin/env python
+"""Benchmark of the approximate-matching hot path (see BASELINE.json).
+
+  python bench.py --gpus N --steps K --warmup W [--impl reference]
+
+Workload (config.workload): BASELINE.json configs[1] -- synthetic 4.6 Mbp
+E. coli-sized reference with injected repeats, 1 M single-end 150 bp reads,
+edit distance k=4, ALL mode, default (dynamic selection) scheme, dynamic
+partitioning.  The 3.1 Gbp configs cannot be indexed inside a benchmark run
+(index construction is host work outside the hot path: ~1 h per suffix array).
+One step = one pass of the whole path over one batch of 1 M reads; with N GPUs
+every rank maps its own 1 M reads (weak scaling, index replicated, no
+data-path collective).
+
+The ours-arm prints `value` (reads resident in HBM, occurrences left in HBM),
+`e2e` (host buffers through clb_map_batch: H2D of the reads and D2H of the
+occurrences inside the timed region), a roofline object for the dominant
+kernel and a cpu_baseline object (the reference's own multithreaded CPU build
+on a bounded sample, rank 0, N=1 only).
+"""
+import argparse
+import json
+import os
+import re
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tools"))
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+REF_BIN = os.path.join(ROOT, "oracle", "_ref", "columba")
+METRIC_NAME = "reads/sec (150bp, k=4 edit, ALL)"
+
+
+def env_int(name, default):
+    try:
+        return int(os.environ.get(name, default))
+    except ValueError:
+        return default
+
+
+# --------------------------------------------------------------------------- data
+def data_dir(args):
+    d = os.path.join(tempfile.gettempdir(), "clb_bench_%d_%d" % (args.ref_bp, args.ref_seed))
+    os.makedirs(d, exist_ok=True)
+    return d
+
+
+def make_reference(args):
+    """FASTA + index files (reference formats, written by the product's
+    host-side index writer).  Returns (base, seqs)."""
+    import gen_data
+    import columba_b200 as cb
+    d = data_dir(args)
+    base = os.path.join(d, "ref")
+    names, seqs = gen_data.gen_reference(args.ref_bp, args.ref_seed, 1, "ecoli")
+    if not os.path.exists(base + ".meta"):
+        fa = base + ".fa"
+        gen_data.write_fasta(fa, names, seqs)
+        cb.build_index(fa, base, 4)
+    return base, seqs
+
+
+def make_reads(args, seqs, rank):
+    import gen_data
+    return gen_data.gen_reads_fast(seqs, args.reads, 150, args.read_seed + rank, "edit", args.k, over_e=args.k + 2)
+
+
+# --------------------------------------------------------------------------- clocks
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu):
+        self.gpu = gpu
+        self.proc = None
+        self.path = None
+
+    def start(self):
+        try:
+            f = tempfile.NamedTemporaryFile(prefix="clocks_", suffix=".csv", delete=False)
+            self.path = f.name
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=f,
+                                         stderr=subprocess.DEVNULL)
+        except OSError:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if not self.proc:
+            return out
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in open(self.path):
+            a = [x.strip() for x in line.split(",")]
+            if len(a) < 9:
+                continue
+            try:
+                sm.append(float(a[1]))
+                mx.append(float(a[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, a[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        os.unlink(self.path)
+        if sm:
+            out.update(sm_mhz=float(np.median(sm)), sm_max_mhz=float(max(mx)), reasons=sorted(reasons),
+                       samples=len(sm))
+        return out
+
+
+# --------------------------------------------------------------------------- reference arm
+def run_reference_cpu(base, reads, k, threads, out_dir):
+    """The reference's own CPU implementation (oracle/_ref/columba, compiled from
+    the unmodified sources) on `reads`; returns (reads/s, seconds, kind)."""
+    import gen_data
+    n = len(reads)
+    if os.path.exists(REF_BIN):
+        fq = os.path.join(out_dir, "sample_%d.fq" % n)
+        if not os.path.exists(fq):
+            gen_data.write_fastq_matrix(fq, reads)
+        shm = "/dev/shm" if os.path.isdir("/dev/shm") else out_dir
+        sam = os.path.join(shm, "clb_ref_out_%d.sam" % os.getpid())
+        cmd = [REF_BIN, "-r", base, "-f", fq, "-a", "all", "-e", str(k), "-t", str(threads), "-o", sam]
+        p = subprocess.run(cmd, capture_output=True, text=True)
+        if os.path.exists(sam):
+            os.unlink(sam)
+        if p.returncode != 0:
+            raise RuntimeError("reference failed: " + p.stdout[-500:] + p.stderr[-500:])
+        m = re.search(r"(\d+) mapping threads finished mapping in ([0-9.]+)s", p.stdout)
+        secs = float(m.group(2))
+        return n / secs, secs, "reference"
+    # the reference binary did not travel: time the oracle port (1 thread)
+    import oracle_util as ou
+    orc = ou.Oracle(base)
+    t0 = time.perf_counter()
+    for i in range(n):
+        orc.map_read(reads[i].tobytes().decode(), k)
+    secs = time.perf_counter() - t0
+    return n / secs, secs, "port"
+
+
+def cpu_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+# --------------------------------------------------------------------------- main
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--reads", type=int, default=1_000_000, help="reads per step per GPU")
+    ap.add_argument("--ref-bp", type=int, default=4_600_000)
+    ap.add_argument("--ref-seed", type=int, default=4600)
+    ap.add_argument("--read-seed", type=int, default=150)
+    ap.add_argument("--k", type=int, default=4)
+    ap.add_argument("--cpu-sample", type=int, default=200_000, help="reads of the cpu_baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+
+    rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
+    config = {"workload": "configs[1]: synthetic %.1f Mbp E. coli-sized reference with injected repeats, %d SE 150 bp "
+                          "reads per step per GPU, edit distance k=%d, ALL mode, default scheme, dynamic partitioning"
+                          % (args.ref_bp / 1e6, args.reads, args.k),
+              "reads_per_step_per_gpu": args.reads, "read_len": 150, "k": args.k, "mode": "ALL",
+              "scheme": "columba (dynamic selection)", "partitioning": "dynamic", "in_text_switch": 4,
+              "sa_sparseness": 4, "kmer": 10, "parallelism": "reads sharded over %d GPU(s), index replicated" % world}
+
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        base, seqs = make_reference(args)
+        import gen_data
+        n = min(args.cpu_sample, args.reads)
+        reads = gen_data.gen_reads_fast(seqs, args.reads, 150, args.read_seed, "edit", args.k, over_e=args.k + 2)[:n]
+        threads = cpu_threads()
+        for _ in range(args.warmup):
+            run_reference_cpu(base, reads, args.k, threads, data_dir(args))
+        secs, kind = [], "reference"
+        for _ in range(args.steps):
+            _, s, kind = run_reference_cpu(base, reads, args.k, threads, data_dir(args))
+            secs.append(s)
+        ms = 1e3 * float(np.mean(secs))
+        val = n / (ms / 1e3)
+        sample = "first %d reads of the step's batch, all %d host threads, mapping time from the reference's own log" \
+                 % (n, threads)
+        line = {"impl": "reference", "metric": METRIC_NAME, "value": val, "unit": "reads/s", "n_gpus": args.gpus,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic", "config": config,
+                "cpu_baseline": {"value": val, "unit": "reads/s", "cores": threads if kind == "reference" else 1,
+                                 "kind": kind, "sample": sample},
+                "e2e": {"value": val, "unit": "reads/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        print(json.dumps(line))
+        return
+
+    import torch
+    import torch.distributed as dist
+    import columba_b200 as cb
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (the product has no CPU fallback)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- data: rank 0 writes the index files, everybody loads them
+    if rank == 0:
+        base, seqs = make_reference(args)
+    barrier()
+    if rank != 0:
+        base, seqs = make_reference(args)
+    reads = make_reads(args, seqs, rank)
+    n, L = reads.shape
+    off = (np.arange(n + 1, dtype=np.int64) * L).astype(np.uint32)
+
+    ix = cb.Index(base, 4, 10, 4, device=local)
+    m = cb.Mapper(ix)
+    stream = torch.cuda.current_stream()
+    m.set_stream(stream.cuda_stream)
+    h_reads = torch.from_numpy(reads.reshape(-1)).pin_memory()
+    h_off = torch.from_numpy(off.view(np.int32)).pin_memory()
+    d_reads = h_reads.cuda(non_blocking=True)
+    d_off = h_off.cuda(non_blocking=True)
+    torch.cuda.synchronize()
+
+    def step_device():
+        return m.map_batch_device(d_reads.data_ptr(), d_off.data_ptr(), n, L, args.k, 0, fetch=False)
+
+    def step_host():
+        r = cb.api.ClbResult()
+        rc = m.lib.clb_map_batch(m.h, h_reads.data_ptr(), h_off.data_ptr(), n, args.k, 0, cb.api.C.byref(r))
+        if rc:
+            raise cb.ClbError(rc, m.lib.clb_last_error(m.h).decode())
+        return r
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        barrier()
+        clk = ClockSampler(local)
+        clk.start()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        e0.record(stream)
+        results = [fn() for _ in range(steps)]
+        e1.record(stream)
+        torch.cuda.synchronize()
+        wall = (time.perf_counter() - t0) * 1e3
+        clocks = clk.stop()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device="cuda", dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item()), wall, results, clocks
+
+    # ---- value: inputs resident in HBM
+    ms, wall, results, clocks = timed(step_device, args.steps, args.warmup)
+    ms_per_step = ms / args.steps
+    value = world * n * args.steps / (ms / 1e3)
+    launches = int(sum(r.gpu_launches for r in results))
+    stage = {s: float(np.mean([r.stage_ms[s] for r in results])) for s in cb.STAGE_NAMES}
+    stats = {s: float(np.mean([r.stats[s] for r in results])) for s in cb.STAT_NAMES}
+    counters = {s: int(results[-1].counters[s]) for s in cb.COUNTER_NAMES}
+
+    # ---- e2e: host buffers through the C ABI, copies inside the timed region
+    ms2, wall2, results2, clocks2 = timed(step_host, args.steps, 2)
+    r_last = results2[-1]
+    h2d = int(h_reads.numel() + h_off.numel() * 4)
+    d2h = int(r_last.n_occ * (24 + 2 * r_last.cigar_stride) + 8 * n)
+    e2e_val = world * n * args.steps / (ms2 / 1e3)
+
+    # ---- roofline of the dominant kernel (CUDA events around that stage's launches)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except (OSError, ValueError):
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
+    dom = max(stage, key=lambda s: stage[s])
+    part_lookups = stats["RANK_LOOKUPS"] - stats["SEARCH_LOOKUPS"]
+    # algorithmic bytes per launch: 32 B per rank lookup; locate = 32 B BWT record +
+    # 16 B marker record per LF step + 16 B marker + 4 B sample per row; verification reads 2-bit text
+    # (1 B per 4 rows) and the read's bit planes (96 B); the filter reads/writes its 24 B records + CIGARs
+    alg = {
+        "prep": n * 2 * (L + L + 2 * 4 * 4 * 8),
+        "partition": part_lookups * 32 + n * 2 * (L + 560),
+        "search": stats["SEARCH_LOOKUPS"] * 32 + stats["SEARCH_ROWS"] * 40,
+        "verify": stats["CANDIDATES"] * (24 + 20 + 96) + stats["LF_STEPS"] * 48 + stats["VERIFY_ROWS"] / 4.0
+        + stats["TEXT_OCCS"] * 44,
+        "fm_expand": stats["FM_OCCS"] * 24 * 3,
+        "text_filter": stats["TEXT_OCCS"] * (24 + 8) * 2 + counters["TOTAL_UNIQUE_MATCHES"] * 44,
+    }
+    achieved = alg[dom] / (stage[dom] / 1e3) / 1e9 if stage[dom] > 0 else 0.0
+    roofline = {"kernel": dom, "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                "kernel_ms": stage[dom], "algorithmic_bytes": alg[dom],
+                "rank_lookups_per_s": stats["RANK_LOOKUPS"] / (ms_per_step / 1e3),
+                "rank_roofline_frac_of_8TBs": stats["RANK_LOOKUPS"] * 32 / (ms_per_step / 1e3) / 8e12}
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    line = {"metric": METRIC_NAME, "value": value, "unit": "reads/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u64", "data": "synthetic", "config": config,
+            "e2e": {"value": e2e_val, "unit": "reads/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": ms2 / args.steps},
+            "gpu_launches": launches, "clocks": clocks, "clocks_e2e": clocks2, "roofline": roofline,
+            "stage_ms": stage, "stats_per_step": stats, "counters": counters,
+            "wall_ms_per_step": wall / args.steps, "index_device_bytes": ix.device_bytes}
+    config["l2"] = "inputs per step (%.0f MB of reads) exceed the 126 MB L2; the %.1f MB index is L2-resident by " \
+                   "the nature of this 4.6 Mbp configuration" % (h2d / 1e6, ix.device_bytes / 1e6)
+    if world == 1 and not args.no_cpu_baseline:
+        ns = min(args.cpu_sample, n)
+        threads = cpu_threads()
+        try:
+            run_reference_cpu(base, reads[:ns], args.k, threads, data_dir(args))  # warms the page cache
+            v, secs, kind = run_reference_cpu(base, reads[:ns], args.k, threads, data_dir(args))
+            line["cpu_baseline"] = {"value": v, "unit": "reads/s", "cores": threads if kind == "reference" else 1,
+                                    "kind": kind, "seconds": secs,
+                                    "sample": "first %d reads of the batch, %s" % (
+                                        ns, "unmodified reference binary (oracle/_ref/columba -t %d), mapping time from "
+                                            "its own log" % threads if kind == "reference" else "oracle port, 1 thread")}
+        except Exception as e:  # the baseline is informative; never lose the GPU numbers over it
+            line["cpu_baseline"] = {"value": None, "unit": "reads/s", "cores": 0, "kind": "reference",
+                                    "sample": "failed: %s" % str(e)[:200]}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -15,14 +15,14 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 DEFAULT_LIB = os.path.join(HERE, "libcolumba_b200.so")
 SCHEMES_DIR = os.path.join(HERE, "schemes")
 
-N_COUNTERS, N_STATS, N_STAGES = 17, 8, 6
+N_COUNTERS, N_STATS, N_STAGES = 17, 9, 6
 COUNTER_NAMES = ["NODE_COUNTER", "TOTAL_REPORTED_POSITIONS", "CIGARS_IN_INDEX", "IN_TEXT_STARTED",
                  "ABORTED_IN_TEXT_VERIF", "CIGARS_IN_TEXT_VERIFICATION", "IMMEDIATE_SWITCH", "SEARCH_STARTED",
                  "DROPPED_UNIQUE_MATCHES", "NUMBER_OF_READS", "TOTAL_UNIQUE_MATCHES", "MAPPED_READS",
                  "TOTAL_UNIQUE_PAIRS", "MAPPED_PAIRS", "DISCORDANTLY_MAPPED_PAIRS", "MAPPED_HALF_PAIRS",
                  "UNPAIRED_BUT_MAPPED_PAIRS"]
 STAT_NAMES = ["RANK_LOOKUPS", "LF_STEPS", "VERIFY_ROWS", "SEARCH_ROWS", "SEARCH_TASKS", "CANDIDATES", "FM_OCCS",
-              "TEXT_OCCS"]
+              "TEXT_OCCS", "SEARCH_LOOKUPS"]
 STAGE_NAMES = ["prep", "partition", "search", "verify", "fm_expand", "text_filter"]
 METRIC = {"hamming": 0, "edit": 1}
 PARTITION = {"uniform": 0, "static": 1, "dynamic": 2}
@@ -47,7 +47,7 @@ class ClbError(RuntimeError):
 EXPORTS = ["clb_abi_version", "clb_device_count", "clb_index_load", "clb_index_free", "clb_index_text_length",
            "clb_index_num_seqs", "clb_index_seq_name", "clb_index_seq_start", "clb_index_device_bytes",
            "clb_ctx_create", "clb_ctx_free", "clb_last_error", "clb_ctx_set_strategy", "clb_ctx_set_options",
-           "clb_ctx_supports_distance", "clb_ctx_num_parts", "clb_map_batch", "clb_map_batch_device", "clb_occ4",
+           "clb_ctx_set_stream", "clb_ctx_supports_distance", "clb_ctx_num_parts", "clb_map_batch", "clb_map_batch_device", "clb_occ4",
            "clb_extend", "clb_find_sa", "clb_kmer_lookup", "clb_build_index"]
 
 _libs = {}
@@ -81,6 +81,7 @@ def load_library(path=None):
     lib.clb_last_error.restype = C.c_char_p
     lib.clb_ctx_set_strategy.argtypes = [vp, C.c_char_p, C.c_char_p, C.c_char_p]
     lib.clb_ctx_set_options.argtypes = [vp, C.c_int, C.c_int]
+    lib.clb_ctx_set_stream.argtypes = [vp, vp]
     lib.clb_ctx_supports_distance.argtypes = [vp, C.c_int]
     lib.clb_ctx_num_parts.argtypes = [vp, C.c_int]
     lib.clb_map_batch.argtypes = [vp, vp, vp, C.c_uint32, C.c_int, C.c_int, C.POINTER(ClbResult)]
@@ -199,6 +200,10 @@ class Mapper:
         if self.h:
             self.lib.clb_ctx_free(self.h)
             self.h = None
+
+    def set_stream(self, cuda_stream):
+        """cuda_stream: integer cudaStream_t handle (0/None: the context's own stream)."""
+        self._check(self.lib.clb_ctx_set_stream(self.h, C.c_void_p(cuda_stream or None)))
 
     def supports(self, k):
         return bool(self.lib.clb_ctx_supports_distance(self.h, k))

@@ -86,7 +86,8 @@ __global__ void __launch_bounds__(1024) clb_scan_kernel(const u32* __restrict__ 
 struct CudaBackend {
     int device;
     int numSMs = 0;
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr;    // stream in use
+    cudaStream_t ownStream = nullptr; // created by this backend
     u32* workCtrs = nullptr; // pool of work counters, one per dynamic launch
     u32 nextCtr = 0;
     static const u32 N_CTRS = 64;
@@ -112,7 +113,8 @@ struct CudaBackend {
             throw BackendError("invalid CUDA device ordinal " + std::to_string(dev));
         CLB_CUDA(cudaSetDevice(dev));
         CLB_CUDA(cudaDeviceGetAttribute(&numSMs, cudaDevAttrMultiProcessorCount, dev));
-        CLB_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+        CLB_CUDA(cudaStreamCreateWithFlags(&ownStream, cudaStreamNonBlocking));
+        stream = ownStream;
         CLB_CUDA(cudaMalloc(&workCtrs, N_CTRS * sizeof(u32)));
         CLB_CUDA(cudaEventCreate(&evBegin));
         CLB_CUDA(cudaEventCreate(&evEnd));
@@ -132,8 +134,13 @@ struct CudaBackend {
         for (auto& ev : evStage)
             if (ev)
                 cudaEventDestroy(ev);
-        if (stream)
-            cudaStreamDestroy(stream);
+        if (ownStream)
+            cudaStreamDestroy(ownStream);
+    }
+    void setStream(void* s) {
+        CLB_CUDA(cudaSetDevice(device));
+        CLB_CUDA(cudaStreamSynchronize(stream));
+        stream = s ? (cudaStream_t)s : ownStream;
     }
     void* alloc(size_t n) {
         void* p = nullptr;

@@ -141,6 +141,17 @@ int clb_ctx_set_options(clb_ctx* c, int metric, int partitioning) {
     c->opt.partStrategy = (clb::u32)partitioning;
     return CLB_OK;
 }
+int clb_ctx_set_stream(clb_ctx* c, void* cuda_stream) {
+    if (!c)
+        return CLB_E_INVALID;
+    try {
+        c->be->setStream(cuda_stream);
+    } catch (std::exception& e) {
+        c->err = e.what();
+        return CLB_E_CUDA;
+    }
+    return CLB_OK;
+}
 int clb_ctx_supports_distance(const clb_ctx* c, int k) {
     return c && c->haveStrategy && k >= 1 && k <= clb::CLB_MAX_K && c->flat[k].supported;
 }

@@ -131,6 +131,7 @@ enum Stat {
     ST_CANDIDATES,    // in-text verification candidates
     ST_FM_OCCS,       // index occurrences reported by the searches
     ST_TEXT_OCCS,     // text occurrences before the per-read filter
+    ST_SEARCH_LOOKUPS, // the part of ST_RANK_LOOKUPS done by the search kernel (rest: partitioning)
     N_STATS
 };
 

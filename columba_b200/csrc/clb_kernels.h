@@ -55,10 +55,12 @@ template <typename W> struct SearchKernel {
         const DevSearch& se = st->sc[pi.scheme].s[task.search];
         SearchCtx<W> X(ix, B, se, pi, s.sc, s.lc, task.t, task.search);
         s.lc.s[ST_SEARCH_TASKS]++;
+        const u64 before = s.lc.s[ST_RANK_LOOKUPS];
         if (B.metric == METRIC_EDIT)
             editSearchTask<W>(X);
         else
             hammingSearchTask<W>(X);
+        s.lc.s[ST_SEARCH_LOOKUPS] += s.lc.s[ST_RANK_LOOKUPS] - before;
         if (X.err)
             atomOr(B.err, X.err);
     }

@@ -51,7 +51,7 @@ enum {
 /* device statistics next to the reference's counters */
 enum {
     CLB_STAT_RANK_LOOKUPS, CLB_STAT_LF_STEPS, CLB_STAT_VERIFY_ROWS, CLB_STAT_SEARCH_ROWS, CLB_STAT_SEARCH_TASKS,
-    CLB_STAT_CANDIDATES, CLB_STAT_FM_OCCS, CLB_STAT_TEXT_OCCS, CLB_N_STATS
+    CLB_STAT_CANDIDATES, CLB_STAT_FM_OCCS, CLB_STAT_TEXT_OCCS, CLB_STAT_SEARCH_LOOKUPS, CLB_N_STATS
 };
 enum { CLB_N_STAGES = 6 }; /* prep, partition, search, verify, fm-expand, text-filter */
 
@@ -119,6 +119,10 @@ const char* clb_last_error(const clb_ctx*); /* ctx may be NULL: last error of in
  * data_dir: directory holding the built-in tables (columba_b200/schemes). */
 int clb_ctx_set_strategy(clb_ctx*, const char* kind, const char* arg, const char* data_dir);
 int clb_ctx_set_options(clb_ctx*, int metric, int partitioning);
+/* Run this context's copies and kernels on the caller's CUDA stream
+ * (cudaStream_t, e.g. torch.cuda.current_stream().cuda_stream) instead of the
+ * context's own stream; NULL restores the own stream. */
+int clb_ctx_set_stream(clb_ctx*, void* cuda_stream);
 int clb_ctx_supports_distance(const clb_ctx*, int k);
 int clb_ctx_num_parts(const clb_ctx*, int k); /* calculateNumParts */
 

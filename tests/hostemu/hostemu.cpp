@@ -45,6 +45,7 @@ struct HostEmuBackend {
         out[n] = run;
     }
     void mark(int) {}
+    void setStream(void*) {}
     void beginBatch() { launches = 0; }
     void endBatch() {}
     void fillTimings(float* stage, float* total, uint32_t* nl) {

@@ -169,6 +169,73 @@ def gen_reads(seqs, n_reads, read_len, seed, metric="edit", max_e=4,
     return out
 
 
+def gen_reads_fast(seqs, n_reads, read_len, seed, metric="edit", max_e=4, frac_over=0.05, frac_exact=0.05,
+                   over_e=6):
+    """Vectorised read generator for the benchmark-sized sets (same error model
+    as gen_reads: edits ~ U{0..max_e} for 90 %, over_e for 5 %, exact for 5 %;
+    each edit substitution .70 / insertion .15 / deletion .15; strands 50/50).
+    Returns a uint8 matrix n_reads x read_len (ASCII)."""
+    rng = np.random.default_rng(seed)
+    lens = np.array([len(s) for s in seqs], dtype=np.int64)
+    starts = np.concatenate([[0], np.cumsum(lens)])
+    cat = np.concatenate(seqs) if len(seqs) > 1 else seqs[0]
+    span = read_len + 8
+    ok = lens > span + 8
+    prob = np.where(ok, lens, 0).astype(np.float64)
+    prob /= prob.sum()
+    sid = rng.choice(len(seqs), size=n_reads, p=prob)
+    p = (rng.random(n_reads) * (lens[sid] - span)).astype(np.int64) + starts[sid]
+    strand = rng.integers(0, 2, n_reads)
+    cls = rng.random(n_reads)
+    ne = rng.integers(0, max_e + 1, n_reads)
+    ne = np.where(cls < frac_over, over_e, ne)
+    ne = np.where(cls > 1.0 - frac_exact, 0, ne)
+    out = np.empty((n_reads, read_len), dtype=np.uint8)
+    J = np.arange(span, dtype=np.int64)[None, :]
+    CH = 1 << 18
+    for c0 in range(0, n_reads, CH):
+        c1 = min(n_reads, c0 + CH)
+        m = c1 - c0
+        frag = cat[p[c0:c1, None] + J]
+        for e in range(int(max(over_e, max_e))):
+            act = ne[c0:c1] > e
+            q = rng.integers(0, read_len, m)
+            t = rng.random(m) if metric == "edit" else np.zeros(m)
+            base = ACGT[rng.integers(0, 4, m)]
+            off = rng.integers(1, 4, m)
+            rows = np.nonzero(act & (t < 0.70))[0]
+            if len(rows):
+                cur = np.searchsorted(ACGT, frag[rows, q[rows]])
+                frag[rows, q[rows]] = ACGT[(cur + off[rows]) % 4]
+            rows = np.nonzero(act & (t >= 0.70) & (t < 0.85))[0]
+            if len(rows):
+                qq = q[rows, None]
+                src = np.where(J > qq, J - 1, J)
+                sub = np.take_along_axis(frag[rows], src, axis=1)
+                sub[np.arange(len(rows)), q[rows]] = base[rows]
+                frag[rows] = sub
+            rows = np.nonzero(act & (t >= 0.85))[0]
+            if len(rows):
+                qq = q[rows, None]
+                src = np.minimum(np.where(J >= qq, J + 1, J), span - 1)
+                frag[rows] = np.take_along_axis(frag[rows], src, axis=1)
+        rd = frag[:, :read_len]
+        rc = COMP[rd[:, ::-1]]
+        out[c0:c1] = np.where(strand[c0:c1, None] == 1, rc, rd)
+    return out
+
+
+def write_fastq_matrix(path, reads, first=0):
+    """FASTQ of a uint8 read matrix; read i is named r<first+i>."""
+    n, L = reads.shape
+    qual = b"I" * L
+    with open(path, "wb") as f:
+        for c0 in range(0, n, 1 << 16):
+            blk = reads[c0:c0 + (1 << 16)]
+            f.write(b"".join(b"@r%d\n%s\n+\n%s\n" % (first + c0 + i, blk[i].tobytes(), qual)
+                             for i in range(len(blk))))
+
+
 def write_fastq(path, reads):
     with open(path, "wb") as f:
         for nm, s in reads:
