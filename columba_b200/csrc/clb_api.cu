@@ -169,6 +169,7 @@ struct CudaBackend {
         }
     }
     u32 workers(int kind) { return blocksFor(kind) * 128; }
+    u32 laneStride() const { return 32; }
     template <class K> void launch(const K& k, u32 nMax, const u32* nDev, int kind) {
         if (nMax == 0)
             return;

@@ -71,18 +71,31 @@ template <typename W> struct SearchKernel {
 struct VerifyKernel {
     IndexView ix;
     Batch B;
-    u8* slabs;
-    size_t slabBytes;
+    u8* slabs;        // per lane group: ops[laneStride], hp[rowsCap][laneStride], d0[rowsCap][laneStride]
+    size_t groupBytes;
     u32 rowsCap;
+    u32 laneStride;   // 32 on the GPU (a warp interleaves its rows), 1 in the host emulation
+    u8* wideSlabs;    // Row<u128>[rowsCap] per worker, only when 128-bit matrices can occur
+    size_t wideBytes;
     struct State {
         LocalCtr lc;
         VerifyScratch vs;
     };
+    static CLB_HD size_t opsBytes(u32 cigW) { return ((size_t)cigW * sizeof(u16) + 15) & ~(size_t)15; }
+    static CLB_HD size_t groupSize(u32 cigW, u32 rowsCap, u32 laneStride) {
+        return ((opsBytes(cigW) * laneStride + 255) & ~(size_t)255) + (size_t)2 * rowsCap * laneStride * sizeof(u64);
+    }
     CLB_HD void begin(State& s, u32 worker) const {
         s.lc.clear();
-        u8* p = slabs + (size_t)worker * slabBytes;
-        s.vs.ops = (u16*)p;
-        s.vs.rows = p + (((size_t)B.cigW * 2 * sizeof(u16) + 63) & ~(size_t)63);
+        const u32 group = worker / laneStride, lane = worker % laneStride;
+        u8* g = slabs + (size_t)group * groupBytes;
+        s.vs.ops = (u16*)(g + lane * opsBytes(B.cigW));
+        u64* hp = (u64*)(g + ((opsBytes(B.cigW) * laneStride + 255) & ~(size_t)255)) + lane;
+        s.vs.rs.hp = hp;
+        s.vs.rs.d0 = hp + (size_t)rowsCap * laneStride;
+        s.vs.rs.stride = laneStride;
+        s.vs.rs.cap = rowsCap;
+        s.vs.rows = wideSlabs ? (void*)(wideSlabs + (size_t)worker * wideBytes) : (void*)0;
         s.vs.rowsCap = rowsCap;
     }
     CLB_HD void run(State& s, u32 i) const {

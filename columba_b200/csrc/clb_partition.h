@@ -24,32 +24,59 @@ CLB_HD u32 asciiCode(u8 c) {
     }
 }
 
-// stage 0: codes of the sequence (strand 1 = reverse complement, nucleotide.h)
-// and its "equals A/C/G/T" bit planes, forward and reversed.
-CLB_HD void prepTask(const Batch& B, u32 t) {
-    const u32 r = t >> 1, strand = t & 1;
+// stage 0: codes of both strands of a read (strand 1 = reverse complement,
+// nucleotide.h) and their "equals A/C/G/T" bit planes, forward and reversed.
+// One task = 64 characters of one read: the planes of the reverse complement
+// are the complement-swapped planes of the read, so both strands come out of
+// one pass; codes are written as 8-byte words, planes from registers.
+CLB_HD void prepTask(const Batch& B, u32 task) {
+    const u32 nc = B.nw - 1; // chunks of 64 characters
+    const u32 r = task / nc, j = task % nc;
     const u32 off = B.readOff[r], len = B.readOff[r + 1] - off;
-    u8* codes = B.codes + (size_t)t * B.seqStride;
-    u64* pf = B.planes + ((size_t)t * 2 + DIR_FWD) * 4 * B.nw;
-    u64* pb = B.planes + ((size_t)t * 2 + DIR_BWD) * 4 * B.nw;
-    for (u32 i = 0; i < 4 * B.nw; i++) {
-        pf[i] = 0;
-        pb[i] = 0;
-    }
-    for (u32 i = 0; i < len; i++) {
-        u32 c;
-        if (strand == 0) {
-            c = asciiCode(B.readsAscii[off + i]);
-        } else {
-            c = asciiCode(B.readsAscii[off + len - 1 - i]);
-            if (c < 4)
-                c = 3 - c;
+    const u32 t0 = 2 * r, t1 = 2 * r + 1;
+    const u8* rd = B.readsAscii + off;
+    u64 P[4] = {0, 0, 0, 0}, Q[4] = {0, 0, 0, 0};
+    u64* c0 = (u64*)(B.codes + (size_t)t0 * B.seqStride);
+    u64* c1 = (u64*)(B.codes + (size_t)t1 * B.seqStride);
+    const u32 words = B.seqStride / 8;
+    for (u32 w = 0; w < 8; w++) {
+        u64 w0 = 0, w1 = 0;
+        for (u32 q = 0; q < 8; q++) {
+            const u32 i = 64 * j + 8 * w + q;
+            u32 a = 4, b = 4;
+            if (i < len) {
+                a = asciiCode(rd[i]);
+                b = asciiCode(rd[len - 1 - i]);
+                if (a < 4)
+                    P[a] |= 1ull << (8 * w + q);
+                if (b < 4) {
+                    Q[b] |= 1ull << (8 * w + q);
+                    b = 3 - b;
+                }
+            }
+            w0 |= (u64)a << (8 * q);
+            w1 |= (u64)b << (8 * q);
         }
-        codes[i] = (u8)c;
-        if (c < 4) {
-            pf[c * B.nw + (i >> 6)] |= 1ull << (i & 63);
-            u32 ri = len - 1 - i;
-            pb[c * B.nw + (ri >> 6)] |= 1ull << (ri & 63);
+        const u32 wi = 8 * j + w;
+        if (wi < words) {
+            c0[wi] = w0;
+            c1[wi] = w1;
+        }
+    }
+    u64* p0f = B.planes + ((size_t)t0 * 2 + DIR_FWD) * 4 * B.nw;
+    u64* p0b = B.planes + ((size_t)t0 * 2 + DIR_BWD) * 4 * B.nw;
+    u64* p1f = B.planes + ((size_t)t1 * 2 + DIR_FWD) * 4 * B.nw;
+    u64* p1b = B.planes + ((size_t)t1 * 2 + DIR_BWD) * 4 * B.nw;
+    for (u32 c = 0; c < 4; c++) {
+        p0f[c * B.nw + j] = P[c];
+        p0b[c * B.nw + j] = Q[c];
+        p1f[c * B.nw + j] = Q[3 - c];
+        p1b[c * B.nw + j] = P[3 - c];
+        if (j == nc - 1) { // zero pad word
+            p0f[c * B.nw + nc] = 0;
+            p0b[c * B.nw + nc] = 0;
+            p1f[c * B.nw + nc] = 0;
+            p1b[c * B.nw + nc] = 0;
         }
     }
 }

@@ -68,7 +68,7 @@ template <typename BE> struct Pipeline {
     BE& be;
     IndexView ix;
     DevBuf<BE> bReads, bOff, bCodes, bPlanes, bParts, bTasks, bCands, bFm, bTx, bTxCig, bOut, bOutCig, bPerRead, bIdx,
-        bMisc, bSlabSearch, bSlabVerify, bSlabFilter, bStrategy;
+        bMisc, bSlabSearch, bSlabVerify, bSlabVerifyWide, bSlabFilter, bStrategy;
     // list capacities (per read multipliers, grown after an overflow)
     double candPerRead = 24, fmPerRead = 4, txPerRead = 24, outPerRead = 8;
     u32 minCap = 1 << 16;
@@ -77,7 +77,8 @@ template <typename BE> struct Pipeline {
     Pipeline(BE& b) : be(b) {}
     ~Pipeline() {
         DevBuf<BE>* all[] = {&bReads, &bOff, &bCodes, &bPlanes, &bParts, &bTasks, &bCands, &bFm, &bTx, &bTxCig, &bOut,
-                             &bOutCig, &bPerRead, &bIdx, &bMisc, &bSlabSearch, &bSlabVerify, &bSlabFilter, &bStrategy};
+                             &bOutCig, &bPerRead, &bIdx, &bMisc, &bSlabSearch, &bSlabVerify, &bSlabVerifyWide, &bSlabFilter,
+                             &bStrategy};
         for (auto* d : all)
             d->release(be);
     }
@@ -122,7 +123,7 @@ template <typename BE> struct Pipeline {
             B.readsAscii = (const u8*)bReads.p;
             B.readOff = (const u32*)bOff.p;
         }
-        B.seqStride = (maxLen + 15) & ~15u;
+        B.seqStride = (maxLen + 63) & ~63u;
         B.nw = (maxLen + 63) / 64 + 1;
         bCodes.ensure(be, (size_t)T * B.seqStride);
         bPlanes.ensure(be, (size_t)T * 2 * 4 * B.nw * 8);
@@ -187,7 +188,7 @@ template <typename BE> struct Pipeline {
         // ---- stage 0/1
         {
             PrepKernel k0{B};
-            be.launch(k0, T, nullptr, WK_LIGHT);
+            be.launch(k0, R * (B.nw - 1), nullptr, WK_LIGHT);
             be.mark(STG_PREP);
             PartitionKernel k1{ix, dst, B};
             be.launch(k1, T, nullptr, WK_LIGHT);
@@ -216,12 +217,13 @@ template <typename BE> struct Pipeline {
         const u32 vRows = maxLen + 3 * opt.k + 8;
         {
             const bool wide = !use64(2 * opt.k + 1, opt.k);
-            size_t sb = (((size_t)B.cigW * 2 * 2 + 63) & ~(size_t)63) +
-                        (size_t)vRows * (wide ? sizeof(Row<u128>) : sizeof(Row<u64>));
-            sb = (sb + 63) & ~(size_t)63;
-            const u32 nw = be.workers(WK_VERIFY);
-            bSlabVerify.ensure(be, sb * nw);
-            VerifyKernel k3{ix, B, (u8*)bSlabVerify.p, sb, vRows};
+            const u32 nw = be.workers(WK_VERIFY), ls = be.laneStride();
+            const size_t gb = VerifyKernel::groupSize(B.cigW, vRows, ls);
+            bSlabVerify.ensure(be, gb * ((nw + ls - 1) / ls));
+            const size_t wb = (size_t)vRows * sizeof(Row<u128>);
+            if (wide)
+                bSlabVerifyWide.ensure(be, wb * nw);
+            VerifyKernel k3{ix, B, (u8*)bSlabVerify.p, gb, vRows, ls, wide ? (u8*)bSlabVerifyWide.p : (u8*)0, wb};
             be.launch(k3, capCands, &M->nCands, WK_VERIFY);
             be.mark(STG_VERIFY);
         }

@@ -100,8 +100,19 @@ CLB_HD u32 pushTextOcc(const Batch& B, const TextOccRec& rec, const u16* ops) {
     return at;
 }
 
+// Row storage of the 64-bit fast path: only what the traceback needs (HP and
+// D0 of every row).  Element i of a worker lives at [i * stride]; on the GPU
+// stride = 32 and the 32 lanes of a warp interleave, so that a warp computing
+// row i for 32 candidates writes 2 x 256 contiguous bytes.
+struct RowStore {
+    u64* hp;
+    u64* d0;
+    u32 stride;
+    u32 cap;
+};
 struct VerifyScratch {
-    void* rows;  // Row<u64> or Row<u128>, rowsCap entries of the larger type
+    void* rows;  // Row<u128>[rowsCap], thread private (wide path only; may be null)
+    RowStore rs; // fast path
     u16* ops;    // cigW entries
     u32 rowsCap;
 };
@@ -132,6 +143,162 @@ struct CandSink {
     }
 };
 
+// 64-bit fast path of verifyWindow: the row state (HP, HN, RAC, score) stays in
+// registers, the four match vectors of the current 32-row block are cut out
+// of the read's bit planes once per block, the text is read one 16-character
+// word at a time, the final-column distances are kept in a small local array
+// and only HP/D0 go to memory (coalesced) for the traceback.  Same results as
+// verifyWindow<u64> (bitparallelmatrix.h:352-415, :591-614, :531-586).
+template <typename Sink>
+CLB_HD bool verifyWindowFast(const IndexView& ix, const Batch& B, u32 t, const RowStore& rs, u32 start, u32 end,
+                             u32 nZeros, u32 maxED, u32 minED, u16* ops, u32 opsCap, LocalCtr& lc, bool& considered,
+                             Sink& sink) {
+    typedef BPC<u64> K;
+    const PartSeq ps = fullSeq(B, t);
+    const u32 n = ps.len + 1;
+    const u32 Wv = nZeros - 1 + maxED, Wh = maxED;
+    const u32 m = Wv + n;
+    const u32 sofc = Wh + Wv + 1;
+    const u32 size = end <= start ? 0u : end - start;
+    considered = true;
+    if (!(size >= m - sofc)) {
+        considered = false;
+        return false;
+    }
+    if (size + 1 > rs.cap) {
+        atomOr(B.err, ERR_ROWS_OVERFLOW);
+        return false;
+    }
+    const u32 firstRow = (m - 1) - sofc, col = n - 1;
+    u8 eds[3 * K::MAX_ED + 4];
+    u64 HP = (~0ull) << K::LEFT, HN = ~HP;
+    {
+        const u32 nn = tmin<u32>(nZeros, K::LEFT + 1);
+        for (u32 i = 1; i < nn; ++i)
+            HN ^= 1ull << (K::LEFT - i);
+    }
+    u64 RAC = 1ull << (K::DIAG_R0 + Wh);
+    u32 score = 0;
+    rs.hp[0] = HP;
+    rs.d0[0] = 0;
+    // distance in the final column of the row held in registers
+    auto edAtCol = [&](u32 i) -> u32 {
+        const u32 bit = (i % K::BLOCK) + K::DIAG_R0;
+        u32 b = (i > col) ? bit - (i - col) + 1 : bit + 1;
+        u32 e = (i > col) ? bit + 1 : bit + (col - i) + 1;
+        u64 mask = ((1ull << (e - b)) - 1ull) << b;
+        int neg = popc64(HN & mask), pos = popc64(HP & mask);
+        return score + ((i > col) ? (u32)(neg - pos) : (u32)(pos - neg));
+    };
+    if (firstRow == 0)
+        eds[0] = (u8)edAtCol(0);
+    u64 Mc[4];
+    for (u32 c = 0; c < 4; c++)
+        Mc[c] = matchVec<u64>(ps, 0, c);
+    u32 tw = ix.text[start >> 4];
+    u32 i;
+    bool ok = true;
+    for (i = 1; i <= size; ++i) {
+        const u32 p = start + i - 1;
+        if ((p & 15) == 0)
+            tw = ix.text[p >> 4];
+        const u32 Y = (tw >> ((p & 15) * 2)) & 3u;
+        const u32 l = i % K::BLOCK;
+        RAC <<= 1;
+        if (l == 0) {
+            HP >>= K::BLOCK;
+            HN >>= K::BLOCK;
+            RAC >>= K::BLOCK;
+            const u32 b = i / K::BLOCK;
+            for (u32 c = 0; c < 4; c++)
+                Mc[c] = matchVec<u64>(ps, b, c);
+        }
+        const u64 M = Mc[Y];
+        const u64 D0 = (((M & HP) + HP) ^ HP) | M | HN;
+        const u64 VP = HN | ~(D0 | HP);
+        const u64 VN = D0 & HP;
+        HP = (VN << 1) | ~(D0 | (VP << 1));
+        HN = D0 & (VP << 1);
+        const u32 diagBit = l + K::DIAG_R0;
+        score += (D0 >> diagBit) & 1ull ? 0u : 1u;
+        if (!(D0 & RAC)) {
+            u32 val = 1u;
+            while (val > 0) {
+                if (HP & RAC)
+                    val--;
+                if (HN & RAC)
+                    val++;
+                if (RAC == (1ull << (diagBit - Wv))) {
+                    ok = false;
+                    break;
+                }
+                RAC >>= 1;
+            }
+        }
+        rs.hp[(size_t)i * rs.stride] = HP;
+        rs.d0[(size_t)i * rs.stride] = D0;
+        if (!ok)
+            break;
+        if (i >= firstRow)
+            eds[i - firstRow] = (u8)edAtCol(i);
+    }
+    lc.s[ST_VERIFY_ROWS] += (i <= size) ? i : size;
+    const u32 lastRow = i - 1; // number of rows computed successfully
+    if (lastRow <= size - sofc) // unsigned, as in the reference
+        return false;
+    MatGeom g;
+    g.n = n;
+    g.m = m;
+    g.Wv = Wv;
+    g.Wh = Wh;
+    g.maxED = maxED;
+    TextRef ref;
+    ref.ix = &ix;
+    ref.start = start;
+    bool any = false;
+    for (u32 r = lastRow; r > firstRow; r--) {
+        const u32 ED = eds[r - firstRow];
+        if (ED > maxED || ED < minED)
+            continue;
+        const bool above = ED <= eds[r - 1 - firstRow];
+        const bool below = (r == lastRow) || ED <= eds[r + 1 - firstRow];
+        if (!(above && below))
+            continue;
+        any = true;
+        // traceBack from (r, n-1), bitparallelmatrix.h:531-586
+        u32 ti = r, tj = n - 1, nops = 0;
+        while (tj > 0) {
+            const u32 b = ti / K::BLOCK;
+            const u64 bit = 1ull << ((tj - b * K::BLOCK) + K::DIAG_R0);
+            u32 op;
+            if (rs.hp[(size_t)ti * rs.stride] & bit) {
+                --tj;
+                op = CIG_I;
+            } else if ((ti > 0) && ((matchVec<u64>(ps, b, ref(ti - 1)) | ~rs.d0[(size_t)ti * rs.stride]) & bit)) {
+                --ti;
+                --tj;
+                op = CIG_M;
+            } else {
+                --ti;
+                op = CIG_D;
+            }
+            nops = cigPush(ops, nops, opsCap, op);
+            if (nops == 0xFFFFFFFFu)
+                break;
+        }
+        if (nops != 0xFFFFFFFFu)
+            cigReverse(ops, nops);
+        lc.c[CIGARS_IN_TEXT_VERIFICATION]++;
+        VerifyHit h;
+        h.b = start + ti;
+        h.e = start + r;
+        h.dist = ED;
+        h.ncig = nops;
+        sink(h, ops);
+    }
+    return any;
+}
+
 // stage 3 task (edit distance)
 CLB_HD void verifyEditTask(const IndexView& ix, const Batch& B, u32 ci, VerifyScratch& vs, LocalCtr& lc) {
     const Cand c = B.cands.data[ci];
@@ -144,15 +311,13 @@ CLB_HD void verifyEditTask(const IndexView& ix, const Batch& B, u32 ci, VerifySc
     lc.c[IN_TEXT_STARTED]++;
     CandSink sink(B, c);
     bool considered = true, ok;
+    // number of rows: Wv + n with Wv = nZeros - 1 + maxED (fmindex.cpp:290-299)
+    const u32 nRows = nZeros - 1 + maxED + len + 1;
+    const u32 end = tmin(ix.textLength - 1, start + nRows - 1);
     if (use64(nZeros, maxED)) {
-        // number of rows: Wv + n with Wv = nZeros - 1 + maxED
-        u32 nRows = nZeros - 1 + maxED + len + 1;
-        u32 end = tmin(ix.textLength - 1, start + nRows - 1);
-        ok = verifyWindow<u64>(ix, B, c.t, (Row<u64>*)vs.rows, start, end, nZeros, maxED, minED, vs.ops, B.cigW, lc,
-                               considered, sink);
+        ok = verifyWindowFast(ix, B, c.t, vs.rs, start, end, nZeros, maxED, minED, vs.ops, B.cigW, lc, considered,
+                              sink);
     } else {
-        u32 nRows = nZeros - 1 + maxED + len + 1;
-        u32 end = tmin(ix.textLength - 1, start + nRows - 1);
         ok = verifyWindow<u128>(ix, B, c.t, (Row<u128>*)vs.rows, start, end, nZeros, maxED, minED, vs.ops, B.cigW, lc,
                                 considered, sink);
     }

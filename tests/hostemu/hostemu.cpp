@@ -26,6 +26,7 @@ struct HostEmuBackend {
     void d2h(void* d, const void* s, size_t n) { std::memcpy(d, s, n); }
     void sync() {}
     u32 workers(int) { return 1; }
+    u32 laneStride() const { return 1; }
     template <class K> void launch(const K& k, u32 nMax, const u32* nDev, int) {
         u32 n = nDev ? (*nDev < nMax ? *nDev : nMax) : nMax;
         typename K::State st;
