@@ -56,15 +56,39 @@ __global__ void __launch_bounds__(128) clb_kernel(const K k, u32 nMax, const u32
     k.end(st);
 }
 
-// exclusive scan of n u32 values by one block (out[n] = total)
-__global__ void __launch_bounds__(1024) clb_scan_kernel(const u32* __restrict__ in, u32* __restrict__ out, u32 n) {
+// exclusive scan of n u32 values (out[n] = total) in three launches:
+// per-tile sums, scan of the tile sums by one block, per-tile scan + offset.
+static const u32 SCAN_TILE = 2048; // 256 threads x 8 values
+__global__ void __launch_bounds__(256) clb_scan_tile_sums(const u32* __restrict__ in, u32* __restrict__ sums, u32 n) {
+    __shared__ u32 red[8];
+    const u32 base = blockIdx.x * SCAN_TILE;
+    u32 s = 0;
+    for (u32 q = 0; q < 8; q++) {
+        u32 i = base + q * 256 + threadIdx.x;
+        if (i < n)
+            s += in[i];
+    }
+    for (u32 o = 16; o > 0; o >>= 1)
+        s += __shfl_down_sync(0xFFFFFFFFu, s, o);
+    if ((threadIdx.x & 31) == 0)
+        red[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        u32 t = 0;
+        for (u32 w = 0; w < 8; w++)
+            t += red[w];
+        sums[blockIdx.x] = t;
+    }
+}
+// in place exclusive scan of the tile sums by one block; total -> *total
+__global__ void __launch_bounds__(1024) clb_scan_sums(u32* __restrict__ sums, u32 nb, u32* __restrict__ total) {
     __shared__ u32 part[1024];
     const u32 tid = threadIdx.x, nt = blockDim.x;
-    const u32 per = (n + nt - 1) / nt;
-    const u32 b = tid * per, e = (b + per < n) ? b + per : n;
+    const u32 per = (nb + nt - 1) / nt;
+    const u32 b = tid * per, e = (b + per < nb) ? b + per : nb;
     u32 sum = 0;
     for (u32 i = b; i < e; i++)
-        sum += in[i];
+        sum += sums[i];
     part[tid] = sum;
     __syncthreads();
     for (u32 off = 1; off < nt; off <<= 1) {
@@ -75,12 +99,42 @@ __global__ void __launch_bounds__(1024) clb_scan_kernel(const u32* __restrict__ 
     }
     u32 run = part[tid] - sum;
     for (u32 i = b; i < e; i++) {
-        u32 v = in[i];
-        out[i] = run;
+        u32 v = sums[i];
+        sums[i] = run;
         run += v;
     }
     if (tid == nt - 1)
-        out[n] = part[nt - 1];
+        *total = part[nt - 1];
+}
+__global__ void __launch_bounds__(256) clb_scan_tiles(const u32* __restrict__ in, u32* __restrict__ out,
+                                                      const u32* __restrict__ sums, u32 n) {
+    __shared__ u32 wsum[8];
+    const u32 base = blockIdx.x * SCAN_TILE + threadIdx.x * 8;
+    u32 v[8], s = 0;
+    for (u32 q = 0; q < 8; q++) {
+        v[q] = (base + q < n) ? in[base + q] : 0;
+        s += v[q];
+    }
+    // exclusive scan of s over the block
+    u32 incl = s;
+    const u32 lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (u32 o = 1; o < 32; o <<= 1) {
+        u32 t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+        if (lane >= o)
+            incl += t;
+    }
+    if (lane == 31)
+        wsum[warp] = incl;
+    __syncthreads();
+    u32 woff = 0;
+    for (u32 w = 0; w < warp; w++)
+        woff += wsum[w];
+    u32 run = sums[blockIdx.x] + woff + incl - s;
+    for (u32 q = 0; q < 8; q++) {
+        if (base + q < n)
+            out[base + q] = run;
+        run += v[q];
+    }
 }
 
 struct CudaBackend {
@@ -89,6 +143,8 @@ struct CudaBackend {
     cudaStream_t stream = nullptr;    // stream in use
     cudaStream_t ownStream = nullptr; // created by this backend
     u32* workCtrs = nullptr; // pool of work counters, one per dynamic launch
+    u32* scanSums = nullptr; // tile sums of exclusiveScan
+    u32 scanCap = 0;
     u32 nextCtr = 0;
     static const u32 N_CTRS = 64;
     cudaEvent_t evBegin = nullptr, evEnd = nullptr, evStage[N_STAGES + 1];
@@ -127,6 +183,8 @@ struct CudaBackend {
             cudaStreamSynchronize(stream);
         if (workCtrs)
             cudaFree(workCtrs);
+        if (scanSums)
+            cudaFree(scanSums);
         if (evBegin)
             cudaEventDestroy(evBegin);
         if (evEnd)
@@ -189,9 +247,20 @@ struct CudaBackend {
         launches++;
     }
     void exclusiveScan(const u32* in, u32* out, u32 n) {
-        clb_scan_kernel<<<1, 1024, 0, stream>>>(in, out, n);
+        const u32 nb = (n + SCAN_TILE - 1) / SCAN_TILE;
+        if (nb > scanCap) {
+            if (scanSums) {
+                CLB_CUDA(cudaStreamSynchronize(stream));
+                cudaFree(scanSums);
+            }
+            scanCap = nb + nb / 2 + 64;
+            CLB_CUDA(cudaMalloc(&scanSums, scanCap * sizeof(u32)));
+        }
+        clb_scan_tile_sums<<<nb, 256, 0, stream>>>(in, scanSums, n);
+        clb_scan_sums<<<1, 1024, 0, stream>>>(scanSums, nb, out + n);
+        clb_scan_tiles<<<nb, 256, 0, stream>>>(in, out, scanSums, n);
         CLB_CUDA(cudaGetLastError());
-        launches++;
+        launches += 3;
     }
     void mark(int stage) {
         if (stage >= 0 && stage < N_STAGES) {

@@ -255,38 +255,60 @@ CLB_HD bool verifyWindowFast(const IndexView& ix, const Batch& B, u32 t, const R
     TextRef ref;
     ref.ix = &ix;
     ref.start = start;
-    bool any = false;
+    // cluster centres first (findClusterCenters, bitparallelmatrix.h:591-614), then
+    // one traceback per centre: keeping the two loops apart lets the lanes of a
+    // warp run their tracebacks side by side
+    u8 centres[3 * K::MAX_ED + 4];
+    u32 nCentres = 0;
     for (u32 r = lastRow; r > firstRow; r--) {
         const u32 ED = eds[r - firstRow];
         if (ED > maxED || ED < minED)
             continue;
         const bool above = ED <= eds[r - 1 - firstRow];
         const bool below = (r == lastRow) || ED <= eds[r + 1 - firstRow];
-        if (!(above && below))
-            continue;
-        any = true;
-        // traceBack from (r, n-1), bitparallelmatrix.h:531-586
-        u32 ti = r, tj = n - 1, nops = 0;
+        if (above && below)
+            centres[nCentres++] = (u8)(r - firstRow);
+    }
+    const u8* codes = seqCodes(B, t);
+    for (u32 ci = 0; ci < nCentres; ci++) {
+        const u32 r = firstRow + centres[ci];
+        const u32 ED = eds[r - firstRow];
+        // traceBack from (r, n-1), bitparallelmatrix.h:531-586, branch-light: the
+        // match-vector bit of column tj is (read[tj-1] == text[ti-1])
+        u32 ti = r, tj = n - 1, nops = 0, runOp = 4, runLen = 0;
+        bool over = false;
         while (tj > 0) {
-            const u32 b = ti / K::BLOCK;
-            const u64 bit = 1ull << ((tj - b * K::BLOCK) + K::DIAG_R0);
-            u32 op;
-            if (rs.hp[(size_t)ti * rs.stride] & bit) {
-                --tj;
-                op = CIG_I;
-            } else if ((ti > 0) && ((matchVec<u64>(ps, b, ref(ti - 1)) | ~rs.d0[(size_t)ti * rs.stride]) & bit)) {
-                --ti;
-                --tj;
-                op = CIG_M;
+            const u32 bitpos = (tj - (ti / K::BLOCK) * K::BLOCK) + K::DIAG_R0;
+            const u64 hpw = rs.hp[(size_t)ti * rs.stride], d0w = rs.d0[(size_t)ti * rs.stride];
+            const u32 isI = (u32)(hpw >> bitpos) & 1u;
+            const u32 Y = ti > 0 ? ref(ti - 1) : 5u;
+            const u32 diag = (ti > 0) && (codes[tj - 1] == Y || !((d0w >> bitpos) & 1ull));
+            const u32 isM = (isI ^ 1u) & diag;
+            const u32 op = isI ? (u32)CIG_I : (isM ? (u32)CIG_M : (u32)CIG_D);
+            tj -= (isI | isM);
+            ti -= (isI ^ 1u);
+            if (op == runOp) {
+                runLen++;
             } else {
-                --ti;
-                op = CIG_D;
+                if (runLen) { // the run in registers is complete: one store per run
+                    if (nops < opsCap)
+                        ops[nops++] = (u16)((runLen << 2) | runOp);
+                    else
+                        over = true;
+                }
+                runOp = op;
+                runLen = 1;
             }
-            nops = cigPush(ops, nops, opsCap, op);
-            if (nops == 0xFFFFFFFFu)
-                break;
         }
-        if (nops != 0xFFFFFFFFu)
+        if (runLen) {
+            if (nops < opsCap)
+                ops[nops++] = (u16)((runLen << 2) | runOp);
+            else
+                over = true;
+        }
+        if (over)
+            nops = 0xFFFFFFFFu;
+        else
             cigReverse(ops, nops);
         lc.c[CIGARS_IN_TEXT_VERIFICATION]++;
         VerifyHit h;
@@ -296,7 +318,7 @@ CLB_HD bool verifyWindowFast(const IndexView& ix, const Batch& B, u32 t, const R
         h.ncig = nops;
         sink(h, ops);
     }
-    return any;
+    return nCentres > 0;
 }
 
 // stage 3 task (edit distance)
