@@ -24,8 +24,21 @@ namespace clb {
 // One thread = one worker.  Static striding for uniform tasks; for tasks of
 // very different cost (searches, verifications, per-read filters) each warp
 // claims 32 tasks at a time from a global counter.
+// optional per-CTA shared memory of a functor: K::smemBytes(nThreads) and
+// K::bindShared(state, smem, tid, nThreads)
+template <class K> auto smemBytesOf(const K&, u32 nThreads, int) -> decltype(K::smemBytes(nThreads)) {
+    return K::smemBytes(nThreads);
+}
+template <class K> size_t smemBytesOf(const K&, u32, long) { return 0; }
+template <class K, class S>
+__device__ __forceinline__ auto bindSharedOf(const K& k, S& st, u8* smem, int) -> decltype(k.bindShared(st, smem, 0u, 0u)) {
+    k.bindShared(st, smem, threadIdx.x, blockDim.x);
+}
+template <class K, class S> __device__ __forceinline__ void bindSharedOf(const K&, S&, u8*, long) {}
+
 template <class K>
 __global__ void __launch_bounds__(128) clb_kernel(const K k, u32 nMax, const u32* __restrict__ nDev, u32* workCtr) {
+    extern __shared__ __align__(16) u8 clb_smem[];
     u32 n = nMax;
     if (nDev) {
         u32 v = *nDev;
@@ -35,6 +48,7 @@ __global__ void __launch_bounds__(128) clb_kernel(const K k, u32 nMax, const u32
     const u32 nWorkers = gridDim.x * blockDim.x;
     typename K::State st;
     k.begin(st, worker);
+    bindSharedOf(k, st, clb_smem, 0);
     if (workCtr == nullptr) {
         for (u32 i = worker; i < n; i += nWorkers)
             k.run(st, i);
@@ -232,6 +246,20 @@ struct CudaBackend {
         if (nMax == 0)
             return;
         u32 blocks = blocksFor(kind);
+        const size_t smem = smemBytesOf(k, 128u, 0);
+        if (smem) {
+            // never more CTAs than can be resident: the slabs are sized for blocksFor(kind) workers
+            static int perSM = 0;
+            if (!perSM) {
+                if (smem > 48 * 1024)
+                    CLB_CUDA(cudaFuncSetAttribute(clb_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+                CLB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, clb_kernel<K>, 128, smem));
+                if (perSM < 1)
+                    throw BackendError("kernel does not fit on an SM");
+            }
+            if ((u32)perSM * (u32)numSMs < blocks)
+                blocks = (u32)perSM * (u32)numSMs;
+        }
         u32* ctr = nullptr;
         if (kind != WK_LIGHT) {
             if (nextCtr >= N_CTRS)
@@ -242,7 +270,7 @@ struct CudaBackend {
             if (need < blocks)
                 blocks = need;
         }
-        clb_kernel<K><<<blocks, 128, 0, stream>>>(k, nMax, nDev, ctr);
+        clb_kernel<K><<<blocks, 128, smem, stream>>>(k, nMax, nDev, ctr);
         CLB_CUDA(cudaGetLastError());
         launches++;
     }

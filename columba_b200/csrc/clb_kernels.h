@@ -71,10 +71,10 @@ template <typename W> struct SearchKernel {
 struct VerifyKernel {
     IndexView ix;
     Batch B;
-    u8* slabs;        // per lane group: ops[laneStride], hp[rowsCap][laneStride], d0[rowsCap][laneStride]
+    u8* slabs;        // per lane group: ops[laneStride], cp[2 * cpCap][laneStride], ring[32][laneStride]
     size_t groupBytes;
     u32 rowsCap;
-    u32 laneStride;   // 32 on the GPU (a warp interleaves its rows), 1 in the host emulation
+    u32 laneStride;   // 32 on the GPU (the lanes of a warp interleave), 1 in the host emulation
     u8* wideSlabs;    // Row<u128>[rowsCap] per worker, only when 128-bit matrices can occur
     size_t wideBytes;
     struct State {
@@ -82,19 +82,29 @@ struct VerifyKernel {
         VerifyScratch vs;
     };
     static CLB_HD size_t opsBytes(u32 cigW) { return ((size_t)cigW * sizeof(u16) + 15) & ~(size_t)15; }
+    static CLB_HD u32 cpCapOf(u32 rowsCap) { return rowsCap / BPC<u64>::BLOCK + 2; }
+    static CLB_HD size_t opsGroup(u32 cigW, u32 laneStride) { return (opsBytes(cigW) * laneStride + 255) & ~(size_t)255; }
     static CLB_HD size_t groupSize(u32 cigW, u32 rowsCap, u32 laneStride) {
-        return ((opsBytes(cigW) * laneStride + 255) & ~(size_t)255) + (size_t)2 * rowsCap * laneStride * sizeof(u64);
+        return opsGroup(cigW, laneStride) + (size_t)(2 * cpCapOf(rowsCap) + BPC<u64>::BLOCK) * laneStride * sizeof(u64);
+    }
+    // the CUDA launcher gives every CTA a ring in shared memory
+    static CLB_HD size_t smemBytes(u32 nThreads) { return (size_t)BPC<u64>::BLOCK * nThreads * sizeof(u64); }
+    CLB_HD void bindShared(State& s, u8* smem, u32 tid, u32 nThreads) const {
+        s.vs.bs.ring = (u64*)smem + tid;
+        s.vs.bs.ringStride = nThreads;
     }
     CLB_HD void begin(State& s, u32 worker) const {
         s.lc.clear();
         const u32 group = worker / laneStride, lane = worker % laneStride;
         u8* g = slabs + (size_t)group * groupBytes;
         s.vs.ops = (u16*)(g + lane * opsBytes(B.cigW));
-        u64* hp = (u64*)(g + ((opsBytes(B.cigW) * laneStride + 255) & ~(size_t)255)) + lane;
-        s.vs.rs.hp = hp;
-        s.vs.rs.d0 = hp + (size_t)rowsCap * laneStride;
-        s.vs.rs.stride = laneStride;
-        s.vs.rs.cap = rowsCap;
+        u64* cp = (u64*)(g + opsGroup(B.cigW, laneStride)) + lane;
+        const u32 cpCap = cpCapOf(rowsCap);
+        s.vs.bs.cp = cp;
+        s.vs.bs.cpStride = laneStride;
+        s.vs.bs.cpCap = cpCap;
+        s.vs.bs.ring = cp + (size_t)2 * cpCap * laneStride;
+        s.vs.bs.ringStride = laneStride;
         s.vs.rows = wideSlabs ? (void*)(wideSlabs + (size_t)worker * wideBytes) : (void*)0;
         s.vs.rowsCap = rowsCap;
     }

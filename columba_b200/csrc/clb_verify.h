@@ -100,20 +100,26 @@ CLB_HD u32 pushTextOcc(const Batch& B, const TextOccRec& rec, const u16* ops) {
     return at;
 }
 
-// Row storage of the 64-bit fast path: only what the traceback needs (HP and
-// D0 of every row).  Element i of a worker lives at [i * stride]; on the GPU
-// stride = 32 and the 32 lanes of a warp interleave, so that a warp computing
-// row i for 32 candidates writes 2 x 256 contiguous bytes.
-struct RowStore {
-    u64* hp;
-    u64* d0;
-    u32 stride;
-    u32 cap;
+// Storage of the 64-bit fast path.  No matrix row goes to HBM: the traceback
+// only needs, per cell of the band, "horizontal delta is +1" (HP) and "the
+// diagonal predecessor explains the value" (match | !D0), i.e. 2 bits per
+// cell of a band that is at most 31 cells wide.  The forward pass keeps these
+// for the rows of the current 32-row block in `ring` (shared memory on the
+// GPU) and one checkpoint (HP, HN entering the block) per block in `cp`; the
+// traceback re-computes an earlier block from its checkpoint into the ring
+// when it gets there.  Element i of a worker lives at [i * stride] (stride =
+// number of workers that interleave: lanes of a warp / threads of a CTA).
+struct BandStore {
+    u64* ring;      // 32 slots: low word = HP band, high word = (M | ~D0) band
+    u32 ringStride;
+    u64* cp;        // 2 x cpCap: HP, HN
+    u32 cpStride;
+    u32 cpCap;
 };
 struct VerifyScratch {
-    void* rows;  // Row<u128>[rowsCap], thread private (wide path only; may be null)
-    RowStore rs; // fast path
-    u16* ops;    // cigW entries
+    void* rows;   // Row<u128>[rowsCap], thread private (wide path only; may be null)
+    BandStore bs; // fast path
+    u16* ops;     // cigW entries
     u32 rowsCap;
 };
 
@@ -143,14 +149,26 @@ struct CandSink {
     }
 };
 
+// One row of the banded matrix (bitparallelmatrix.h:352-398) on the state in
+// registers; returns D0.
+CLB_HD u64 bandRow(u64& HP, u64& HN, u64 M) {
+    const u64 D0 = (((M & HP) + HP) ^ HP) | M | HN;
+    const u64 VP = HN | ~(D0 | HP);
+    const u64 VN = D0 & HP;
+    HP = (VN << 1) | ~(D0 | (VP << 1));
+    HN = D0 & (VP << 1);
+    return D0;
+}
+CLB_HD u64 bandPack(u64 HP, u64 X, u32 sh) { return (u64)(u32)(HP >> sh) | ((u64)(u32)(X >> sh) << 32); }
+
 // 64-bit fast path of verifyWindow: the row state (HP, HN, RAC, score) stays in
 // registers, the four match vectors of the current 32-row block are cut out
 // of the read's bit planes once per block, the text is read one 16-character
 // word at a time, the final-column distances are kept in a small local array
-// and only HP/D0 go to memory (coalesced) for the traceback.  Same results as
-// verifyWindow<u64> (bitparallelmatrix.h:352-415, :591-614, :531-586).
+// and the traceback information lives in the BandStore (see there).  Same
+// results as verifyWindow<u64> (bitparallelmatrix.h:352-415, :591-614, :531-586).
 template <typename Sink>
-CLB_HD bool verifyWindowFast(const IndexView& ix, const Batch& B, u32 t, const RowStore& rs, u32 start, u32 end,
+CLB_HD bool verifyWindowFast(const IndexView& ix, const Batch& B, u32 t, const BandStore& bs, u32 start, u32 end,
                              u32 nZeros, u32 maxED, u32 minED, u16* ops, u32 opsCap, LocalCtr& lc, bool& considered,
                              Sink& sink) {
     typedef BPC<u64> K;
@@ -165,11 +183,12 @@ CLB_HD bool verifyWindowFast(const IndexView& ix, const Batch& B, u32 t, const R
         considered = false;
         return false;
     }
-    if (size + 1 > rs.cap) {
+    if (size / K::BLOCK + 1 > bs.cpCap) {
         atomOr(B.err, ERR_ROWS_OVERFLOW);
         return false;
     }
     const u32 firstRow = (m - 1) - sofc, col = n - 1;
+    const u32 sh0 = K::DIAG_R0 - Wv; // band of row i = bits [i%32 + sh0, i%32 + sh0 + Wv + Wh]
     u8 eds[3 * K::MAX_ED + 4];
     u64 HP = (~0ull) << K::LEFT, HN = ~HP;
     {
@@ -179,8 +198,9 @@ CLB_HD bool verifyWindowFast(const IndexView& ix, const Batch& B, u32 t, const R
     }
     u64 RAC = 1ull << (K::DIAG_R0 + Wh);
     u32 score = 0;
-    rs.hp[0] = HP;
-    rs.d0[0] = 0;
+    bs.ring[0] = bandPack(HP, 0, sh0);
+    bs.cp[0] = HP;
+    bs.cp[bs.cpStride] = HN;
     // distance in the final column of the row held in registers
     auto edAtCol = [&](u32 i) -> u32 {
         const u32 bit = (i % K::BLOCK) + K::DIAG_R0;
@@ -212,13 +232,11 @@ CLB_HD bool verifyWindowFast(const IndexView& ix, const Batch& B, u32 t, const R
             const u32 b = i / K::BLOCK;
             for (u32 c = 0; c < 4; c++)
                 Mc[c] = matchVec<u64>(ps, b, c);
+            bs.cp[(size_t)(2 * b) * bs.cpStride] = HP;
+            bs.cp[(size_t)(2 * b + 1) * bs.cpStride] = HN;
         }
         const u64 M = Mc[Y];
-        const u64 D0 = (((M & HP) + HP) ^ HP) | M | HN;
-        const u64 VP = HN | ~(D0 | HP);
-        const u64 VN = D0 & HP;
-        HP = (VN << 1) | ~(D0 | (VP << 1));
-        HN = D0 & (VP << 1);
+        const u64 D0 = bandRow(HP, HN, M);
         const u32 diagBit = l + K::DIAG_R0;
         score += (D0 >> diagBit) & 1ull ? 0u : 1u;
         if (!(D0 & RAC)) {
@@ -235,10 +253,9 @@ CLB_HD bool verifyWindowFast(const IndexView& ix, const Batch& B, u32 t, const R
                 RAC >>= 1;
             }
         }
-        rs.hp[(size_t)i * rs.stride] = HP;
-        rs.d0[(size_t)i * rs.stride] = D0;
         if (!ok)
             break;
+        bs.ring[(size_t)l * bs.ringStride] = bandPack(HP, M | ~D0, l + sh0);
         if (i >= firstRow)
             eds[i - firstRow] = (u8)edAtCol(i);
     }
@@ -246,15 +263,6 @@ CLB_HD bool verifyWindowFast(const IndexView& ix, const Batch& B, u32 t, const R
     const u32 lastRow = i - 1; // number of rows computed successfully
     if (lastRow <= size - sofc) // unsigned, as in the reference
         return false;
-    MatGeom g;
-    g.n = n;
-    g.m = m;
-    g.Wv = Wv;
-    g.Wh = Wh;
-    g.maxED = maxED;
-    TextRef ref;
-    ref.ix = &ix;
-    ref.start = start;
     // cluster centres first (findClusterCenters, bitparallelmatrix.h:591-614), then
     // one traceback per centre: keeping the two loops apart lets the lanes of a
     // warp run their tracebacks side by side
@@ -269,37 +277,67 @@ CLB_HD bool verifyWindowFast(const IndexView& ix, const Batch& B, u32 t, const R
         if (above && below)
             centres[nCentres++] = (u8)(r - firstRow);
     }
-    const u8* codes = seqCodes(B, t);
+    u32 ringBlock = lastRow / K::BLOCK; // the block whose rows the ring holds
     for (u32 ci = 0; ci < nCentres; ci++) {
         const u32 r = firstRow + centres[ci];
         const u32 ED = eds[r - firstRow];
-        // traceBack from (r, n-1), bitparallelmatrix.h:531-586, branch-light: the
-        // match-vector bit of column tj is (read[tj-1] == text[ti-1])
+        // traceBack from (r, n-1), bitparallelmatrix.h:531-586 (precedence I, diagonal, D)
         u32 ti = r, tj = n - 1, nops = 0, runOp = 4, runLen = 0;
-        bool over = false;
-        while (tj > 0) {
-            const u32 bitpos = (tj - (ti / K::BLOCK) * K::BLOCK) + K::DIAG_R0;
-            const u64 hpw = rs.hp[(size_t)ti * rs.stride], d0w = rs.d0[(size_t)ti * rs.stride];
-            const u32 isI = (u32)(hpw >> bitpos) & 1u;
-            const u32 Y = ti > 0 ? ref(ti - 1) : 5u;
-            const u32 diag = (ti > 0) && (codes[tj - 1] == Y || !((d0w >> bitpos) & 1ull));
-            const u32 isM = (isI ^ 1u) & diag;
-            const u32 op = isI ? (u32)CIG_I : (isM ? (u32)CIG_M : (u32)CIG_D);
-            tj -= (isI | isM);
-            ti -= (isI ^ 1u);
-            if (op == runOp) {
-                runLen++;
-            } else {
-                if (runLen) { // the run in registers is complete: one store per run
-                    if (nops < opsCap)
-                        ops[nops++] = (u16)((runLen << 2) | runOp);
-                    else
-                        over = true;
+        bool over = false, bad = false;
+        while (tj > 0 && !bad) {
+            const u32 cb = ti / K::BLOCK;
+            if (cb != ringBlock) {
+                // rows of block cb again, from its checkpoint
+                u64 hp = bs.cp[(size_t)(2 * cb) * bs.cpStride], hn = bs.cp[(size_t)(2 * cb + 1) * bs.cpStride];
+                u64 Mr[4];
+                for (u32 c = 0; c < 4; c++)
+                    Mr[c] = matchVec<u64>(ps, cb, c);
+                u32 i0 = cb * K::BLOCK;
+                if (cb == 0) {
+                    bs.ring[0] = bandPack(hp, 0, sh0);
+                    i0 = 1;
                 }
-                runOp = op;
-                runLen = 1;
+                const u32 i1 = tmin(cb * K::BLOCK + K::BLOCK - 1, lastRow);
+                u32 w = ix.text[(start + i0 - 1) >> 4];
+                for (u32 q = i0; q <= i1; q++) {
+                    const u32 p = start + q - 1;
+                    if ((p & 15) == 0)
+                        w = ix.text[p >> 4];
+                    const u64 M = Mr[(w >> ((p & 15) * 2)) & 3u];
+                    const u64 D0 = bandRow(hp, hn, M);
+                    const u32 l = q % K::BLOCK;
+                    bs.ring[(size_t)l * bs.ringStride] = bandPack(hp, M | ~D0, l + sh0);
+                }
+                ringBlock = cb;
             }
+            do {
+                const u64 w = bs.ring[(size_t)(ti % K::BLOCK) * bs.ringStride];
+                const u32 bidx = tj + Wv - ti; // cell (ti, tj) within the band of row ti
+                if (bidx > Wv + Wh) {
+                    bad = true;
+                    break;
+                }
+                const u32 isI = ((u32)w >> bidx) & 1u;
+                const u32 isM = (isI ^ 1u) & ((u32)(w >> 32) >> bidx) & 1u;
+                const u32 op = isI ? (u32)CIG_I : (isM ? (u32)CIG_M : (u32)CIG_D);
+                tj -= (isI | isM);
+                ti -= (isI ^ 1u);
+                if (op == runOp) {
+                    runLen++;
+                } else {
+                    if (runLen) { // the run in registers is complete: one store per run
+                        if (nops < opsCap)
+                            ops[nops++] = (u16)((runLen << 2) | runOp);
+                        else
+                            over = true;
+                    }
+                    runOp = op;
+                    runLen = 1;
+                }
+            } while (tj > 0 && ti / K::BLOCK == cb);
         }
+        if (bad)
+            atomOr(B.err, ERR_INTERNAL);
         if (runLen) {
             if (nops < opsCap)
                 ops[nops++] = (u16)((runLen << 2) | runOp);
@@ -337,7 +375,7 @@ CLB_HD void verifyEditTask(const IndexView& ix, const Batch& B, u32 ci, VerifySc
     const u32 nRows = nZeros - 1 + maxED + len + 1;
     const u32 end = tmin(ix.textLength - 1, start + nRows - 1);
     if (use64(nZeros, maxED)) {
-        ok = verifyWindowFast(ix, B, c.t, vs.rs, start, end, nZeros, maxED, minED, vs.ops, B.cigW, lc, considered,
+        ok = verifyWindowFast(ix, B, c.t, vs.bs, start, end, nZeros, maxED, minED, vs.ops, B.cigW, lc, considered,
                               sink);
     } else {
         ok = verifyWindow<u128>(ix, B, c.t, (Row<u128>*)vs.rows, start, end, nZeros, maxED, minED, vs.ops, B.cigW, lc,
