@@ -67,21 +67,21 @@ CLB_HD BwtRec loadRec(const BwtRec* p) {
 }
 
 // occ of A,C,G,T in BWT[0,p)
-CLB_HD void occ4(const BwtView& v, u32 p, u32 o[4]) {
-    BwtRec r = loadRec(v.rec + (p >> 6));
+CLB_HD void occ4raw(const BwtRec* rec, u32 dollarPos, u32 p, u32 o[4]) {
+    BwtRec r = loadRec(rec + (p >> 6));
     u32 off = p & 63;
     u64 m = (1ull << off) - 1ull;
     u64 lo = r.lo & m, hi = r.hi & m;
     u32 nT = popc64(hi & lo), nG = popc64(hi) - nT, nC = popc64(lo) - nT;
     u32 nA = off - nT - nG - nC;
     // '$' is stored as an 'A'
-    if ((v.dollarPos >> 6) == (p >> 6) && v.dollarPos < p)
-        nA--;
+    nA -= ((dollarPos >> 6) == (p >> 6) && dollarPos < p) ? 1u : 0u;
     o[0] = r.cnt[0] + nA;
     o[1] = r.cnt[1] + nC;
     o[2] = r.cnt[2] + nG;
     o[3] = r.cnt[3] + nT;
 }
+CLB_HD void occ4(const BwtView& v, u32 p, u32 o[4]) { occ4raw(v.rec, v.dollarPos, p, o); }
 // symbol (0..3) of BWT[p]; caller handles p == dollarPos
 CLB_HD u32 bwtSym(const BwtRec& r, u32 off) {
     return (u32)((r.lo >> off) & 1) | ((u32)((r.hi >> off) & 1) << 1);
@@ -121,35 +121,33 @@ CLB_HD void extendAll(const IndexView& ix, int dir, bool uniBack, const RangePai
         }
     }
 }
-// single character (code 0..3) -- indexinterface.cpp:1034-1049 (addChar)
+// single character (code 0..3) -- indexinterface.cpp:1034-1049 (addChar).
+// Written without branches on dir / uniBack / c: the lanes of a warp extend
+// different parts in different directions in the same instruction stream.
 CLB_HD bool extendOne(const IndexView& ix, int dir, bool uniBack, u32 c, RangePair& r) {
-    const BwtView& bw = (dir == DIR_BWD) ? ix.fwd : ix.rev;
-    const Range t = (dir == DIR_BWD) ? r.sa : r.rev;
+    const bool bwd = (dir == DIR_BWD);
+    const BwtRec* rec = bwd ? ix.fwd.rec : ix.rev.rec;
+    const u32 dollar = bwd ? ix.fwd.dollarPos : ix.rev.dollarPos;
+    const u32 tb = bwd ? r.sa.b : r.rev.b, te = bwd ? r.sa.e : r.rev.e;
+    const u32 s = bwd ? r.rev.b : r.sa.b;
     u32 ob[4], oe[4];
-    occ4(bw, t.b, ob);
-    occ4(bw, t.e, oe);
-    u32 s = (dir == DIR_BWD) ? r.rev.b : r.sa.b;
-    u32 x = (t.b <= bw.dollarPos && bw.dollarPos < t.e) ? 1u : 0u;
-    for (u32 i = 0; i < c; i++)
-        x += oe[i] - ob[i];
-    Range r1;
-    r1.b = ob[c] + ix.C[c + 1];
-    r1.e = oe[c] + ix.C[c + 1];
-    u32 w = r1.width();
-    Range r2;
-    r2.b = s + x;
-    r2.e = s + x + w;
-    if (uniBack) {
-        r.sa = r1;
-        r.rev.b = r.rev.e = 0;
-    } else if (dir == DIR_BWD) {
-        r.sa = r1;
-        r.rev = r2;
-    } else {
-        r.sa = r2;
-        r.rev = r1;
-    }
-    return !r1.empty();
+    occ4raw(rec, dollar, tb, ob);
+    occ4raw(rec, dollar, te, oe);
+    u32 x = (tb <= dollar && dollar < te) ? 1u : 0u;
+    x += (c > 0) ? oe[0] - ob[0] : 0u;
+    x += (c > 1) ? oe[1] - ob[1] : 0u;
+    x += (c > 2) ? oe[2] - ob[2] : 0u;
+    const u32 obc = (c == 0) ? ob[0] : (c == 1) ? ob[1] : (c == 2) ? ob[2] : ob[3];
+    const u32 oec = (c == 0) ? oe[0] : (c == 1) ? oe[1] : (c == 2) ? oe[2] : oe[3];
+    const u32 Cc = (c == 0) ? ix.C[1] : (c == 1) ? ix.C[2] : (c == 2) ? ix.C[3] : ix.C[4];
+    const u32 b1 = obc + Cc, e1 = oec + Cc;
+    const u32 w = e1 <= b1 ? 0u : e1 - b1;
+    const u32 b2 = s + x, e2 = s + x + w;
+    r.sa.b = bwd ? b1 : b2;
+    r.sa.e = bwd ? e1 : e2;
+    r.rev.b = uniBack ? 0u : (bwd ? b2 : b1);
+    r.rev.e = uniBack ? 0u : (bwd ? e2 : e1);
+    return w != 0;
 }
 
 CLB_HD RangePair completeRange(const IndexView& ix) { return mkPair(0, ix.textLength, 0, ix.textLength); }

@@ -159,26 +159,28 @@ CLB_HD void partitionDynamic(const IndexView& ix, const DevStrategy& st, const u
             }
         }
     }
-    int dir = DIR_FWD;
-    u32 partToExtend = 0;
+    // The greedy loop of partitionDynamic (:340-376).  key[i] = width x weight of
+    // part i while it can still grow (0 otherwise); only the extended part and
+    // the neighbour it grew towards change per step, so a step is one argmax over
+    // P cached keys, one single-character extension and two key updates.
+    u64 key[MAXP];
+    u32 wd[MAXP];
+    for (u32 i = 0; i < P; i++)
+        wd[i] = ps.emr[i].width();
+    auto keyOf = [&](u32 i) -> u64 {
+        const bool noL = (i == 0) || ps.b[i] == ps.e[i - 1];
+        const bool noR = (i == P - 1) || ps.e[i] == ps.b[i + 1];
+        return (noL && noR) ? 0ull : (u64)wd[i] * st.weights[i];
+    };
+    for (u32 i = 0; i < P; i++)
+        key[i] = keyOf(i);
     for (u32 j = matched; j < pSize; j++) {
         u64 maxW = 0;
+        u32 p = 0;
         for (u32 i = 0; i < P; i++) {
-            bool noL = (i == 0) || ps.b[i] == ps.e[i - 1];
-            bool noR = (i == P - 1) || ps.e[i] == ps.b[i + 1];
-            if (noL && noR)
-                continue;
-            u64 w = (u64)ps.emr[i].width() * st.weights[i];
-            if (w > maxW) {
-                maxW = w;
-                partToExtend = i;
-                if (noL)
-                    dir = DIR_FWD;
-                else if (noR)
-                    dir = DIR_BWD;
-                else
-                    dir = (ps.emr[i - 1].width() < ps.emr[i + 1].width()) ? DIR_BWD : DIR_FWD;
-            }
+            const u64 w = key[i];
+            p = (w > maxW) ? i : p;
+            maxW = (w > maxW) ? w : maxW;
         }
         if (maxW == 0) { // extendParts, :283-297
             for (u32 i = 0; i < P; i++) {
@@ -189,15 +191,23 @@ CLB_HD void partitionDynamic(const IndexView& ix, const DevStrategy& st, const u
             }
             return;
         }
-        u32 c;
-        if (dir == DIR_FWD) {
-            ps.e[partToExtend]++;
-            c = pat[ps.e[partToExtend] - 1];
-        } else {
-            ps.b[partToExtend]--;
-            c = pat[ps.b[partToExtend]];
-        }
-        addChar(ix, dir, partToExtend == P - 1, c, ps.emr[partToExtend], lc);
+        const u32 pb = ps.b[p], pe = ps.e[p];
+        const bool noL = (p == 0) || pb == ps.e[p - 1];
+        const bool noR = (p == P - 1) || pe == ps.b[p + 1];
+        // both neighbours exist when neither side is closed
+        const u32 wl = wd[p == 0 ? 0 : p - 1], wr = wd[p == P - 1 ? p : p + 1];
+        const int dir = noL ? DIR_FWD : (noR ? DIR_BWD : ((wl < wr) ? DIR_BWD : DIR_FWD));
+        const bool fwd = (dir == DIR_FWD);
+        const u32 c = pat[fwd ? pe : pb - 1];
+        ps.b[p] = fwd ? pb : pb - 1;
+        ps.e[p] = fwd ? pe + 1 : pe;
+        RangePair r = ps.emr[p];
+        addChar(ix, dir, p == P - 1, c, r, lc);
+        ps.emr[p] = r;
+        wd[p] = r.width();
+        key[p] = keyOf(p);
+        const u32 q = fwd ? (p == P - 1 ? p : p + 1) : (p == 0 ? p : p - 1);
+        key[q] = keyOf(q);
     }
 }
 
