@@ -26,8 +26,8 @@ namespace clb {
 // claims 32 tasks at a time from a global counter.
 // optional per-CTA shared memory of a functor: K::smemBytes(nThreads) and
 // K::bindShared(state, smem, tid, nThreads)
-template <class K> auto smemBytesOf(const K&, u32 nThreads, int) -> decltype(K::smemBytes(nThreads)) {
-    return K::smemBytes(nThreads);
+template <class K> auto smemBytesOf(const K& k, u32 nThreads, int) -> decltype(k.smemBytes(nThreads)) {
+    return k.smemBytes(nThreads);
 }
 template <class K> size_t smemBytesOf(const K&, u32, long) { return 0; }
 template <class K, class S>
@@ -69,6 +69,62 @@ __global__ void __launch_bounds__(128) clb_kernel(const K k, u32 nMax, const u32
     }
     k.end(st);
 }
+
+// Stepped functors (K::kStepped): a task is start(), some number of step()s,
+// finish().  Every lane owns one task at a time; lanes whose task is finished
+// claim the next one (one atomic per warp and refill round) while the other
+// lanes keep stepping, so the step loop runs with (almost) full warps even
+// when the tasks differ a lot in their number of steps.
+template <class K>
+__global__ void __launch_bounds__(128) clb_kernel_stepped(const K k, u32 nMax, const u32* __restrict__ nDev, u32* workCtr) {
+    u32 n = nMax;
+    if (nDev) {
+        u32 v = *nDev;
+        n = v < nMax ? v : nMax;
+    }
+    const u32 worker = blockIdx.x * blockDim.x + threadIdx.x;
+    const u32 lane = threadIdx.x & 31;
+    extern __shared__ __align__(16) u8 clb_smem[];
+    typename K::State st;
+    k.begin(st, worker);
+    bindSharedOf(k, st, clb_smem, 0);
+    bool have = false, done = false;
+    for (;;) {
+        const unsigned need = __ballot_sync(0xFFFFFFFFu, !have && !done);
+        if (need) {
+            const int leader = __ffs(need) - 1;
+            u32 base = 0;
+            if ((int)lane == leader)
+                base = atomicAdd(workCtr, (u32)__popc(need));
+            base = __shfl_sync(0xFFFFFFFFu, base, leader);
+            if (!have && !done) {
+                const u32 i = base + __popc(need & ((1u << lane) - 1u));
+                if (i < n) {
+                    k.start(st, i);
+                    have = true;
+                } else {
+                    done = true;
+                }
+            }
+        }
+        if (__all_sync(0xFFFFFFFFu, done))
+            break;
+        // a few steps per refill round: lanes that finish in between wait
+        bool fin = false;
+        if (have) {
+#pragma unroll 1
+            for (int q = 0; q < 4 && !fin; q++)
+                fin = k.step(st);
+        }
+        if (fin) {
+            k.finish(st);
+            have = false;
+        }
+    }
+    k.end(st);
+}
+template <class K> constexpr auto isStepped(int) -> decltype(K::kStepped) { return K::kStepped; }
+template <class K> constexpr bool isStepped(long) { return false; }
 
 // exclusive scan of n u32 values (out[n] = total) in three launches:
 // per-tile sums, scan of the tile sums by one block, per-tile scan + offset.
@@ -242,35 +298,40 @@ struct CudaBackend {
     }
     u32 workers(int kind) { return blocksFor(kind) * 128; }
     u32 laneStride() const { return 32; }
+    u32 fallbackWorkers() const { return 0; }
     template <class K> void launch(const K& k, u32 nMax, const u32* nDev, int kind) {
         if (nMax == 0)
             return;
+        void (*fn)(const K, u32, const u32*, u32*);
+        if constexpr (isStepped<K>(0))
+            fn = clb_kernel_stepped<K>;
+        else
+            fn = clb_kernel<K>;
         u32 blocks = blocksFor(kind);
         const size_t smem = smemBytesOf(k, 128u, 0);
         if (smem) {
-            // never more CTAs than can be resident: the slabs are sized for blocksFor(kind) workers
-            static int perSM = 0;
-            if (!perSM) {
-                if (smem > 48 * 1024)
-                    CLB_CUDA(cudaFuncSetAttribute(clb_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-                CLB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, clb_kernel<K>, 128, smem));
-                if (perSM < 1)
-                    throw BackendError("kernel does not fit on an SM");
-            }
+            // never more CTAs than can be resident
+            int perSM = 0;
+            if (smem > 48 * 1024)
+                CLB_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            CLB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, fn, 128, smem));
+            if (perSM < 1)
+                throw BackendError("kernel does not fit on an SM");
             if ((u32)perSM * (u32)numSMs < blocks)
                 blocks = (u32)perSM * (u32)numSMs;
         }
         u32* ctr = nullptr;
-        if (kind != WK_LIGHT) {
+        if (kind != WK_LIGHT || isStepped<K>(0)) {
             if (nextCtr >= N_CTRS)
                 throw BackendError("work counter pool exhausted");
             ctr = workCtrs + nextCtr++;
-        } else if (!nDev) {
+        }
+        if (kind == WK_LIGHT && !nDev) {
             u32 need = (nMax + 127) / 128;
             if (need < blocks)
                 blocks = need;
         }
-        clb_kernel<K><<<blocks, 128, smem, stream>>>(k, nMax, nDev, ctr);
+        fn<<<blocks, 128, smem, stream>>>(k, nMax, nDev, ctr);
         CLB_CUDA(cudaGetLastError());
         launches++;
     }

@@ -22,14 +22,34 @@ struct PrepKernel {
     CLB_HD void end(State&) const {}
 };
 
-// stage 1
+// stage 1.  Stepped functor: besides run() (the whole task, used by the host
+// emulation) it offers start / step / finish, which the CUDA launcher drives
+// with per-lane task refill (clb_kernel_stepped).
 struct PartitionKernel {
     IndexView ix;
     const DevStrategy* st;
     Batch B;
-    typedef WorkerCtr State;
-    CLB_HD void begin(State& s, u32) const { s.lc.clear(); }
-    CLB_HD void run(State& s, u32 t) const { partitionTask(ix, *st, B, t, s.lc); }
+    u32 P;       // parts (st->P, known to the host)
+    u8* slabs;   // scratch of the workers when there is no shared memory (host emulation), else null
+    static const bool kStepped = true;
+    struct State {
+        LocalCtr lc;
+        PartState ps;
+    };
+    CLB_HD size_t smemBytes(u32 nThreads) const { return PartScratch::bytesPerWorker(P) * nThreads; }
+    CLB_HD void bindShared(State& s, u8* smem, u32 tid, u32 nThreads) const {
+        s.ps.ps.w = (u32*)smem + tid;
+        s.ps.ps.stride = nThreads;
+    }
+    CLB_HD void begin(State& s, u32 worker) const {
+        s.lc.clear();
+        s.ps.ps.w = slabs ? (u32*)(slabs + (size_t)worker * PartScratch::bytesPerWorker(P)) : (u32*)0;
+        s.ps.ps.stride = 1;
+    }
+    CLB_HD void run(State& s, u32 t) const { partitionTask(ix, *st, B, t, s.ps, s.lc); }
+    CLB_HD void start(State& s, u32 t) const { partStart(ix, *st, B, t, s.ps, s.lc); }
+    CLB_HD bool step(State& s) const { return partStep(ix, *st, s.ps, s.lc); }
+    CLB_HD void finish(State& s) const { partFinish(ix, *st, B, s.ps, s.lc); }
     CLB_HD void end(State& s) const { s.lc.flush(B.counters, B.stats); }
 };
 

@@ -114,108 +114,150 @@ CLB_HD RangePair matchString(const IndexView& ix, int dir, bool uni, const u8* p
     return r;
 }
 
+// Working state of one partitioning task: per part begin, end, exact range
+// (4 words) and greedy key (2 words) = 8 words, element j of a worker at
+// w[j * stride].  On the GPU w points into shared memory (stride = threads per
+// CTA: conflict free, and no local-memory traffic through L2); the host
+// emulation uses a slab.
 struct PartScratch {
-    u32 b[MAXP], e[MAXP];
-    RangePair emr[MAXP];
+    u32* w;
+    u32 stride;
+    CLB_HD u32& at(u32 i, u32 f) const { return w[(size_t)(i * 8 + f) * stride]; }
+    CLB_HD u32& b(u32 i) const { return at(i, 0); }
+    CLB_HD u32& e(u32 i) const { return at(i, 1); }
+    CLB_HD RangePair emr(u32 i) const { return mkPair(at(i, 2), at(i, 3), at(i, 4), at(i, 5)); }
+    CLB_HD void setEmr(u32 i, const RangePair& r) const {
+        at(i, 2) = r.sa.b; at(i, 3) = r.sa.e; at(i, 4) = r.rev.b; at(i, 5) = r.rev.e;
+    }
+    CLB_HD u32 width(u32 i) const {
+        const u32 sb = at(i, 2), se = at(i, 3);
+        return se <= sb ? 0u : se - sb;
+    }
+    CLB_HD u64 key(u32 i) const { return (u64)at(i, 6) | ((u64)at(i, 7) << 32); }
+    CLB_HD void setKey(u32 i, u64 k) const { at(i, 6) = (u32)k; at(i, 7) = (u32)(k >> 32); }
+    static CLB_HD size_t bytesPerWorker(u32 P) { return (size_t)P * 8 * sizeof(u32); }
 };
 
-CLB_HD void calcExactRanges(const IndexView& ix, const u8* pat, u32 P, PartScratch& ps, LocalCtr& lc) {
+CLB_HD void calcExactRanges(const IndexView& ix, const u8* pat, u32 P, const PartScratch& ps, LocalCtr& lc) {
     const u32 ws = ix.K;
     for (u32 i = 0; i < P; ++i) {
-        u32 size = ps.e[i] <= ps.b[i] ? 0 : ps.e[i] - ps.b[i];
-        u32 start = ps.b[i] + ((size >= ws) ? ws : 0);
-        RangePair init = (size >= ws) ? lookUpKmer(ix, pat + ps.b[i]) : completeRange(ix);
-        ps.emr[i] = matchString(ix, DIR_FWD, false, pat, start, ps.e[i], DIR_FWD, init, lc);
+        u32 size = ps.e(i) <= ps.b(i) ? 0 : ps.e(i) - ps.b(i);
+        u32 start = ps.b(i) + ((size >= ws) ? ws : 0);
+        RangePair init = (size >= ws) ? lookUpKmer(ix, pat + ps.b(i)) : completeRange(ix);
+        ps.setEmr(i, matchString(ix, DIR_FWD, false, pat, start, ps.e(i), DIR_FWD, init, lc));
     }
-    u32 lb = ps.b[P - 1], le = ps.e[P - 1];
+    u32 lb = ps.b(P - 1), le = ps.e(P - 1);
     u32 size = le <= lb ? 0 : le - lb;
     u32 end = (size >= ws) ? le - ws : le;
     RangePair init = (size >= ws) ? lookUpKmer(ix, pat + end) : completeRange(ix);
-    ps.emr[P - 1] = matchString(ix, DIR_BWD, true, pat, lb, end, DIR_BWD, init, lc);
+    ps.setEmr(P - 1, matchString(ix, DIR_BWD, true, pat, lb, end, DIR_BWD, init, lc));
 }
 
-CLB_HD void partitionDynamic(const IndexView& ix, const DevStrategy& st, const u8* pat, u32 pSize, u32 P,
-                             PartScratch& ps, LocalCtr& lc) {
-    // seed(), searchstrategy.cpp:381-419
+// State of one (read,strand) partitioning task.  The dynamic strategy is a
+// resumable state machine (start / step / finish) so that the lanes of a warp
+// can each be at a different task: a sequence that does not occur in the index
+// (e.g. the reverse complement of a read from the forward strand) runs out of
+// extendable parts after ~20 of its ~100 steps, and its lane takes the next
+// task while the other lanes keep stepping.
+struct PartState {
+    PartScratch ps;
+    const u8* pat;
+    u32 t, pSize, j;
+    u32 stepping; // 1: greedy steps outstanding
+};
+
+// width x weight of part i while it can still grow, else 0
+CLB_HD u64 partKey(const DevStrategy& st, const PartScratch& ps, u32 P, u32 i) {
+    const bool noL = (i == 0) || ps.b(i) == ps.e(i - 1);
+    const bool noR = (i == P - 1) || ps.e(i) == ps.b(i + 1);
+    return (noL && noR) ? 0ull : (u64)ps.width(i) * st.weights[i];
+}
+
+// seed(), searchstrategy.cpp:381-419 (+ seedIfNoKmers :255-271)
+CLB_HD void dynSeed(const IndexView& ix, const DevStrategy& st, u32 P, PartState& S, LocalCtr& lc) {
+    const PartScratch& ps = S.ps;
+    const u8* pat = S.pat;
+    const u32 pSize = S.pSize;
     const bool useK = ((u64)P * ix.K < ((u64)pSize * 2) / 3) && pSize >= st.useKmerCutOff;
     const int wSize = useK ? (int)ix.K : 1;
-    ps.b[0] = 0;
+    ps.b(0) = 0;
     for (u32 i = 1; i + 1 < P; i++)
-        ps.b[i] = (u32)(int)dsub(dmul(st.seeds[i - 1], (double)pSize), (double)(wSize / 2));
+        ps.b(i) = (u32)(int)dsub(dmul(st.seeds[i - 1], (double)pSize), (double)(wSize / 2));
     for (u32 i = 0; i + 1 < P; i++)
-        ps.e[i] = ps.b[i] + wSize;
-    ps.b[P - 1] = pSize - wSize;
-    ps.e[P - 1] = pSize;
+        ps.e(i) = ps.b(i) + wSize;
+    ps.b(P - 1) = pSize - wSize;
+    ps.e(P - 1) = pSize;
     for (u32 i = 0; i < P; i++)
-        ps.emr[i] = useK ? lookUpKmer(ix, pat + ps.b[i]) : rangeOfSingleChar(ix, pat[ps.b[i]]);
+        ps.setEmr(i, useK ? lookUpKmer(ix, pat + ps.b(i)) : rangeOfSingleChar(ix, pat[ps.b(i)]));
     u32 matched = P * (u32)wSize;
     if (matched == 0) { // seedIfNoKmers, :255-271
         u32 size = (pSize >= 4 * P) ? 4 : 1;
         for (u32 i = 0; i + 1 < P; i++) {
-            ps.e[i] = tmin(ps.e[i] + size, pSize);
-            for (u32 j = ps.b[i]; j < ps.e[i]; j++) {
-                addChar(ix, DIR_FWD, false, pat[j], ps.emr[i], lc);
+            ps.e(i) = tmin(ps.e(i) + size, pSize);
+            RangePair r = ps.emr(i);
+            for (u32 j = ps.b(i); j < ps.e(i); j++) {
+                addChar(ix, DIR_FWD, false, pat[j], r, lc);
                 matched++;
             }
+            ps.setEmr(i, r);
         }
     }
-    // The greedy loop of partitionDynamic (:340-376).  key[i] = width x weight of
-    // part i while it can still grow (0 otherwise); only the extended part and
-    // the neighbour it grew towards change per step, so a step is one argmax over
-    // P cached keys, one single-character extension and two key updates.
-    u64 key[MAXP];
-    u32 wd[MAXP];
     for (u32 i = 0; i < P; i++)
-        wd[i] = ps.emr[i].width();
-    auto keyOf = [&](u32 i) -> u64 {
-        const bool noL = (i == 0) || ps.b[i] == ps.e[i - 1];
-        const bool noR = (i == P - 1) || ps.e[i] == ps.b[i + 1];
-        return (noL && noR) ? 0ull : (u64)wd[i] * st.weights[i];
-    };
-    for (u32 i = 0; i < P; i++)
-        key[i] = keyOf(i);
-    for (u32 j = matched; j < pSize; j++) {
-        u64 maxW = 0;
-        u32 p = 0;
-        for (u32 i = 0; i < P; i++) {
-            const u64 w = key[i];
-            p = (w > maxW) ? i : p;
-            maxW = (w > maxW) ? w : maxW;
-        }
-        if (maxW == 0) { // extendParts, :283-297
-            for (u32 i = 0; i < P; i++) {
-                if ((i != P - 1) && (ps.e[i] != ps.b[i + 1]))
-                    ps.e[i] = ps.b[i + 1];
-                if ((i != 0) && (ps.b[i] != ps.e[i - 1]))
-                    ps.b[i] = ps.e[i - 1];
-            }
-            return;
-        }
-        const u32 pb = ps.b[p], pe = ps.e[p];
-        const bool noL = (p == 0) || pb == ps.e[p - 1];
-        const bool noR = (p == P - 1) || pe == ps.b[p + 1];
-        // both neighbours exist when neither side is closed
-        const u32 wl = wd[p == 0 ? 0 : p - 1], wr = wd[p == P - 1 ? p : p + 1];
-        const int dir = noL ? DIR_FWD : (noR ? DIR_BWD : ((wl < wr) ? DIR_BWD : DIR_FWD));
-        const bool fwd = (dir == DIR_FWD);
-        const u32 c = pat[fwd ? pe : pb - 1];
-        ps.b[p] = fwd ? pb : pb - 1;
-        ps.e[p] = fwd ? pe + 1 : pe;
-        RangePair r = ps.emr[p];
-        addChar(ix, dir, p == P - 1, c, r, lc);
-        ps.emr[p] = r;
-        wd[p] = r.width();
-        key[p] = keyOf(p);
-        const u32 q = fwd ? (p == P - 1 ? p : p + 1) : (p == 0 ? p : p - 1);
-        key[q] = keyOf(q);
-    }
+        ps.setKey(i, partKey(st, ps, P, i));
+    S.j = matched;
 }
 
-// stage 1 task.  Emits the immediate-switch candidates (order slot 0) and the
-// search tasks of the selected scheme.
-CLB_HD void partitionTask(const IndexView& ix, const DevStrategy& st, const Batch& B, u32 t, LocalCtr& lc) {
-    const u8* pat = seqCodes(B, t);
-    const u32 pSize = seqLen(B, t);
+// One step of the greedy loop of partitionDynamic (:340-376): only the
+// extended part and the neighbour it grew towards change, so a step is one
+// argmax over P cached keys, one single-character extension and two key
+// updates.  Returns true when the partitioning is complete.
+CLB_HD bool dynStep(const IndexView& ix, const DevStrategy& st, u32 P, PartState& S, LocalCtr& lc) {
+    const PartScratch& ps = S.ps;
+    if (S.j >= S.pSize)
+        return true;
+    u64 maxW = 0;
+    u32 p = 0;
+    for (u32 i = 0; i < P; i++) {
+        const u64 w = ps.key(i);
+        p = (w > maxW) ? i : p;
+        maxW = (w > maxW) ? w : maxW;
+    }
+    if (maxW == 0) { // extendParts, :283-297
+        for (u32 i = 0; i < P; i++) {
+            if ((i != P - 1) && (ps.e(i) != ps.b(i + 1)))
+                ps.e(i) = ps.b(i + 1);
+            if ((i != 0) && (ps.b(i) != ps.e(i - 1)))
+                ps.b(i) = ps.e(i - 1);
+        }
+        return true;
+    }
+    const u32 pb = ps.b(p), pe = ps.e(p);
+    const bool noL = (p == 0) || pb == ps.e(p - 1);
+    const bool noR = (p == P - 1) || pe == ps.b(p + 1);
+    // both neighbours exist when neither side is closed
+    const u32 wl = ps.width(p == 0 ? 0 : p - 1), wr = ps.width(p == P - 1 ? p : p + 1);
+    const int dir = noL ? DIR_FWD : (noR ? DIR_BWD : ((wl < wr) ? DIR_BWD : DIR_FWD));
+    const bool fwd = (dir == DIR_FWD);
+    const u32 c = S.pat[fwd ? pe : pb - 1];
+    ps.b(p) = fwd ? pb : pb - 1;
+    ps.e(p) = fwd ? pe + 1 : pe;
+    RangePair r = ps.emr(p);
+    addChar(ix, dir, p == P - 1, c, r, lc);
+    ps.setEmr(p, r);
+    ps.setKey(p, partKey(st, ps, P, p));
+    const u32 q = fwd ? (p == P - 1 ? p : p + 1) : (p == 0 ? p : p - 1);
+    ps.setKey(q, partKey(st, ps, P, q));
+    S.j++;
+    return S.j >= S.pSize;
+}
+
+// stage 1 task, first half: everything up to the greedy steps.
+CLB_HD void partStart(const IndexView& ix, const DevStrategy& st, const Batch& B, u32 t, PartState& S, LocalCtr& lc) {
+    S.t = t;
+    S.pat = seqCodes(B, t);
+    S.pSize = seqLen(B, t);
+    S.stepping = 0;
+    const u32 pSize = S.pSize;
     const u32 P = st.P;
     PartInfo& pi = B.parts[t];
     pi.len = (u16)pSize;
@@ -225,39 +267,59 @@ CLB_HD void partitionTask(const IndexView& ix, const DevStrategy& st, const Batc
         atomOr(B.err, ERR_SHORT_READ);
         return;
     }
-    PartScratch ps;
-    if (B.partStrategy == PART_DYNAMIC) {
-        partitionDynamic(ix, st, pat, pSize, P, ps, lc);
-    } else {
-        if (B.partStrategy == PART_UNIFORM) { // :194-209
-            for (u32 i = 0; i < P; i++) {
-                ps.b[i] = (u32)dmul(ddiv(dmul((double)(int)i, 1.0), (double)P), (double)pSize);
-                ps.e[i] = (u32)dmul(ddiv(dmul((double)(int)(i + 1), 1.0), (double)P), (double)pSize);
-            }
-            ps.e[P - 1] = pSize;
-        } else { // :212-238
-            ps.b[0] = 0;
-            ps.e[0] = (u32)dmul(st.begins[0], (double)(int)pSize);
-            for (u32 i = 0; i + 2 < P; i++) {
-                ps.b[i + 1] = (u32)dmul(st.begins[i], (double)(int)pSize);
-                ps.e[i + 1] = (u32)dmul(st.begins[i + 1], (double)(int)pSize);
-            }
-            ps.b[P - 1] = (u32)dmul(st.begins[P - 2], (double)(int)pSize);
-            ps.e[P - 1] = pSize;
-        }
-        calcExactRanges(ix, pat, P, ps, lc);
-    }
-    for (u32 i = 0; i < P; i++) {
-        pi.begin[i] = (u16)ps.b[i];
-        pi.end[i] = (u16)ps.e[i];
-        pi.emr[i] = ps.emr[i];
-    }
     pi.valid = 1;
+    const PartScratch& ps = S.ps;
+    if (B.partStrategy == PART_DYNAMIC) {
+        dynSeed(ix, st, P, S, lc);
+        S.stepping = 1;
+        return;
+    }
+    if (B.partStrategy == PART_UNIFORM) { // :194-209
+        for (u32 i = 0; i < P; i++) {
+            ps.b(i) = (u32)dmul(ddiv(dmul((double)(int)i, 1.0), (double)P), (double)pSize);
+            ps.e(i) = (u32)dmul(ddiv(dmul((double)(int)(i + 1), 1.0), (double)P), (double)pSize);
+        }
+        ps.e(P - 1) = pSize;
+    } else { // :212-238
+        ps.b(0) = 0;
+        ps.e(0) = (u32)dmul(st.begins[0], (double)(int)pSize);
+        for (u32 i = 0; i + 2 < P; i++) {
+            ps.b(i + 1) = (u32)dmul(st.begins[i], (double)(int)pSize);
+            ps.e(i + 1) = (u32)dmul(st.begins[i + 1], (double)(int)pSize);
+        }
+        ps.b(P - 1) = (u32)dmul(st.begins[P - 2], (double)(int)pSize);
+        ps.e(P - 1) = pSize;
+    }
+    calcExactRanges(ix, S.pat, P, ps, lc);
+}
+// true when the task has no (more) greedy steps to do
+CLB_HD bool partStep(const IndexView& ix, const DevStrategy& st, PartState& S, LocalCtr& lc) {
+    if (!S.stepping)
+        return true;
+    if (dynStep(ix, st, st.P, S, lc))
+        S.stepping = 0;
+    return !S.stepping;
+}
+
+// stage 1 task, second half.  Emits the immediate-switch candidates (order
+// slot 0) and the search tasks of the selected scheme.
+CLB_HD void partFinish(const IndexView& ix, const DevStrategy& st, const Batch& B, PartState& S, LocalCtr& lc) {
+    const u32 t = S.t;
+    const u32 P = st.P;
+    PartInfo& pi = B.parts[t];
+    if (!pi.valid)
+        return;
+    const PartScratch& ps = S.ps;
+    for (u32 i = 0; i < P; i++) {
+        pi.begin[i] = (u16)ps.b(i);
+        pi.end[i] = (u16)ps.e(i);
+        pi.emr[i] = ps.emr(i);
+    }
     // A) immediate switch, searchstrategy.cpp:464-476 -> fmindex.cpp:245-265 /
     //    :344-356
     u32 emit = 0;
     for (u32 i = 0; i < P; i++) {
-        u32 width = ps.emr[i].width();
+        u32 width = ps.width(i);
         if (width != 0 && width <= ix.switchPoint) {
             Cand c;
             c.t = t;
@@ -267,16 +329,16 @@ CLB_HD void partitionTask(const IndexView& ix, const DevStrategy& st, const Batc
             c.add = 0;
             if (B.metric == METRIC_EDIT) {
                 lc.c[IMMEDIATE_SWITCH]++;
-                u32 startDiff = (ps.b[i] == 0) ? 0 : ps.b[i] + B.k;
+                u32 startDiff = (ps.b(i) == 0) ? 0 : ps.b(i) + B.k;
                 c.sub = startDiff;
-                c.fixedStart = (ps.b[i] == 0);
+                c.fixedStart = (ps.b(i) == 0);
             } else {
-                c.sub = ps.b[i];
+                c.sub = ps.b(i);
                 c.fixedStart = 1;
             }
             u32 at = B.cands.reserve(width, B.err, ERR_CAND_OVERFLOW);
             for (u32 row = 0; row < width; row++) {
-                c.row = ps.emr[i].sa.b + row;
+                c.row = ps.at(i, 2) + row;
                 c.order = emit++;
                 if (at != 0xFFFFFFFFu)
                     B.cands.data[at + row] = c;
@@ -288,11 +350,11 @@ CLB_HD void partitionTask(const IndexView& ix, const DevStrategy& st, const Batc
     if (st.nSchemes > 1) {
         u32 total = 0;
         for (u32 i = 0; i < P; i++)
-            total += ps.emr[i].width();
+            total += ps.width(i);
         if (total > P) {
-            u32 minValue = ps.emr[st.sc[0].criticalPart].width();
+            u32 minValue = ps.width(st.sc[0].criticalPart);
             for (u32 i = 1; i < st.nSchemes; i++) {
-                u32 w = ps.emr[st.sc[i].criticalPart].width();
+                u32 w = ps.width(st.sc[i].criticalPart);
                 if (w < minValue) {
                     minValue = w;
                     sel = i;
@@ -305,7 +367,7 @@ CLB_HD void partitionTask(const IndexView& ix, const DevStrategy& st, const Batc
     const DevScheme& sc = st.sc[sel];
     for (u32 s = 0; s < sc.nSearches; s++) {
         const DevSearch& se = sc.s[s];
-        bool start = se.U[0] > 0 || ps.emr[se.order[0]].width() > ix.switchPoint;
+        bool start = se.U[0] > 0 || ps.width(se.order[0]) > ix.switchPoint;
         if (start) {
             SearchTask task;
             task.t = t;
@@ -313,6 +375,14 @@ CLB_HD void partitionTask(const IndexView& ix, const DevStrategy& st, const Batc
             B.tasks.push(task, B.err, ERR_TASK_OVERFLOW);
         }
     }
+}
+
+// the whole task in one go (host emulation, tests)
+CLB_HD void partitionTask(const IndexView& ix, const DevStrategy& st, const Batch& B, u32 t, PartState& S, LocalCtr& lc) {
+    partStart(ix, st, B, t, S, lc);
+    while (!partStep(ix, st, S, lc)) {
+    }
+    partFinish(ix, st, B, S, lc);
 }
 
 } // namespace clb

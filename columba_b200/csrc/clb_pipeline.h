@@ -6,6 +6,7 @@
 //   void* alloc(size_t), void free(void*), void zero(void*, size_t),
 //   void h2d(void* dst, const void* src, size_t), void d2h(void* dst, const void* src, size_t),
 //   void sync(), u32 workers(int kind) (number of workers for scratch slabs),
+//   u32 fallbackWorkers() (workers that need slabs instead of shared memory; 0 on the GPU),
 //   template<class K> void launch(const K&, u32 nMax, const u32* nDev, int kind),
 //   void exclusiveScan(const u32* in, u32* out, u32 n)   (out[n] = total),
 //   void mark(int stage) (timing hook)
@@ -68,7 +69,7 @@ template <typename BE> struct Pipeline {
     BE& be;
     IndexView ix;
     DevBuf<BE> bReads, bOff, bCodes, bPlanes, bParts, bTasks, bCands, bFm, bTx, bTxCig, bOut, bOutCig, bPerRead, bIdx,
-        bMisc, bSlabSearch, bSlabVerify, bSlabVerifyWide, bSlabFilter, bStrategy;
+        bMisc, bSlabPart, bSlabSearch, bSlabVerify, bSlabVerifyWide, bSlabFilter, bStrategy;
     // list capacities (per read multipliers, grown after an overflow)
     double candPerRead = 24, fmPerRead = 4, txPerRead = 24, outPerRead = 8;
     u32 minCap = 1 << 16;
@@ -77,7 +78,7 @@ template <typename BE> struct Pipeline {
     Pipeline(BE& b) : be(b) {}
     ~Pipeline() {
         DevBuf<BE>* all[] = {&bReads, &bOff, &bCodes, &bPlanes, &bParts, &bTasks, &bCands, &bFm, &bTx, &bTxCig, &bOut,
-                             &bOutCig, &bPerRead, &bIdx, &bMisc, &bSlabSearch, &bSlabVerify, &bSlabVerifyWide, &bSlabFilter,
+                             &bOutCig, &bPerRead, &bIdx, &bMisc, &bSlabPart, &bSlabSearch, &bSlabVerify, &bSlabVerifyWide, &bSlabFilter,
                              &bStrategy};
         for (auto* d : all)
             d->release(be);
@@ -190,7 +191,11 @@ template <typename BE> struct Pipeline {
             PrepKernel k0{B};
             be.launch(k0, R * (B.nw - 1), nullptr, WK_LIGHT);
             be.mark(STG_PREP);
-            PartitionKernel k1{ix, dst, B};
+            // shared memory on the GPU; a slab for backends without it
+            const u32 fw = be.fallbackWorkers();
+            if (fw)
+                bSlabPart.ensure(be, PartScratch::bytesPerWorker(P) * fw);
+            PartitionKernel k1{ix, dst, B, P, fw ? (u8*)bSlabPart.p : (u8*)0};
             be.launch(k1, T, nullptr, WK_LIGHT);
             be.mark(STG_PARTITION);
         }

@@ -27,6 +27,7 @@ struct HostEmuBackend {
     void sync() {}
     u32 workers(int) { return 1; }
     u32 laneStride() const { return 1; }
+    u32 fallbackWorkers() const { return 1; }
     template <class K> void launch(const K& k, u32 nMax, const u32* nDev, int) {
         u32 n = nDev ? (*nDev < nMax ? *nDev : nMax) : nMax;
         typename K::State st;
