@@ -36,6 +36,14 @@ __device__ __forceinline__ auto bindSharedOf(const K& k, S& st, u8* smem, int) -
 }
 template <class K, class S> __device__ __forceinline__ void bindSharedOf(const K&, S&, u8*, long) {}
 
+// functors that want to know which lanes run a task next to them take the
+// lane mask as a third argument of run()
+template <class K, class S>
+__device__ __forceinline__ auto runOf(const K& k, S& st, u32 i, unsigned act, int) -> decltype(k.run(st, i, act)) {
+    k.run(st, i, act);
+}
+template <class K, class S> __device__ __forceinline__ void runOf(const K& k, S& st, u32 i, unsigned, long) { k.run(st, i); }
+
 template <class K>
 __global__ void __launch_bounds__(128) clb_kernel(const K k, u32 nMax, const u32* __restrict__ nDev, u32* workCtr) {
     extern __shared__ __align__(16) u8 clb_smem[];
@@ -62,8 +70,9 @@ __global__ void __launch_bounds__(128) clb_kernel(const K k, u32 nMax, const u32
             if (base >= n)
                 break;
             u32 i = base + lane;
+            const unsigned act = __ballot_sync(0xFFFFFFFFu, i < n);
             if (i < n)
-                k.run(st, i);
+                runOf(k, st, i, act, 0);
             __syncwarp();
         }
     }

@@ -121,6 +121,7 @@ struct Batch {
     // lists
     DevList<SearchTask> tasks;
     DevList<Cand> cands;
+    DevList<u32> extra;    // candidates with more than one cluster centre (second verification pass)
     DevList<FMOccRec> fmOccs;
     DevList<TextOccRec> textOccs;
     u16* textCig;          // textOccs.cap x cigW

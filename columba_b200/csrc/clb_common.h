@@ -64,6 +64,32 @@ CLB_HD void atomOr(u32* p, u32 v) {
 #endif
 }
 
+// warp-level votes over the lanes in `mask` (the lanes that run a task side
+// by side); the host emulation runs one task at a time
+CLB_HD unsigned warpBallot(unsigned mask, bool p) {
+#if defined(__CUDA_ARCH__)
+    return __ballot_sync(mask, p);
+#else
+    (void)mask;
+    return p ? 1u : 0u;
+#endif
+}
+CLB_HD bool warpAny(unsigned mask, bool p) {
+#if defined(__CUDA_ARCH__)
+    return __any_sync(mask, p) != 0;
+#else
+    (void)mask;
+    return p;
+#endif
+}
+CLB_HD void warpSync(unsigned mask) {
+#if defined(__CUDA_ARCH__)
+    __syncwarp(mask);
+#else
+    (void)mask;
+#endif
+}
+
 // IEEE double ops without FMA contraction (partition boundaries must truncate
 // exactly as the reference's x86-64 code does: searchstrategy.cpp:194-238,396)
 CLB_HD double dmul(double a, double b) {

@@ -97,6 +97,7 @@ struct VerifyKernel {
     u32 laneStride;   // 32 on the GPU (the lanes of a warp interleave), 1 in the host emulation
     u8* wideSlabs;    // Row<u128>[rowsCap] per worker, only when 128-bit matrices can occur
     size_t wideBytes;
+    u32 pass;         // 0: all candidates, first centre; 1: the `extra` list, remaining centres
     struct State {
         LocalCtr lc;
         VerifyScratch vs;
@@ -127,11 +128,21 @@ struct VerifyKernel {
         s.vs.bs.ringStride = laneStride;
         s.vs.rows = wideSlabs ? (void*)(wideSlabs + (size_t)worker * wideBytes) : (void*)0;
         s.vs.rowsCap = rowsCap;
+        s.vs.warpMask = 1u;
+    }
+    // act: the lanes of the warp that run a task in this round
+    CLB_HD void run(State& s, u32 i, unsigned act) const {
+        s.vs.warpMask = act;
+        run(s, i);
     }
     CLB_HD void run(State& s, u32 i) const {
+        if (pass) {
+            verifyEditTask(ix, B, B.extra.data[i], s.vs, s.lc, 1);
+            return;
+        }
         s.lc.s[ST_CANDIDATES]++;
         if (B.metric == METRIC_EDIT)
-            verifyEditTask(ix, B, i, s.vs, s.lc);
+            verifyEditTask(ix, B, i, s.vs, s.lc, 0);
         else
             verifyHammingTask(ix, B, i, s.lc);
     }

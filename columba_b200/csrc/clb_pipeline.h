@@ -68,7 +68,7 @@ struct MapResult {
 template <typename BE> struct Pipeline {
     BE& be;
     IndexView ix;
-    DevBuf<BE> bReads, bOff, bCodes, bPlanes, bParts, bTasks, bCands, bFm, bTx, bTxCig, bOut, bOutCig, bPerRead, bIdx,
+    DevBuf<BE> bReads, bOff, bCodes, bPlanes, bParts, bTasks, bCands, bExtra, bFm, bTx, bTxCig, bOut, bOutCig, bPerRead, bIdx,
         bMisc, bSlabPart, bSlabSearch, bSlabVerify, bSlabVerifyWide, bSlabFilter, bStrategy;
     // list capacities (per read multipliers, grown after an overflow)
     double candPerRead = 24, fmPerRead = 4, txPerRead = 24, outPerRead = 8;
@@ -77,7 +77,7 @@ template <typename BE> struct Pipeline {
 
     Pipeline(BE& b) : be(b) {}
     ~Pipeline() {
-        DevBuf<BE>* all[] = {&bReads, &bOff, &bCodes, &bPlanes, &bParts, &bTasks, &bCands, &bFm, &bTx, &bTxCig, &bOut,
+        DevBuf<BE>* all[] = {&bReads, &bOff, &bCodes, &bPlanes, &bParts, &bTasks, &bCands, &bExtra, &bFm, &bTx, &bTxCig, &bOut,
                              &bOutCig, &bPerRead, &bIdx, &bMisc, &bSlabPart, &bSlabSearch, &bSlabVerify, &bSlabVerifyWide, &bSlabFilter,
                              &bStrategy};
         for (auto* d : all)
@@ -89,7 +89,7 @@ template <typename BE> struct Pipeline {
         u64 counters[N_COUNTERS];
         u64 stats[N_STATS];
         u32 err;
-        u32 nTasks, nCands, nFm, nTx, nOut;
+        u32 nTasks, nCands, nFm, nTx, nOut, nExtra;
         u32 nT, nR; // 2R and R as device-side task counts
     };
 
@@ -149,6 +149,8 @@ template <typename BE> struct Pipeline {
                   capOut = capOf(outPerRead);
         bTasks.ensure(be, (size_t)capTasks * sizeof(SearchTask));
         bCands.ensure(be, (size_t)capCands * sizeof(Cand));
+        const u32 capExtra = capCands / 4 + 1024;
+        bExtra.ensure(be, (size_t)capExtra * sizeof(u32));
         bFm.ensure(be, (size_t)capFm * sizeof(FMOccRec));
         bTx.ensure(be, (size_t)capTx * sizeof(TextOccRec));
         bTxCig.ensure(be, (size_t)capTx * B.cigW * 2);
@@ -164,6 +166,7 @@ template <typename BE> struct Pipeline {
         be.h2d(bMisc.p, &hm, sizeof(hm));
         B.tasks.data = (SearchTask*)bTasks.p; B.tasks.count = &M->nTasks; B.tasks.cap = capTasks;
         B.cands.data = (Cand*)bCands.p; B.cands.count = &M->nCands; B.cands.cap = capCands;
+        B.extra.data = (u32*)bExtra.p; B.extra.count = &M->nExtra; B.extra.cap = capExtra;
         B.fmOccs.data = (FMOccRec*)bFm.p; B.fmOccs.count = &M->nFm; B.fmOccs.cap = capFm;
         B.textOccs.data = (TextOccRec*)bTx.p; B.textOccs.count = &M->nTx; B.textOccs.cap = capTx;
         B.textCig = (u16*)bTxCig.p;
@@ -228,8 +231,13 @@ template <typename BE> struct Pipeline {
             const size_t wb = (size_t)vRows * sizeof(Row<u128>);
             if (wide)
                 bSlabVerifyWide.ensure(be, wb * nw);
-            VerifyKernel k3{ix, B, (u8*)bSlabVerify.p, gb, vRows, ls, wide ? (u8*)bSlabVerifyWide.p : (u8*)0, wb};
+            VerifyKernel k3{ix, B, (u8*)bSlabVerify.p, gb, vRows, ls, wide ? (u8*)bSlabVerifyWide.p : (u8*)0, wb, 0};
             be.launch(k3, capCands, &M->nCands, WK_VERIFY);
+            if (opt.metric == METRIC_EDIT) { // remaining centres of the candidates that have several
+                VerifyKernel k3x = k3;
+                k3x.pass = 1;
+                be.launch(k3x, capExtra, &M->nExtra, WK_VERIFY);
+            }
             be.mark(STG_VERIFY);
         }
         // ---- stages 4-6

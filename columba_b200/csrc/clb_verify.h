@@ -121,13 +121,14 @@ struct VerifyScratch {
     BandStore bs; // fast path
     u16* ops;     // cigW entries
     u32 rowsCap;
+    unsigned warpMask; // lanes of the warp that run a task in this round (1 on the host)
 };
 
 struct CandSink {
     const Batch& B;
     const Cand& c;
     u32 sub;
-    CLB_HD CandSink(const Batch& B_, const Cand& c_) : B(B_), c(c_), sub(0) {}
+    CLB_HD CandSink(const Batch& B_, const Cand& c_, u32 first) : B(B_), c(c_), sub(first) {}
     CLB_HD void operator()(const VerifyHit& h, const u16* ops) {
         TextOccRec r;
         r.t = c.t;
@@ -167,10 +168,14 @@ CLB_HD u64 bandPack(u64 HP, u64 X, u32 sh) { return (u64)(u32)(HP >> sh) | ((u64
 // word at a time, the final-column distances are kept in a small local array
 // and the traceback information lives in the BandStore (see there).  Same
 // results as verifyWindow<u64> (bitparallelmatrix.h:352-415, :591-614, :531-586).
+// `wm` = the lanes of the warp that call this function together: they are
+// brought back together after the forward pass (their row counts differ:
+// fixed-start and free-start candidates, aborted candidates) and walk the
+// traceback phase in lock step.
 template <typename Sink>
 CLB_HD bool verifyWindowFast(const IndexView& ix, const Batch& B, u32 t, const BandStore& bs, u32 start, u32 end,
                              u32 nZeros, u32 maxED, u32 minED, u16* ops, u32 opsCap, LocalCtr& lc, bool& considered,
-                             Sink& sink) {
+                             Sink& sink, unsigned wm, u32 firstCentre, u32 maxCentres, u32& totalCentres) {
     typedef BPC<u64> K;
     const PartSeq ps = fullSeq(B, t);
     const u32 n = ps.len + 1;
@@ -179,13 +184,13 @@ CLB_HD bool verifyWindowFast(const IndexView& ix, const Batch& B, u32 t, const B
     const u32 sofc = Wh + Wv + 1;
     const u32 size = end <= start ? 0u : end - start;
     considered = true;
+    bool run = true;
     if (!(size >= m - sofc)) {
         considered = false;
-        return false;
-    }
-    if (size / K::BLOCK + 1 > bs.cpCap) {
+        run = false;
+    } else if (size / K::BLOCK + 1 > bs.cpCap) {
         atomOr(B.err, ERR_ROWS_OVERFLOW);
-        return false;
+        run = false;
     }
     const u32 firstRow = (m - 1) - sofc, col = n - 1;
     const u32 sh0 = K::DIAG_R0 - Wv; // band of row i = bits [i%32 + sh0, i%32 + sh0 + Wv + Wh]
@@ -198,9 +203,6 @@ CLB_HD bool verifyWindowFast(const IndexView& ix, const Batch& B, u32 t, const B
     }
     u64 RAC = 1ull << (K::DIAG_R0 + Wh);
     u32 score = 0;
-    bs.ring[0] = bandPack(HP, 0, sh0);
-    bs.cp[0] = HP;
-    bs.cp[bs.cpStride] = HN;
     // distance in the final column of the row held in registers
     auto edAtCol = [&](u32 i) -> u32 {
         const u32 bit = (i % K::BLOCK) + K::DIAG_R0;
@@ -210,181 +212,219 @@ CLB_HD bool verifyWindowFast(const IndexView& ix, const Batch& B, u32 t, const B
         int neg = popc64(HN & mask), pos = popc64(HP & mask);
         return score + ((i > col) ? (u32)(neg - pos) : (u32)(pos - neg));
     };
-    if (firstRow == 0)
-        eds[0] = (u8)edAtCol(0);
-    u64 Mc[4];
-    for (u32 c = 0; c < 4; c++)
-        Mc[c] = matchVec<u64>(ps, 0, c);
-    u32 tw = ix.text[start >> 4];
-    u32 i;
-    bool ok = true;
-    for (i = 1; i <= size; ++i) {
-        const u32 p = start + i - 1;
-        if ((p & 15) == 0)
-            tw = ix.text[p >> 4];
-        const u32 Y = (tw >> ((p & 15) * 2)) & 3u;
-        const u32 l = i % K::BLOCK;
-        RAC <<= 1;
-        if (l == 0) {
-            HP >>= K::BLOCK;
-            HN >>= K::BLOCK;
-            RAC >>= K::BLOCK;
-            const u32 b = i / K::BLOCK;
-            for (u32 c = 0; c < 4; c++)
-                Mc[c] = matchVec<u64>(ps, b, c);
-            bs.cp[(size_t)(2 * b) * bs.cpStride] = HP;
-            bs.cp[(size_t)(2 * b + 1) * bs.cpStride] = HN;
-        }
-        const u64 M = Mc[Y];
-        const u64 D0 = bandRow(HP, HN, M);
-        const u32 diagBit = l + K::DIAG_R0;
-        score += (D0 >> diagBit) & 1ull ? 0u : 1u;
-        if (!(D0 & RAC)) {
-            u32 val = 1u;
-            while (val > 0) {
-                if (HP & RAC)
-                    val--;
-                if (HN & RAC)
-                    val++;
-                if (RAC == (1ull << (diagBit - Wv))) {
-                    ok = false;
-                    break;
-                }
-                RAC >>= 1;
+    u32 i = 1;
+    if (run) {
+        bs.ring[0] = bandPack(HP, 0, sh0);
+        bs.cp[0] = HP;
+        bs.cp[bs.cpStride] = HN;
+        if (firstRow == 0)
+            eds[0] = (u8)edAtCol(0);
+        u64 Mc[4];
+        for (u32 c = 0; c < 4; c++)
+            Mc[c] = matchVec<u64>(ps, 0, c);
+        u32 tw = ix.text[start >> 4];
+        bool ok = true;
+        for (i = 1; i <= size; ++i) {
+            const u32 p = start + i - 1;
+            if ((p & 15) == 0)
+                tw = ix.text[p >> 4];
+            const u32 Y = (tw >> ((p & 15) * 2)) & 3u;
+            const u32 l = i % K::BLOCK;
+            RAC <<= 1;
+            if (l == 0) {
+                HP >>= K::BLOCK;
+                HN >>= K::BLOCK;
+                RAC >>= K::BLOCK;
+                const u32 b = i / K::BLOCK;
+                for (u32 c = 0; c < 4; c++)
+                    Mc[c] = matchVec<u64>(ps, b, c);
+                bs.cp[(size_t)(2 * b) * bs.cpStride] = HP;
+                bs.cp[(size_t)(2 * b + 1) * bs.cpStride] = HN;
             }
+            const u64 M = Mc[Y];
+            const u64 D0 = bandRow(HP, HN, M);
+            const u32 diagBit = l + K::DIAG_R0;
+            score += (D0 >> diagBit) & 1ull ? 0u : 1u;
+            if (!(D0 & RAC)) {
+                u32 val = 1u;
+                while (val > 0) {
+                    if (HP & RAC)
+                        val--;
+                    if (HN & RAC)
+                        val++;
+                    if (RAC == (1ull << (diagBit - Wv))) {
+                        ok = false;
+                        break;
+                    }
+                    RAC >>= 1;
+                }
+            }
+            if (!ok)
+                break;
+            bs.ring[(size_t)l * bs.ringStride] = bandPack(HP, M | ~D0, l + sh0);
+            if (i >= firstRow)
+                eds[i - firstRow] = (u8)edAtCol(i);
         }
-        if (!ok)
-            break;
-        bs.ring[(size_t)l * bs.ringStride] = bandPack(HP, M | ~D0, l + sh0);
-        if (i >= firstRow)
-            eds[i - firstRow] = (u8)edAtCol(i);
+        if (firstCentre == 0)
+            lc.s[ST_VERIFY_ROWS] += (i <= size) ? i : size;
     }
-    lc.s[ST_VERIFY_ROWS] += (i <= size) ? i : size;
     const u32 lastRow = i - 1; // number of rows computed successfully
-    if (lastRow <= size - sofc) // unsigned, as in the reference
-        return false;
     // cluster centres first (findClusterCenters, bitparallelmatrix.h:591-614), then
-    // one traceback per centre: keeping the two loops apart lets the lanes of a
-    // warp run their tracebacks side by side
+    // one traceback per centre
     u8 centres[3 * K::MAX_ED + 4];
     u32 nCentres = 0;
-    for (u32 r = lastRow; r > firstRow; r--) {
-        const u32 ED = eds[r - firstRow];
-        if (ED > maxED || ED < minED)
-            continue;
-        const bool above = ED <= eds[r - 1 - firstRow];
-        const bool below = (r == lastRow) || ED <= eds[r + 1 - firstRow];
-        if (above && below)
-            centres[nCentres++] = (u8)(r - firstRow);
+    if (run && !(lastRow <= size - sofc)) { // unsigned compare, as in the reference
+        for (u32 r = lastRow; r > firstRow; r--) {
+            const u32 ED = eds[r - firstRow];
+            if (ED > maxED || ED < minED)
+                continue;
+            const bool above = ED <= eds[r - 1 - firstRow];
+            const bool below = (r == lastRow) || ED <= eds[r + 1 - firstRow];
+            if (above && below)
+                centres[nCentres++] = (u8)(r - firstRow);
+        }
     }
+    // this pass traces centres [firstCentre, firstCentre + maxCentres): the lanes
+    // of a warp almost always have exactly one, and a lane with more would keep
+    // the whole warp waiting for its extra rounds
+    totalCentres = nCentres;
+    const u32 endCentre = tmin(nCentres, firstCentre + maxCentres);
+    warpSync(wm);
     u32 ringBlock = lastRow / K::BLOCK; // the block whose rows the ring holds
-    for (u32 ci = 0; ci < nCentres; ci++) {
-        const u32 r = firstRow + centres[ci];
-        const u32 ED = eds[r - firstRow];
-        // traceBack from (r, n-1), bitparallelmatrix.h:531-586 (precedence I, diagonal, D)
-        u32 ti = r, tj = n - 1, nops = 0, runOp = 4, runLen = 0;
-        bool over = false, bad = false;
-        while (tj > 0 && !bad) {
-            const u32 cb = ti / K::BLOCK;
-            if (cb != ringBlock) {
-                // rows of block cb again, from its checkpoint
-                u64 hp = bs.cp[(size_t)(2 * cb) * bs.cpStride], hn = bs.cp[(size_t)(2 * cb + 1) * bs.cpStride];
-                u64 Mr[4];
-                for (u32 c = 0; c < 4; c++)
-                    Mr[c] = matchVec<u64>(ps, cb, c);
-                u32 i0 = cb * K::BLOCK;
-                if (cb == 0) {
-                    bs.ring[0] = bandPack(hp, 0, sh0);
-                    i0 = 1;
-                }
-                const u32 i1 = tmin(cb * K::BLOCK + K::BLOCK - 1, lastRow);
-                u32 w = ix.text[(start + i0 - 1) >> 4];
-                for (u32 q = i0; q <= i1; q++) {
-                    const u32 p = start + q - 1;
-                    if ((p & 15) == 0)
-                        w = ix.text[p >> 4];
-                    const u64 M = Mr[(w >> ((p & 15) * 2)) & 3u];
-                    const u64 D0 = bandRow(hp, hn, M);
-                    const u32 l = q % K::BLOCK;
-                    bs.ring[(size_t)l * bs.ringStride] = bandPack(hp, M | ~D0, l + sh0);
-                }
-                ringBlock = cb;
+    // traceBack from (r, n-1), bitparallelmatrix.h:531-586 (precedence I, diagonal,
+    // D), one 32-row block per round of the warp
+    u32 ci = firstCentre, r = 0, ti = 0, tj = 0, nops = 0, runOp = 4, runLen = 0;
+    bool started = false, over = false, bad = false;
+    for (;;) {
+        const bool active = ci < endCentre;
+        if (!warpAny(wm, active))
+            break;
+        if (!active)
+            continue;
+        if (!started) {
+            r = firstRow + centres[ci];
+            ti = r;
+            tj = n - 1;
+            nops = 0;
+            runOp = 4;
+            runLen = 0;
+            over = false;
+            bad = false;
+            started = true;
+        }
+        const u32 cb = ti / K::BLOCK;
+        if (cb != ringBlock) {
+            // rows of block cb again, from its checkpoint
+            u64 hp = bs.cp[(size_t)(2 * cb) * bs.cpStride], hn = bs.cp[(size_t)(2 * cb + 1) * bs.cpStride];
+            u64 Mr[4];
+            for (u32 c = 0; c < 4; c++)
+                Mr[c] = matchVec<u64>(ps, cb, c);
+            u32 i0 = cb * K::BLOCK;
+            if (cb == 0) {
+                bs.ring[0] = bandPack(hp, 0, sh0);
+                i0 = 1;
             }
-            do {
-                const u64 w = bs.ring[(size_t)(ti % K::BLOCK) * bs.ringStride];
-                const u32 bidx = tj + Wv - ti; // cell (ti, tj) within the band of row ti
-                if (bidx > Wv + Wh) {
-                    bad = true;
-                    break;
-                }
-                const u32 isI = ((u32)w >> bidx) & 1u;
-                const u32 isM = (isI ^ 1u) & ((u32)(w >> 32) >> bidx) & 1u;
-                const u32 op = isI ? (u32)CIG_I : (isM ? (u32)CIG_M : (u32)CIG_D);
-                tj -= (isI | isM);
-                ti -= (isI ^ 1u);
-                if (op == runOp) {
-                    runLen++;
-                } else {
-                    if (runLen) { // the run in registers is complete: one store per run
-                        if (nops < opsCap)
-                            ops[nops++] = (u16)((runLen << 2) | runOp);
-                        else
-                            over = true;
-                    }
-                    runOp = op;
-                    runLen = 1;
-                }
-            } while (tj > 0 && ti / K::BLOCK == cb);
+            const u32 i1 = tmin(cb * K::BLOCK + K::BLOCK - 1, lastRow);
+            u32 w = ix.text[(start + i0 - 1) >> 4];
+            for (u32 q = i0; q <= i1; q++) {
+                const u32 p = start + q - 1;
+                if ((p & 15) == 0)
+                    w = ix.text[p >> 4];
+                const u64 M = Mr[(w >> ((p & 15) * 2)) & 3u];
+                const u64 D0 = bandRow(hp, hn, M);
+                const u32 l = q % K::BLOCK;
+                bs.ring[(size_t)l * bs.ringStride] = bandPack(hp, M | ~D0, l + sh0);
+            }
+            ringBlock = cb;
         }
-        if (bad)
-            atomOr(B.err, ERR_INTERNAL);
-        if (runLen) {
-            if (nops < opsCap)
-                ops[nops++] = (u16)((runLen << 2) | runOp);
+        do {
+            const u64 w = bs.ring[(size_t)(ti % K::BLOCK) * bs.ringStride];
+            const u32 bidx = tj + Wv - ti; // cell (ti, tj) within the band of row ti
+            if (bidx > Wv + Wh) {
+                bad = true;
+                break;
+            }
+            const u32 isI = ((u32)w >> bidx) & 1u;
+            const u32 isM = (isI ^ 1u) & ((u32)(w >> 32) >> bidx) & 1u;
+            const u32 op = isI ? (u32)CIG_I : (isM ? (u32)CIG_M : (u32)CIG_D);
+            tj -= (isI | isM);
+            ti -= (isI ^ 1u);
+            if (op == runOp) {
+                runLen++;
+            } else {
+                if (runLen) { // the run in registers is complete: one store per run
+                    if (nops < opsCap)
+                        ops[nops++] = (u16)((runLen << 2) | runOp);
+                    else
+                        over = true;
+                }
+                runOp = op;
+                runLen = 1;
+            }
+        } while (tj > 0 && ti / K::BLOCK == cb);
+        if (tj == 0 || bad) {
+            if (bad)
+                atomOr(B.err, ERR_INTERNAL);
+            if (runLen) {
+                if (nops < opsCap)
+                    ops[nops++] = (u16)((runLen << 2) | runOp);
+                else
+                    over = true;
+            }
+            if (over)
+                nops = 0xFFFFFFFFu;
             else
-                over = true;
+                cigReverse(ops, nops);
+            lc.c[CIGARS_IN_TEXT_VERIFICATION]++;
+            VerifyHit h;
+            h.b = start + ti;
+            h.e = start + r;
+            h.dist = eds[r - firstRow];
+            h.ncig = nops;
+            sink(h, ops);
+            ci++;
+            started = false;
         }
-        if (over)
-            nops = 0xFFFFFFFFu;
-        else
-            cigReverse(ops, nops);
-        lc.c[CIGARS_IN_TEXT_VERIFICATION]++;
-        VerifyHit h;
-        h.b = start + ti;
-        h.e = start + r;
-        h.dist = ED;
-        h.ncig = nops;
-        sink(h, ops);
     }
     return nCentres > 0;
 }
 
-// stage 3 task (edit distance)
-CLB_HD void verifyEditTask(const IndexView& ix, const Batch& B, u32 ci, VerifyScratch& vs, LocalCtr& lc) {
+// stage 3 task (edit distance).  pass 0: the candidate's first cluster centre
+// (all of them on the 128-bit path); candidates with more centres go to the
+// `extra` list, whose entries pass 1 verifies again for the remaining centres.
+CLB_HD void verifyEditTask(const IndexView& ix, const Batch& B, u32 ci, VerifyScratch& vs, LocalCtr& lc, u32 pass) {
     const Cand c = B.cands.data[ci];
-    u32 pos = findSA(ix, c.row, lc.s[ST_LF_STEPS]);
+    u64 lfDummy = 0;
+    u32 pos = findSA(ix, c.row, pass == 0 ? lc.s[ST_LF_STEPS] : lfDummy);
     u32 sum = pos + c.add;
     u32 start = sum >= c.sub ? sum - c.sub : 0u;
     const u32 maxED = c.maxED, minED = c.minED;
     const u32 nZeros = c.fixedStart ? 1u : 2 * maxED + 1;
     const u32 len = seqLen(B, c.t);
-    lc.c[IN_TEXT_STARTED]++;
-    CandSink sink(B, c);
+    if (pass == 0)
+        lc.c[IN_TEXT_STARTED]++;
+    const u32 first = pass == 0 ? 0u : 1u;
+    CandSink sink(B, c, first);
     bool considered = true, ok;
     // number of rows: Wv + n with Wv = nZeros - 1 + maxED (fmindex.cpp:290-299)
     const u32 nRows = nZeros - 1 + maxED + len + 1;
     const u32 end = tmin(ix.textLength - 1, start + nRows - 1);
-    if (use64(nZeros, maxED)) {
+    const bool fast = use64(nZeros, maxED);
+    const unsigned fm = warpBallot(vs.warpMask, fast);
+    if (fast) {
+        u32 total = 0;
         ok = verifyWindowFast(ix, B, c.t, vs.bs, start, end, nZeros, maxED, minED, vs.ops, B.cigW, lc, considered,
-                              sink);
+                              sink, fm, first, pass == 0 ? 1u : 0xFFFFu, total);
+        if (pass == 0 && total > 1)
+            B.extra.push(ci, B.err, ERR_CAND_OVERFLOW);
     } else {
         ok = verifyWindow<u128>(ix, B, c.t, (Row<u128>*)vs.rows, start, end, nZeros, maxED, minED, vs.ops, B.cigW, lc,
                                 considered, sink);
     }
-    if (!ok && considered)
+    if (pass == 0 && !ok && considered)
         lc.c[ABORTED_IN_TEXT_VERIF]++;
-    lc.c[TOTAL_REPORTED_POSITIONS] += sink.sub;
-    lc.s[ST_TEXT_OCCS] += sink.sub;
+    lc.c[TOTAL_REPORTED_POSITIONS] += sink.sub - first;
+    lc.s[ST_TEXT_OCCS] += sink.sub - first;
 }
 
 // stage 3 task (Hamming distance), fmindex.cpp:358-407
