@@ -180,6 +180,17 @@ CLB_HD u32 findSA(const IndexView& ix, u32 i, u64& lfSteps) {
     }
 }
 
+// 32 characters (2 bits each) of the text starting at position p (any
+// alignment); the text array is padded so that p may run up to 64 characters
+// past the end
+CLB_HD u64 textWindow64(const IndexView& ix, u32 p) {
+    const u32 wi = p >> 4, sh = (p & 15) * 2;
+    const u32 w0 = ix.text[wi], w1 = ix.text[wi + 1], w2 = ix.text[wi + 2];
+    const u32 lo = (u32)((((u64)w1 << 32) | w0) >> sh);
+    const u32 hi = (u32)((((u64)w2 << 32) | w1) >> sh);
+    return ((u64)hi << 32) | lo;
+}
+
 CLB_HD u32 textAt(const IndexView& ix, u32 p) { return (ix.text[p >> 4] >> ((p & 15) * 2)) & 3u; }
 
 } // namespace clb

@@ -155,7 +155,7 @@ template <typename BE> struct DeviceIndex {
             f.read((char*)&tl, 4);
             if (tl != view.textLength)
                 throw std::runtime_error("Text length does not match the character counts: " + base + ".txt.bin");
-            std::vector<u32> packed((size_t)tl / 16 + 2, 0);
+            std::vector<u32> packed((size_t)tl / 16 + 8, 0); // padded: textWindow64 reads up to 3 words past a position
             std::vector<char> buf(1 << 20);
             size_t pos = 0;
             while (pos < tl) {

@@ -222,16 +222,17 @@ CLB_HD bool verifyWindowFast(const IndexView& ix, const Batch& B, u32 t, const B
         u64 Mc[4];
         for (u32 c = 0; c < 4; c++)
             Mc[c] = matchVec<u64>(ps, 0, c);
-        u32 tw = ix.text[start >> 4];
+        // text of the rows of a block as one 64-bit window (row i <-> bits 2 * (i % 32));
+        // the next block's window is fetched a block ahead, at the same iteration
+        // in every lane
+        u64 tcur = textWindow64(ix, start) << 2, tnxt = textWindow64(ix, start + K::BLOCK - 1);
         bool ok = true;
         for (i = 1; i <= size; ++i) {
-            const u32 p = start + i - 1;
-            if ((p & 15) == 0)
-                tw = ix.text[p >> 4];
-            const u32 Y = (tw >> ((p & 15) * 2)) & 3u;
             const u32 l = i % K::BLOCK;
             RAC <<= 1;
             if (l == 0) {
+                tcur = tnxt;
+                tnxt = textWindow64(ix, start + i + K::BLOCK - 1);
                 HP >>= K::BLOCK;
                 HN >>= K::BLOCK;
                 RAC >>= K::BLOCK;
@@ -241,6 +242,7 @@ CLB_HD bool verifyWindowFast(const IndexView& ix, const Batch& B, u32 t, const B
                 bs.cp[(size_t)(2 * b) * bs.cpStride] = HP;
                 bs.cp[(size_t)(2 * b + 1) * bs.cpStride] = HN;
             }
+            const u32 Y = (u32)(tcur >> (2 * l)) & 3u;
             const u64 M = Mc[Y];
             const u64 D0 = bandRow(HP, HN, M);
             const u32 diagBit = l + K::DIAG_R0;
@@ -325,14 +327,11 @@ CLB_HD bool verifyWindowFast(const IndexView& ix, const Batch& B, u32 t, const B
                 i0 = 1;
             }
             const u32 i1 = tmin(cb * K::BLOCK + K::BLOCK - 1, lastRow);
-            u32 w = ix.text[(start + i0 - 1) >> 4];
+            const u64 tw = (cb == 0) ? textWindow64(ix, start) << 2 : textWindow64(ix, start + cb * K::BLOCK - 1);
             for (u32 q = i0; q <= i1; q++) {
-                const u32 p = start + q - 1;
-                if ((p & 15) == 0)
-                    w = ix.text[p >> 4];
-                const u64 M = Mr[(w >> ((p & 15) * 2)) & 3u];
-                const u64 D0 = bandRow(hp, hn, M);
                 const u32 l = q % K::BLOCK;
+                const u64 M = Mr[(u32)(tw >> (2 * l)) & 3u];
+                const u64 D0 = bandRow(hp, hn, M);
                 bs.ring[(size_t)l * bs.ringStride] = bandPack(hp, M | ~D0, l + sh0);
             }
             ringBlock = cb;
