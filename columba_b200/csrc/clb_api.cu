@@ -221,6 +221,8 @@ struct CudaBackend {
     int numSMs = 0;
     cudaStream_t stream = nullptr;    // stream in use
     cudaStream_t ownStream = nullptr; // created by this backend
+    cudaStream_t copyStream = nullptr; // sliced host-to-device copies
+    cudaEvent_t evCopy[8] = {}, evCopyStart = nullptr;
     u32* workCtrs = nullptr; // pool of work counters, one per dynamic launch
     u32* scanSums = nullptr; // tile sums of exclusiveScan
     u32 scanCap = 0;
@@ -271,6 +273,13 @@ struct CudaBackend {
         for (auto& ev : evStage)
             if (ev)
                 cudaEventDestroy(ev);
+        if (copyStream) {
+            cudaStreamSynchronize(copyStream);
+            for (auto& ev : evCopy)
+                cudaEventDestroy(ev);
+            cudaEventDestroy(evCopyStart);
+            cudaStreamDestroy(copyStream);
+        }
         if (ownStream)
             cudaStreamDestroy(ownStream);
     }
@@ -290,13 +299,40 @@ struct CudaBackend {
         cudaStreamSynchronize(stream);
         cudaFree(p);
     }
+    void* hostAlloc(size_t n) {
+        void* p = nullptr;
+        CLB_CUDA(cudaSetDevice(device));
+        CLB_CUDA(cudaHostAlloc(&p, n ? n : 16, cudaHostAllocDefault));
+        return p;
+    }
+    void hostFree(void* p) { cudaFreeHost(p); }
     void zero(void* p, size_t n) { CLB_CUDA(cudaMemsetAsync(p, 0, n, stream)); }
     void h2d(void* d, const void* s, size_t n) { CLB_CUDA(cudaMemcpyAsync(d, s, n, cudaMemcpyHostToDevice, stream)); }
     void d2h(void* d, const void* s, size_t n) {
         CLB_CUDA(cudaMemcpyAsync(d, s, n, cudaMemcpyDeviceToHost, stream));
         CLB_CUDA(cudaStreamSynchronize(stream));
     }
+    void d2hAsync(void* d, const void* s, size_t n) { CLB_CUDA(cudaMemcpyAsync(d, s, n, cudaMemcpyDeviceToHost, stream)); }
     void sync() { CLB_CUDA(cudaStreamSynchronize(stream)); }
+    // sliced host-to-device copies on a second stream: the copy of slice s+1 runs
+    // while the kernels of slice s do
+    void copyBegin() {
+        if (!copyStream) {
+            CLB_CUDA(cudaStreamCreateWithFlags(&copyStream, cudaStreamNonBlocking));
+            for (auto& ev : evCopy)
+                CLB_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+            CLB_CUDA(cudaEventCreateWithFlags(&evCopyStart, cudaEventDisableTiming));
+        }
+        // the copies may overwrite buffers that earlier work on the main stream still reads
+        CLB_CUDA(cudaEventRecord(evCopyStart, stream));
+        CLB_CUDA(cudaStreamWaitEvent(copyStream, evCopyStart, 0));
+    }
+    void copySlice(void* d, const void* s, size_t n, u32 slice) {
+        if (n)
+            CLB_CUDA(cudaMemcpyAsync(d, s, n, cudaMemcpyHostToDevice, copyStream));
+        CLB_CUDA(cudaEventRecord(evCopy[slice], copyStream));
+    }
+    void copyWait(u32 slice) { CLB_CUDA(cudaStreamWaitEvent(stream, evCopy[slice], 0)); }
     u32 blocksFor(int kind) const {
         switch (kind) {
         case WK_SEARCH: return (u32)numSMs * 2;   // x128 threads: 256 workers per SM (large slabs)

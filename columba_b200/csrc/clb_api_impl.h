@@ -29,8 +29,12 @@ struct clb_ctx {
     clb::DevStrategy flat[clb::CLB_MAX_K + 1];
     int uploadedK = -1;
     clb::MapOptions opt;
-    clb::MapResult res;
+    clb::MapResult<CLB_BE> res;
     std::string err;
+    ~clb_ctx() {
+        if (be)
+            res.release(*be);
+    }
 };
 static thread_local std::string g_clbLoadError;
 

@@ -16,9 +16,10 @@ struct WorkerCtr {
 // stage 0
 struct PrepKernel {
     Batch B;
+    u32 firstRead; // the launch covers reads [firstRead, ...)
     struct State {};
     CLB_HD void begin(State&, u32) const {}
-    CLB_HD void run(State&, u32 i) const { prepTask(B, i); }
+    CLB_HD void run(State&, u32 i) const { prepTask(B, i, firstRead); }
     CLB_HD void end(State&) const {}
 };
 

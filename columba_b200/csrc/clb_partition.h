@@ -29,9 +29,9 @@ CLB_HD u32 asciiCode(u8 c) {
 // One task = 64 characters of one read: the planes of the reverse complement
 // are the complement-swapped planes of the read, so both strands come out of
 // one pass; codes are written as 8-byte words, planes from registers.
-CLB_HD void prepTask(const Batch& B, u32 task) {
+CLB_HD void prepTask(const Batch& B, u32 task, u32 firstRead) {
     const u32 nc = B.nw - 1; // chunks of 64 characters
-    const u32 r = task / nc, j = task % nc;
+    const u32 r = firstRead + task / nc, j = task % nc;
     const u32 off = B.readOff[r], len = B.readOff[r + 1] - off;
     const u32 t0 = 2 * r, t1 = 2 * r + 1;
     const u8* rd = B.readsAscii + off;

@@ -4,6 +4,10 @@
 //
 // BE must provide:
 //   void* alloc(size_t), void free(void*), void zero(void*, size_t),
+//   void* hostAlloc(size_t), void hostFree(void*)  (result arrays on the host),
+//   void d2hAsync(dst, src, n) (completed by sync()),
+//   void copyBegin(), void copySlice(dst, src, n, slice), void copyWait(slice)  (host-to-device copies that
+//   overlap the kernels: slice s is usable by work launched after copyWait(s)),
 //   void h2d(void* dst, const void* src, size_t), void d2h(void* dst, const void* src, size_t),
 //   void sync(), u32 workers(int kind) (number of workers for scratch slabs),
 //   u32 fallbackWorkers() (workers that need slabs instead of shared memory; 0 on the GPU),
@@ -54,15 +58,45 @@ struct MapOptions {
     u32 noCigar = 0;
 };
 
-struct MapResult {
+// host array that the backend allocates (page-locked on the GPU, so that the
+// device-to-host copies of the results run at full PCIe speed)
+template <typename BE, typename T> struct HostBuf {
+    T* p = nullptr;
+    size_t n = 0, cap = 0;
+    void resize(BE& be, size_t want) {
+        if (want > cap) {
+            if (p)
+                be.hostFree(p);
+            cap = want + want / 4 + 1024;
+            p = (T*)be.hostAlloc(cap * sizeof(T));
+        }
+        n = want;
+    }
+    void release(BE& be) {
+        if (p)
+            be.hostFree(p);
+        p = nullptr;
+        n = cap = 0;
+    }
+    size_t size() const { return n; }
+    T* data() { return p; }
+};
+
+template <typename BE> struct MapResult {
     // host copies
-    std::vector<OutOcc> occ;
-    std::vector<u16> cig; // occ.size() x cigW
-    std::vector<u32> outStart, outCount; // per read
+    HostBuf<BE, OutOcc> occ;
+    HostBuf<BE, u16> cig; // occ.size() x cigW
+    HostBuf<BE, u32> outStart, outCount; // per read
     u32 cigW = 0;
     u64 counters[N_COUNTERS];
     u64 stats[N_STATS];
     u32 err = 0;
+    void release(BE& be) {
+        occ.release(be);
+        cig.release(be);
+        outStart.release(be);
+        outCount.release(be);
+    }
 };
 
 template <typename BE> struct Pipeline {
@@ -102,7 +136,7 @@ template <typename BE> struct Pipeline {
     // copied in.  Returns 0 or an error bit mask (after growing the lists the
     // caller may simply call again).
     u32 runOnce(const DevStrategy& st, const u8* reads, const u32* off, u32 R, u32 maxLen, size_t totalBytes,
-                bool readsOnDevice, const MapOptions& opt, MapResult* res, bool fetch) {
+                bool readsOnDevice, const MapOptions& opt, MapResult<BE>* res, bool fetch) {
         Batch B;
         B.R = R;
         B.maxLen = maxLen;
@@ -113,14 +147,24 @@ template <typename BE> struct Pipeline {
         B.cigW = 2 * opt.k + 2;
         B.noCigarFlag = opt.noCigar;
         const u32 T = 2 * R;
+        // host reads go up in slices on the copy stream; the preparation kernel of a
+        // slice starts as soon as its bytes have arrived (see stage 0 below)
+        const u32 nSlices = readsOnDevice ? 1u : tmin<u32>(8u, R / 65536u + 1u);
+        u32 sliceEnd[8];
         if (readsOnDevice) {
             B.readsAscii = reads;
             B.readOff = off;
+            sliceEnd[0] = R;
         } else {
             bReads.ensure(be, totalBytes + 16);
             bOff.ensure(be, (size_t)(R + 1) * 4);
-            be.h2d(bReads.p, reads, totalBytes);
             be.h2d(bOff.p, off, (size_t)(R + 1) * 4);
+            be.copyBegin();
+            for (u32 s = 0; s < nSlices; s++) {
+                const u32 r0 = (u32)((u64)R * s / nSlices), r1 = (u32)((u64)R * (s + 1) / nSlices);
+                sliceEnd[s] = r1;
+                be.copySlice((u8*)bReads.p + off[r0], reads + off[r0], (size_t)off[r1] - off[r0], s);
+            }
             B.readsAscii = (const u8*)bReads.p;
             B.readOff = (const u32*)bOff.p;
         }
@@ -191,8 +235,12 @@ template <typename BE> struct Pipeline {
 
         // ---- stage 0/1
         {
-            PrepKernel k0{B};
-            be.launch(k0, R * (B.nw - 1), nullptr, WK_LIGHT);
+            for (u32 sl = 0, r0 = 0; sl < nSlices; r0 = sliceEnd[sl], sl++) {
+                if (!readsOnDevice)
+                    be.copyWait(sl);
+                PrepKernel k0{B, r0};
+                be.launch(k0, (sliceEnd[sl] - r0) * (B.nw - 1), nullptr, WK_LIGHT);
+            }
             be.mark(STG_PREP);
             // shared memory on the GPU; a slab for backends without it
             const u32 fw = be.fallbackWorkers();
@@ -283,16 +331,17 @@ template <typename BE> struct Pipeline {
             res->cigW = B.cigW;
             if (fetch && !(err & ~(u32)ERR_SHORT_READ)) {
                 u32 n = hm.nOut;
-                res->occ.resize(n);
-                res->cig.resize((size_t)n * B.cigW);
-                res->outStart.resize(R);
-                res->outCount.resize(R);
+                res->occ.resize(be, n);
+                res->cig.resize(be, (size_t)n * B.cigW);
+                res->outStart.resize(be, R);
+                res->outCount.resize(be, R);
                 if (n) {
-                    be.d2h(res->occ.data(), bOut.p, (size_t)n * sizeof(OutOcc));
-                    be.d2h(res->cig.data(), bOutCig.p, (size_t)n * B.cigW * 2);
+                    be.d2hAsync(res->occ.data(), bOut.p, (size_t)n * sizeof(OutOcc));
+                    be.d2hAsync(res->cig.data(), bOutCig.p, (size_t)n * B.cigW * 2);
                 }
-                be.d2h(res->outStart.data(), B.outStart, (size_t)R * 4);
-                be.d2h(res->outCount.data(), B.outCount, (size_t)R * 4);
+                be.d2hAsync(res->outStart.data(), B.outStart, (size_t)R * 4);
+                be.d2hAsync(res->outCount.data(), B.outCount, (size_t)R * 4);
+                be.sync();
             }
         }
         return err;
@@ -300,7 +349,7 @@ template <typename BE> struct Pipeline {
 
     // run with automatic re-run after list overflows
     u32 run(const DevStrategy& st, const u8* reads, const u32* off, u32 R, u32 maxLen, size_t totalBytes,
-            bool readsOnDevice, const MapOptions& opt, MapResult* res, bool fetch) {
+            bool readsOnDevice, const MapOptions& opt, MapResult<BE>* res, bool fetch) {
         const u32 retry = ERR_CAND_OVERFLOW | ERR_FMOCC_OVERFLOW | ERR_TEXTOCC_OVERFLOW | ERR_OUT_OVERFLOW;
         u32 err = 0;
         for (int attempt = 0; attempt < 8; attempt++) {

@@ -25,8 +25,14 @@ struct HostEmuBackend {
     void h2d(void* d, const void* s, size_t n) { std::memcpy(d, s, n); }
     void d2h(void* d, const void* s, size_t n) { std::memcpy(d, s, n); }
     void sync() {}
+    void d2hAsync(void* d, const void* s, size_t n) { std::memcpy(d, s, n); }
+    void copyBegin() {}
+    void copySlice(void* d, const void* s, size_t n, u32) { std::memcpy(d, s, n); }
+    void copyWait(u32) {}
     u32 workers(int) { return 1; }
     u32 laneStride() const { return 1; }
+    void* hostAlloc(size_t n) { return std::malloc(n ? n : 16); }
+    void hostFree(void* p) { std::free(p); }
     u32 fallbackWorkers() const { return 1; }
     template <class K> void launch(const K& k, u32 nMax, const u32* nDev, int) {
         u32 n = nDev ? (*nDev < nMax ? *nDev : nMax) : nMax;
