@@ -58,8 +58,13 @@ __global__ void __launch_bounds__(128) clb_kernel(const K k, u32 nMax, const u32
     k.begin(st, worker);
     bindSharedOf(k, st, clb_smem, 0);
     if (workCtr == nullptr) {
-        for (u32 i = worker; i < n; i += nWorkers)
-            k.run(st, i);
+        // warp-uniform trip count, so that the lanes of a warp can vote
+        for (u32 i0 = worker - (threadIdx.x & 31); i0 < n; i0 += nWorkers) {
+            const u32 i = i0 + (threadIdx.x & 31);
+            const unsigned act = __ballot_sync(0xFFFFFFFFu, i < n);
+            if (i < n)
+                runOf(k, st, i, act, 0);
+        }
     } else {
         const u32 lane = threadIdx.x & 31;
         for (;;) {

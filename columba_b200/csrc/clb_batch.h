@@ -20,6 +20,9 @@ struct PartInfo {
     u8 scheme; // index into DevStrategy::sc
     u8 valid;  // 0: read too short for partitioning
     u16 len;
+    u16 matched;  // characters matched by the seeding (dynamic partitioning)
+    u8 stepping;  // 1: the greedy steps of the dynamic partitioning are still to be done
+    u8 pad;
 };
 
 // one search of the chosen scheme for one (read,strand)
@@ -89,6 +92,34 @@ template <typename T> struct DevList {
         data[i] = v;
         return i;
     }
+    // reserve n slots for every lane in `act` (all of them call this together; the
+    // lanes outside act are the top lanes of the warp) with one atomic per warp
+    CLB_HD u32 warpReserve(u32 n, unsigned act, u32* err, u32 errBit) const {
+#if defined(__CUDA_ARCH__)
+        const u32 lane = threadIdx.x & 31;
+        u32 incl = n;
+        for (u32 o = 1; o < 32; o <<= 1) {
+            const u32 v = __shfl_up_sync(act, incl, o);
+            if (lane >= o)
+                incl += v;
+        }
+        const int last = 31 - __clz((int)act);
+        u32 base = 0;
+        if ((int)lane == last && incl)
+            base = atomicAdd(count, incl);
+        base = __shfl_sync(act, base, last);
+        const u32 i = base + incl - n;
+        if (i + n > cap || i + n < i) {
+            if (n)
+                atomOr(err, errBit);
+            return 0xFFFFFFFFu;
+        }
+        return i;
+#else
+        (void)act;
+        return reserve(n, err, errBit);
+#endif
+    }
     // reserve n consecutive slots; returns first index or 0xFFFFFFFF
     CLB_HD u32 reserve(u32 n, u32* err, u32 errBit) const {
         u32 i = atomAdd<u32>(count, n);
@@ -140,6 +171,7 @@ struct Batch {
     u32* outStart;  // R+1
     DevList<OutOcc> out;
     u16* outCig;    // out.cap x cigW
+    DevList<u32> cigJobs;  // indices into out[] whose CIGAR is still to be computed (index occurrences)
     // statistics
     u64* counters;  // N_COUNTERS
     u64* stats;     // N_STATS

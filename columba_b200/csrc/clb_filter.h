@@ -111,6 +111,62 @@ struct FilterScratch {
     u32 rowsCap;
 };
 
+// 64-bit fast path of bpFindCigar (bitparallelmatrix.h:460-526): row state in
+// registers, text as prefetched 64-bit windows, and per row only the band bits
+// the traceback needs (HP and match | !D0, see BandStore) in `band`.
+CLB_HD u32 findCigarFast(const IndexView& ix, const Batch& B, const PartSeq& ps, u32 b, u32 refLen, u32 score,
+                         u64* band, u16* ops, u32 cap) {
+    typedef BPC<u64> K;
+    const u32 n = ps.len + 1, Wv = score, Wh = score, sh0 = K::DIAG_R0 - Wv;
+    u64 HP = (~0ull) << K::LEFT, HN = ~HP;
+    band[0] = bandPack(HP, 0, sh0);
+    u64 Mc[4];
+    for (u32 c = 0; c < 4; c++)
+        Mc[c] = matchVec<u64>(ps, 0, c);
+    u64 tcur = textWindow64(ix, b) << 2, tnxt = textWindow64(ix, b + K::BLOCK - 1);
+    for (u32 i = 1; i <= refLen; i++) {
+        const u32 l = i % K::BLOCK;
+        if (l == 0) {
+            HP >>= K::BLOCK;
+            HN >>= K::BLOCK;
+            tcur = tnxt;
+            tnxt = textWindow64(ix, b + i + K::BLOCK - 1);
+            for (u32 c = 0; c < 4; c++)
+                Mc[c] = matchVec<u64>(ps, i / K::BLOCK, c);
+        }
+        const u64 M = Mc[(u32)(tcur >> (2 * l)) & 3u];
+        const u64 D0 = bandRow(HP, HN, M);
+        band[i] = bandPack(HP, M | ~D0, l + sh0);
+    }
+    u32 i = refLen, j = n - 1, nn = 0;
+    while (j > 0 || i > 0) {
+        const u64 w = band[i];
+        const u32 bidx = j + Wv - i; // wraps when the cell is left of the band
+        const bool inBand = bidx <= Wv + Wh;
+        u32 op;
+        if (j > 0 && inBand && (((u32)w >> bidx) & 1u)) {
+            --j;
+            op = CIG_I;
+        } else if (i > 0 && j > 0 && inBand && (((u32)(w >> 32) >> bidx) & 1u)) {
+            --i;
+            --j;
+            op = CIG_M;
+        } else {
+            if (i == 0 || (j > 0 && !inBand)) { // the alignment left the band: not an occurrence with `score` errors
+                atomOr(B.err, ERR_INTERNAL);
+                return 0xFFFFFFFFu;
+            }
+            --i;
+            op = CIG_D;
+        }
+        nn = cigPush(ops, nn, cap, op);
+        if (nn == 0xFFFFFFFFu)
+            return nn;
+    }
+    cigReverse(ops, nn);
+    return nn;
+}
+
 // generateCIGAR, indexinterface.h:959-997: re-align the read against text[b,e)
 CLB_HD u32 cigarForOcc(const IndexView& ix, const Batch& B, u32 t, u32 b, u32 e, u32 dist, FilterScratch& fs,
                        u16* ops, LocalCtr& lc) {
@@ -127,7 +183,7 @@ CLB_HD u32 cigarForOcc(const IndexView& ix, const Batch& B, u32 t, u32 b, u32 e,
     }
     u32 n;
     if (BPC<u64>::MAX_ED >= dist)
-        n = bpFindCigar<u64>((Row<u64>*)fs.rows, ps, ref, refLen, dist, ops, B.cigW);
+        n = findCigarFast(ix, B, ps, b, refLen, dist, (u64*)fs.rows, ops, B.cigW);
     else
         n = bpFindCigar<u128>((Row<u128>*)fs.rows, ps, ref, refLen, dist, ops, B.cigW);
     if (n == 0xFFFFFFFFu) {
@@ -277,9 +333,9 @@ CLB_HD void txPerReadTask(const IndexView& ix, const Batch& B, u32 r, FilterScra
     for (u32 i = 0; i < nOut; i++) {
         TextOccRec o = d[idx[i]];
         u16* cig = B.textCig + (size_t)idx[i] * B.cigW;
-        if (edit && !B.noCigarFlag && o.ncig == 0) {
-            o.ncig = (u8)cigarForOcc(ix, B, o.t, o.b, o.e, o.dist, fs, cig, lc);
-        }
+        // generateCIGARS for index occurrences (indexinterface.h:939-949): the
+        // alignment itself is left to a dense follow-up kernel (cigarJobTask)
+        const bool pending = edit && !B.noCigarFlag && o.ncig == 0;
         // findSeqName, indexinterface.cpp:799-897
         u32 lo = 0, hi = ix.numSeq + 1; // upper_bound over seqStart[0..numSeq]
         while (lo < hi) {
@@ -296,6 +352,8 @@ CLB_HD void txPerReadTask(const IndexView& ix, const Batch& B, u32 r, FilterScra
         u32 ncig = o.ncig;
         const u16* src = cig;
         if (o.e <= ix.seqStart[index + 1]) {
+            if (pending)
+                B.cigJobs.push(at + w, B.err, ERR_OUT_OVERFLOW);
             out.trimmed = 0;
             out.indexBegin = o.b;
             out.pos = o.b - ix.seqStart[index];
@@ -304,6 +362,8 @@ CLB_HD void txPerReadTask(const IndexView& ix, const Batch& B, u32 r, FilterScra
         } else {
             if (!edit)
                 continue;
+            if (pending)
+                lc.c[CIGARS_IN_INDEX]++; // computed by the reference, then superseded by the trimmed alignment
             u32 nb, ne;
             const u32 largest = B.k;
             if ((ix.seqStart[index + 1] - o.b) <= largest) {
@@ -349,6 +409,16 @@ CLB_HD void txPerReadTask(const IndexView& ix, const Batch& B, u32 r, FilterScra
     }
     B.outStart[r] = at;
     B.outCount[r] = w;
+}
+
+// CIGAR of one surviving index occurrence (out[j]); one task per job so that
+// the alignments run in full warps instead of inside the per-read filter.
+CLB_HD void cigarJobTask(const IndexView& ix, const Batch& B, u32 job, FilterScratch& fs, LocalCtr& lc) {
+    const u32 j = B.cigJobs.data[job];
+    OutOcc& o = B.out.data[j];
+    const u32 t = 2 * o.read + o.strand;
+    u16* dst = B.outCig + (size_t)j * B.cigW;
+    o.ncig = (u8)cigarForOcc(ix, B, t, o.indexBegin, o.indexBegin + (o.end - o.pos), o.dist, fs, dst, lc);
 }
 
 } // namespace clb

@@ -52,14 +52,16 @@ struct IndexView {
 
 CLB_HD BwtRec loadRec(const BwtRec* p) {
 #if defined(__CUDA_ARCH__)
-    // one 32-byte sector, read through the non-coherent path as two 16-byte
-    // vector loads
-    const uint4* q = reinterpret_cast<const uint4*>(p);
-    uint4 a = __ldg(q), b = __ldg(q + 1);
+    // one 32-byte sector, read through the non-coherent path as ONE 256-bit load
+    // (LDG.E.256, sm_100): the lanes of a warp hit 32 different lines, and the
+    // L1 tag stage -- one lookup per lane and load instruction -- is what bounds
+    // the rank throughput of a warp
+    u64 a, b, lo, hi;
+    asm("ld.global.nc.v4.u64 {%0,%1,%2,%3}, [%4];" : "=l"(a), "=l"(b), "=l"(lo), "=l"(hi) : "l"(p));
     BwtRec r;
-    r.cnt[0] = a.x; r.cnt[1] = a.y; r.cnt[2] = a.z; r.cnt[3] = a.w;
-    r.lo = ((u64)b.y << 32) | b.x;
-    r.hi = ((u64)b.w << 32) | b.z;
+    r.cnt[0] = (u32)a; r.cnt[1] = (u32)(a >> 32); r.cnt[2] = (u32)b; r.cnt[3] = (u32)(b >> 32);
+    r.lo = lo;
+    r.hi = hi;
     return r;
 #else
     return *p;

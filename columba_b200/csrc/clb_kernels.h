@@ -23,35 +23,64 @@ struct PrepKernel {
     CLB_HD void end(State&) const {}
 };
 
-// stage 1.  Stepped functor: besides run() (the whole task, used by the host
-// emulation) it offers start / step / finish, which the CUDA launcher drives
-// with per-lane task refill (clb_kernel_stepped).
-struct PartitionKernel {
+// stage 1a / 1c: uniform kernels around the greedy steps (clb_partition.h)
+struct PartBase {
     IndexView ix;
     const DevStrategy* st;
     Batch B;
     u32 P;       // parts (st->P, known to the host)
     u8* slabs;   // scratch of the workers when there is no shared memory (host emulation), else null
+    u32 patWords; // words per worker for the sequence as 4-bit codes in shared memory (0: not staged)
+};
+struct PartWorkerState {
+    LocalCtr lc;
+    PartState ps;
+};
+#define CLB_PART_COMMON                                                                                        \
+    PartBase a;                                                                                                \
+    typedef PartWorkerState State;                                                                             \
+    CLB_HD size_t smemBytes(u32 nThreads) const {                                                              \
+        return (PartScratch::bytesPerWorker(a.P) + (size_t)a.patWords * sizeof(u32)) * nThreads;               \
+    }                                                                                                          \
+    CLB_HD void bindShared(State& s, u8* smem, u32 tid, u32 nThreads) const {                                  \
+        s.ps.ps.w = (u32*)smem + tid;                                                                          \
+        s.ps.ps.stride = nThreads;                                                                             \
+        s.ps.patS = a.patWords ? (u32*)smem + (size_t)a.P * 8 * nThreads + tid : (u32*)0;                      \
+        s.ps.patStride = nThreads;                                                                             \
+    }                                                                                                          \
+    CLB_HD void begin(State& s, u32 worker) const {                                                            \
+        s.lc.clear();                                                                                          \
+        s.ps.patS = (u32*)0;                                                                                   \
+        s.ps.patStride = 1;                                                                                    \
+        s.ps.ps.w = a.slabs ? (u32*)(a.slabs + (size_t)worker * PartScratch::bytesPerWorker(a.P)) : (u32*)0;   \
+        s.ps.ps.stride = 1;                                                                                    \
+    }                                                                                                          \
+    CLB_HD void end(State& s) const { s.lc.flush(a.B.counters, a.B.stats); }
+
+struct SeedKernel {
+    CLB_PART_COMMON
+    CLB_HD void run(State& s, u32 t) const { partStart(a.ix, *a.st, a.B, t, s.ps, s.lc); }
+};
+// stage 1b.  Stepped functor: besides run() (the whole task, used by the host
+// emulation) it offers start / step / finish, which the CUDA launcher drives
+// with per-lane task refill (clb_kernel_stepped).
+struct GreedyKernel {
+    CLB_PART_COMMON
     static const bool kStepped = true;
-    struct State {
-        LocalCtr lc;
-        PartState ps;
-    };
-    CLB_HD size_t smemBytes(u32 nThreads) const { return PartScratch::bytesPerWorker(P) * nThreads; }
-    CLB_HD void bindShared(State& s, u8* smem, u32 tid, u32 nThreads) const {
-        s.ps.ps.w = (u32*)smem + tid;
-        s.ps.ps.stride = nThreads;
+    CLB_HD void run(State& s, u32 t) const {
+        start(s, t);
+        while (!step(s)) {
+        }
+        finish(s);
     }
-    CLB_HD void begin(State& s, u32 worker) const {
-        s.lc.clear();
-        s.ps.ps.w = slabs ? (u32*)(slabs + (size_t)worker * PartScratch::bytesPerWorker(P)) : (u32*)0;
-        s.ps.ps.stride = 1;
-    }
-    CLB_HD void run(State& s, u32 t) const { partitionTask(ix, *st, B, t, s.ps, s.lc); }
-    CLB_HD void start(State& s, u32 t) const { partStart(ix, *st, B, t, s.ps, s.lc); }
-    CLB_HD bool step(State& s) const { return partStep(ix, *st, s.ps, s.lc); }
-    CLB_HD void finish(State& s) const { partFinish(ix, *st, B, s.ps, s.lc); }
-    CLB_HD void end(State& s) const { s.lc.flush(B.counters, B.stats); }
+    CLB_HD void start(State& s, u32 t) const { greedyStart(*a.st, a.B, t, s.ps); }
+    CLB_HD bool step(State& s) const { return partStep(a.ix, *a.st, s.ps, s.lc); }
+    CLB_HD void finish(State& s) const { greedyFinish(*a.st, a.B, s.ps); }
+};
+struct EmitKernel {
+    CLB_PART_COMMON
+    CLB_HD void run(State& s, u32 t) const { partFinish(a.ix, *a.st, a.B, t, s.ps, s.lc, 1u); }
+    CLB_HD void run(State& s, u32 t, unsigned act) const { partFinish(a.ix, *a.st, a.B, t, s.ps, s.lc, act); }
 };
 
 // stage 2
@@ -225,6 +254,18 @@ struct TxPerReadKernel {
         }
         s.lc.c[NUMBER_OF_READS]++;
     }
+    CLB_HD void end(State& s) const { s.lc.flush(B.counters, B.stats); }
+};
+
+struct CigarJobKernel {
+    IndexView ix;
+    Batch B;
+    u8* slabs;
+    size_t slabBytes;
+    u32 rowsCap;
+    typedef FilterState State;
+    CLB_HD void begin(State& s, u32 worker) const { carveFilter(s, slabs + (size_t)worker * slabBytes, B.cigW, rowsCap); }
+    CLB_HD void run(State& s, u32 i) const { cigarJobTask(ix, B, i, s.fs, s.lc); }
     CLB_HD void end(State& s) const { s.lc.flush(B.counters, B.stats); }
 };
 

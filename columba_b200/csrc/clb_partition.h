@@ -122,7 +122,12 @@ CLB_HD RangePair matchString(const IndexView& ix, int dir, bool uni, const u8* p
 struct PartScratch {
     u32* w;
     u32 stride;
-    CLB_HD u32& at(u32 i, u32 f) const { return w[(size_t)(i * 8 + f) * stride]; }
+    CLB_HD u32& at(u32 i, u32 f) const {
+#if defined(__CUDA_ARCH__)
+        __builtin_assume(__isShared(w)); // the CUDA backend always binds shared memory: LDS/STS, 32-bit addresses
+#endif
+        return w[(i * 8 + f) * stride];
+    }
     CLB_HD u32& b(u32 i) const { return at(i, 0); }
     CLB_HD u32& e(u32 i) const { return at(i, 1); }
     CLB_HD RangePair emr(u32 i) const { return mkPair(at(i, 2), at(i, 3), at(i, 4), at(i, 5)); }
@@ -161,6 +166,10 @@ CLB_HD void calcExactRanges(const IndexView& ix, const u8* pat, u32 P, const Par
 // task while the other lanes keep stepping.
 struct PartState {
     PartScratch ps;
+    // the sequence as 4-bit codes, 8 per word, in shared memory (word j at
+    // patS[j * patStride]); null: read the byte codes from global memory
+    u32* patS;
+    u32 patStride;
     const u8* pat;
     u32 t, pSize, j;
     u32 stepping; // 1: greedy steps outstanding
@@ -232,26 +241,65 @@ CLB_HD bool dynStep(const IndexView& ix, const DevStrategy& st, u32 P, PartState
         return true;
     }
     const u32 pb = ps.b(p), pe = ps.e(p);
-    const bool noL = (p == 0) || pb == ps.e(p - 1);
-    const bool noR = (p == P - 1) || pe == ps.b(p + 1);
+    const u32 pl = (p == 0) ? 0 : p - 1, pr = (p == P - 1) ? p : p + 1;
+    const u32 el = ps.e(pl), br = ps.b(pr); // end of the left / begin of the right neighbour
+    const bool noL = (p == 0) || pb == el;
+    const bool noR = (p == P - 1) || pe == br;
     // both neighbours exist when neither side is closed
-    const u32 wl = ps.width(p == 0 ? 0 : p - 1), wr = ps.width(p == P - 1 ? p : p + 1);
+    const u32 wl = ps.width(pl), wr = ps.width(pr);
     const int dir = noL ? DIR_FWD : (noR ? DIR_BWD : ((wl < wr) ? DIR_BWD : DIR_FWD));
     const bool fwd = (dir == DIR_FWD);
-    const u32 c = S.pat[fwd ? pe : pb - 1];
-    ps.b(p) = fwd ? pb : pb - 1;
-    ps.e(p) = fwd ? pe + 1 : pe;
+    const u32 cpos = fwd ? pe : pb - 1;
+    u32 c;
+    if (S.patS) {
+#if defined(__CUDA_ARCH__)
+        __builtin_assume(__isShared(S.patS));
+#endif
+        c = (S.patS[(cpos >> 3) * S.patStride] >> ((cpos & 7) * 4)) & 15u;
+    } else {
+        c = S.pat[cpos];
+    }
+    const u32 nb = fwd ? pb : pb - 1, ne = fwd ? pe + 1 : pe;
+    ps.at(p, fwd ? 1u : 0u) = fwd ? ne : nb;
     RangePair r = ps.emr(p);
     addChar(ix, dir, p == P - 1, c, r, lc);
     ps.setEmr(p, r);
-    ps.setKey(p, partKey(st, ps, P, p));
-    const u32 q = fwd ? (p == P - 1 ? p : p + 1) : (p == 0 ? p : p - 1);
-    ps.setKey(q, partKey(st, ps, P, q));
+    // keys: the extended part, and the neighbour it grew towards once they touch
+    // (a part's key is width x weight until it is closed on both sides)
+    const bool cL = (p == 0) || nb == el, cR = (p == P - 1) || ne == br;
+    ps.setKey(p, (cL && cR) ? 0ull : (u64)r.width() * st.weights[p]);
+    // (no branch on the direction: lanes extend different parts in different directions)
+    const u32 q = fwd ? pr : pl;
+    const bool touch = fwd ? (p != P - 1 && ne == br) : (p != 0 && nb == el);
+    const u32 q2 = fwd ? ((q == P - 1) ? q : q + 1) : ((q == 0) ? q : q - 1); // the neighbour's other neighbour
+    const bool closed = fwd ? (q == P - 1 || ps.e(q) == ps.b(q2)) : (q == 0 || ps.b(q) == ps.e(q2));
+    if (touch && closed)
+        ps.setKey(q, 0ull);
     S.j++;
     return S.j >= S.pSize;
 }
 
-// stage 1 task, first half: everything up to the greedy steps.
+CLB_HD void storeParts(PartInfo& pi, const PartScratch& ps, u32 P) {
+    for (u32 i = 0; i < P; i++) {
+        pi.begin[i] = (u16)ps.b(i);
+        pi.end[i] = (u16)ps.e(i);
+        pi.emr[i] = ps.emr(i);
+    }
+}
+CLB_HD void loadParts(const PartInfo& pi, const PartScratch& ps, u32 P) {
+    for (u32 i = 0; i < P; i++) {
+        ps.b(i) = pi.begin[i];
+        ps.e(i) = pi.end[i];
+        ps.setEmr(i, pi.emr[i]);
+    }
+}
+
+// Stage 1 runs as three kernels: seeding (one thread per (read,strand), full
+// warps), the greedy extension steps (stepped kernel with per-lane refill) and
+// the emission of candidates and search tasks (one thread per (read,strand)).
+// The parts travel between them in PartInfo.
+//
+// stage 1a: everything up to the greedy steps.
 CLB_HD void partStart(const IndexView& ix, const DevStrategy& st, const Batch& B, u32 t, PartState& S, LocalCtr& lc) {
     S.t = t;
     S.pat = seqCodes(B, t);
@@ -268,10 +316,15 @@ CLB_HD void partStart(const IndexView& ix, const DevStrategy& st, const Batch& B
         return;
     }
     pi.valid = 1;
+    pi.stepping = 0;
+    pi.matched = 0;
     const PartScratch& ps = S.ps;
     if (B.partStrategy == PART_DYNAMIC) {
         dynSeed(ix, st, P, S, lc);
         S.stepping = 1;
+        pi.stepping = 1;
+        pi.matched = (u16)S.j;
+        storeParts(pi, ps, P);
         return;
     }
     if (B.partStrategy == PART_UNIFORM) { // :194-209
@@ -291,6 +344,40 @@ CLB_HD void partStart(const IndexView& ix, const DevStrategy& st, const Batch& B
         ps.e(P - 1) = pSize;
     }
     calcExactRanges(ix, S.pat, P, ps, lc);
+    storeParts(pi, ps, P);
+}
+// stage 1b: the greedy steps of a task seeded by partStart
+CLB_HD void greedyStart(const DevStrategy& st, const Batch& B, u32 t, PartState& S) {
+    const PartInfo& pi = B.parts[t];
+    S.t = t;
+    S.stepping = 0;
+    if (!pi.valid || !pi.stepping)
+        return;
+    S.pat = seqCodes(B, t);
+    S.pSize = pi.len;
+    S.j = pi.matched;
+    if (S.patS) { // 8 byte codes -> 8 nibbles (the code rows are 8-byte aligned and padded)
+        const u64* src = (const u64*)S.pat;
+        const u32 nwords = (S.pSize + 7) / 8;
+        for (u32 j = 0; j < nwords; j++) {
+            u64 x = src[j] & 0x0F0F0F0F0F0F0F0Full;
+            x = (x | (x >> 4)) & 0x00FF00FF00FF00FFull;
+            x = (x | (x >> 8)) & 0x0000FFFF0000FFFFull;
+            x = (x | (x >> 16)) & 0x00000000FFFFFFFFull;
+            S.patS[j * S.patStride] = (u32)x;
+        }
+    }
+    loadParts(pi, S.ps, st.P);
+    for (u32 i = 0; i < st.P; i++)
+        S.ps.setKey(i, partKey(st, S.ps, st.P, i));
+    S.stepping = 1;
+}
+CLB_HD void greedyFinish(const DevStrategy& st, const Batch& B, PartState& S) {
+    PartInfo& pi = B.parts[S.t];
+    if (pi.valid && pi.stepping) {
+        storeParts(pi, S.ps, st.P);
+        pi.stepping = 0;
+    }
 }
 // true when the task has no (more) greedy steps to do
 CLB_HD bool partStep(const IndexView& ix, const DevStrategy& st, PartState& S, LocalCtr& lc) {
@@ -301,20 +388,28 @@ CLB_HD bool partStep(const IndexView& ix, const DevStrategy& st, PartState& S, L
     return !S.stepping;
 }
 
-// stage 1 task, second half.  Emits the immediate-switch candidates (order
-// slot 0) and the search tasks of the selected scheme.
-CLB_HD void partFinish(const IndexView& ix, const DevStrategy& st, const Batch& B, PartState& S, LocalCtr& lc) {
-    const u32 t = S.t;
+// stage 1c: emits the immediate-switch candidates (order slot 0) and the
+// search tasks of the selected scheme.
+// `act`: the lanes of the warp that run this function together.
+CLB_HD void partFinish(const IndexView& ix, const DevStrategy& st, const Batch& B, u32 t, PartState& S, LocalCtr& lc,
+                       unsigned act) {
     const u32 P = st.P;
     PartInfo& pi = B.parts[t];
-    if (!pi.valid)
-        return;
+    const bool valid = pi.valid != 0;
     const PartScratch& ps = S.ps;
-    for (u32 i = 0; i < P; i++) {
-        pi.begin[i] = (u16)ps.b(i);
-        pi.end[i] = (u16)ps.e(i);
-        pi.emr[i] = ps.emr(i);
-    }
+    if (valid)
+        loadParts(pi, ps, P);
+    // slots for all immediate-switch candidates of the warp at once
+    u32 nCand = 0;
+    if (valid)
+        for (u32 i = 0; i < P; i++) {
+            const u32 width = ps.width(i);
+            if (width != 0 && width <= ix.switchPoint)
+                nCand += width;
+        }
+    u32 at = B.cands.warpReserve(nCand, act, B.err, ERR_CAND_OVERFLOW);
+    if (!valid)
+        return;
     // A) immediate switch, searchstrategy.cpp:464-476 -> fmindex.cpp:245-265 /
     //    :344-356
     u32 emit = 0;
@@ -336,12 +431,11 @@ CLB_HD void partFinish(const IndexView& ix, const DevStrategy& st, const Batch& 
                 c.sub = ps.b(i);
                 c.fixedStart = 1;
             }
-            u32 at = B.cands.reserve(width, B.err, ERR_CAND_OVERFLOW);
             for (u32 row = 0; row < width; row++) {
                 c.row = ps.at(i, 2) + row;
                 c.order = emit++;
                 if (at != 0xFFFFFFFFu)
-                    B.cands.data[at + row] = c;
+                    B.cands.data[at++] = c;
             }
         }
     }
@@ -375,14 +469,6 @@ CLB_HD void partFinish(const IndexView& ix, const DevStrategy& st, const Batch& 
             B.tasks.push(task, B.err, ERR_TASK_OVERFLOW);
         }
     }
-}
-
-// the whole task in one go (host emulation, tests)
-CLB_HD void partitionTask(const IndexView& ix, const DevStrategy& st, const Batch& B, u32 t, PartState& S, LocalCtr& lc) {
-    partStart(ix, st, B, t, S, lc);
-    while (!partStep(ix, st, S, lc)) {
-    }
-    partFinish(ix, st, B, S, lc);
 }
 
 } // namespace clb

@@ -102,7 +102,7 @@ template <typename BE> struct MapResult {
 template <typename BE> struct Pipeline {
     BE& be;
     IndexView ix;
-    DevBuf<BE> bReads, bOff, bCodes, bPlanes, bParts, bTasks, bCands, bExtra, bFm, bTx, bTxCig, bOut, bOutCig, bPerRead, bIdx,
+    DevBuf<BE> bReads, bOff, bCodes, bPlanes, bParts, bTasks, bCands, bExtra, bFm, bTx, bTxCig, bOut, bOutCig, bCigJobs, bPerRead, bIdx,
         bMisc, bSlabPart, bSlabSearch, bSlabVerify, bSlabVerifyWide, bSlabFilter, bStrategy;
     // list capacities (per read multipliers, grown after an overflow)
     double candPerRead = 24, fmPerRead = 4, txPerRead = 24, outPerRead = 8;
@@ -111,7 +111,7 @@ template <typename BE> struct Pipeline {
 
     Pipeline(BE& b) : be(b) {}
     ~Pipeline() {
-        DevBuf<BE>* all[] = {&bReads, &bOff, &bCodes, &bPlanes, &bParts, &bTasks, &bCands, &bExtra, &bFm, &bTx, &bTxCig, &bOut,
+        DevBuf<BE>* all[] = {&bReads, &bOff, &bCodes, &bPlanes, &bParts, &bTasks, &bCands, &bExtra, &bFm, &bTx, &bTxCig, &bCigJobs, &bOut,
                              &bOutCig, &bPerRead, &bIdx, &bMisc, &bSlabPart, &bSlabSearch, &bSlabVerify, &bSlabVerifyWide, &bSlabFilter,
                              &bStrategy};
         for (auto* d : all)
@@ -123,7 +123,7 @@ template <typename BE> struct Pipeline {
         u64 counters[N_COUNTERS];
         u64 stats[N_STATS];
         u32 err;
-        u32 nTasks, nCands, nFm, nTx, nOut, nExtra;
+        u32 nTasks, nCands, nFm, nTx, nOut, nExtra, nCigJobs;
         u32 nT, nR; // 2R and R as device-side task counts
     };
 
@@ -200,6 +200,7 @@ template <typename BE> struct Pipeline {
         bTxCig.ensure(be, (size_t)capTx * B.cigW * 2);
         bOut.ensure(be, (size_t)capOut * sizeof(OutOcc));
         bOutCig.ensure(be, (size_t)capOut * B.cigW * 2);
+        bCigJobs.ensure(be, (size_t)capOut * sizeof(u32));
         bMisc.ensure(be, sizeof(Misc));
         be.zero(bMisc.p, sizeof(Misc));
         Misc* M = (Misc*)bMisc.p;
@@ -216,6 +217,7 @@ template <typename BE> struct Pipeline {
         B.textCig = (u16*)bTxCig.p;
         B.out.data = (OutOcc*)bOut.p; B.out.count = &M->nOut; B.out.cap = capOut;
         B.outCig = (u16*)bOutCig.p;
+        B.cigJobs.data = (u32*)bCigJobs.p; B.cigJobs.count = &M->nCigJobs; B.cigJobs.cap = capOut;
         B.counters = M->counters;
         B.stats = M->stats;
         B.err = &M->err;
@@ -246,8 +248,18 @@ template <typename BE> struct Pipeline {
             const u32 fw = be.fallbackWorkers();
             if (fw)
                 bSlabPart.ensure(be, PartScratch::bytesPerWorker(P) * fw);
-            PartitionKernel k1{ix, dst, B, P, fw ? (u8*)bSlabPart.p : (u8*)0};
-            be.launch(k1, T, nullptr, WK_LIGHT);
+            PartBase pb{ix, dst, B, P, fw ? (u8*)bSlabPart.p : (u8*)0, 0};
+            SeedKernel k1a{pb};
+            be.launch(k1a, T, nullptr, WK_LIGHT);
+            if (opt.partStrategy == PART_DYNAMIC) {
+                // the greedy steps read one character of the sequence per step: stage it on chip
+                PartBase pg = pb;
+                pg.patWords = (!fw && maxLen <= 512) ? (maxLen + 7) / 8 : 0;
+                GreedyKernel k1b{pg};
+                be.launch(k1b, T, nullptr, WK_LIGHT);
+            }
+            EmitKernel k1c{pb};
+            be.launch(k1c, T, nullptr, WK_LIGHT);
             be.mark(STG_PARTITION);
         }
         // ---- stage 2
@@ -309,6 +321,8 @@ template <typename BE> struct Pipeline {
             be.launch(d2, capTx, &M->nTx, WK_LIGHT);
             TxPerReadKernel d3{ix, B, (u8*)bSlabFilter.p, sb, vRows};
             be.launch(d3, R, nullptr, WK_FILTER);
+            CigarJobKernel d4{ix, B, (u8*)bSlabFilter.p, sb, vRows};
+            be.launch(d4, capOut, &M->nCigJobs, WK_FILTER);
             be.mark(STG_TEXT);
         }
         // ---- results
