@@ -24,6 +24,53 @@ CLB_HD u32 asciiCode(u8 c) {
     }
 }
 
+// 64 bytes base[x, x + 64) as 16 little-endian words; bytes outside [0, len)
+// read as 0.  On the GPU the bytes come in as aligned 32-bit words (17 loads
+// instead of 64 byte loads: the load/tag stage, not DRAM, bounds this kernel)
+// re-aligned with funnel shifts.
+CLB_HD void loadWindow64(const u8* base, i32 x, u32 len, u32 U[16]) {
+#if defined(__CUDA_ARCH__)
+    const size_t a0 = (size_t)base + (size_t)(ptrdiff_t)x; // address of byte 0 of the window
+    const size_t lo = (size_t)base, hi = (size_t)base + len;
+    const size_t ab = a0 & ~(size_t)3;
+    const u32 sh = (u32)(a0 & 3) * 8;
+    u32 V[17];
+#pragma unroll
+    for (int m = 0; m < 17; m++) {
+        const size_t wa = ab + 4 * (size_t)m;
+        V[m] = (wa + 4 > lo && wa < hi) ? __ldg((const u32*)wa) : 0u; // only words that hold a byte of the read
+    }
+#pragma unroll
+    for (int m = 0; m < 16; m++) {
+        u32 v = __funnelshift_r(V[m], V[m + 1], sh);
+        // zero the bytes outside the read
+        const i32 p0 = x + 4 * m;
+        u32 keep = 0;
+        keep |= (p0 + 0 >= 0 && (u32)(p0 + 0) < len) ? 0x000000FFu : 0u;
+        keep |= (p0 + 1 >= 0 && (u32)(p0 + 1) < len) ? 0x0000FF00u : 0u;
+        keep |= (p0 + 2 >= 0 && (u32)(p0 + 2) < len) ? 0x00FF0000u : 0u;
+        keep |= (p0 + 3 >= 0 && (u32)(p0 + 3) < len) ? 0xFF000000u : 0u;
+        U[m] = v & keep;
+    }
+#else
+    for (int m = 0; m < 16; m++) {
+        u32 v = 0;
+        for (int q = 0; q < 4; q++) {
+            const i32 p = x + 4 * m + q;
+            if (p >= 0 && (u32)p < len)
+                v |= (u32)base[p] << (8 * q);
+        }
+        U[m] = v;
+    }
+#endif
+}
+// A/C/G/T (either case) -> 0..3, anything else (and 0) -> 4
+CLB_HD u32 asciiCodeFast(u32 c) {
+    const u32 u = c & 0xDFu; // upper case
+    const bool ok = (u == 'A') || (u == 'C') || (u == 'G') || (u == 'T');
+    return ok ? (((c >> 1) ^ (c >> 2)) & 3u) : 4u;
+}
+
 // stage 0: codes of both strands of a read (strand 1 = reverse complement,
 // nucleotide.h) and their "equals A/C/G/T" bit planes, forward and reversed.
 // One task = 64 characters of one read: the planes of the reverse complement
@@ -35,38 +82,49 @@ CLB_HD void prepTask(const Batch& B, u32 task, u32 firstRead) {
     const u32 off = B.readOff[r], len = B.readOff[r + 1] - off;
     const u32 t0 = 2 * r, t1 = 2 * r + 1;
     const u8* rd = B.readsAscii + off;
-    u64 P[4] = {0, 0, 0, 0}, Q[4] = {0, 0, 0, 0};
+    u64 P0 = 0, P1 = 0, P2 = 0, P3 = 0, Q0 = 0, Q1 = 0, Q2 = 0, Q3 = 0;
     u64* c0 = (u64*)(B.codes + (size_t)t0 * B.seqStride);
     u64* c1 = (u64*)(B.codes + (size_t)t1 * B.seqStride);
     const u32 words = B.seqStride / 8;
-    for (u32 w = 0; w < 8; w++) {
+    u32 F[16], G[16];
+    loadWindow64(rd, (i32)(64 * j), len, F);                   // read[64j + i]
+    loadWindow64(rd, (i32)len - 64 - (i32)(64 * j), len, G);   // G byte 63 - i = read[len - 1 - (64j + i)]
+#pragma unroll
+    for (int w = 0; w < 8; w++) {
         u64 w0 = 0, w1 = 0;
-        for (u32 q = 0; q < 8; q++) {
-            const u32 i = 64 * j + 8 * w + q;
-            u32 a = 4, b = 4;
-            if (i < len) {
-                a = asciiCode(rd[i]);
-                b = asciiCode(rd[len - 1 - i]);
-                if (a < 4)
-                    P[a] |= 1ull << (8 * w + q);
-                if (b < 4) {
-                    Q[b] |= 1ull << (8 * w + q);
-                    b = 3 - b;
-                }
-            }
+#pragma unroll
+        for (int q = 0; q < 8; q++) {
+            const int i = 8 * w + q;
+            const bool in = 64 * j + (u32)i < len;
+            const u32 fa = (F[i >> 2] >> (8 * (i & 3))) & 0xFFu;
+            const u32 gb = (G[(63 - i) >> 2] >> (8 * ((63 - i) & 3))) & 0xFFu;
+            const u32 a = in ? asciiCodeFast(fa) : 4u;
+            u32 b = in ? asciiCodeFast(gb) : 4u;
+            const u64 bit = 1ull << i;
+            P0 |= (a == 0) ? bit : 0ull;
+            P1 |= (a == 1) ? bit : 0ull;
+            P2 |= (a == 2) ? bit : 0ull;
+            P3 |= (a == 3) ? bit : 0ull;
+            Q0 |= (b == 0) ? bit : 0ull;
+            Q1 |= (b == 1) ? bit : 0ull;
+            Q2 |= (b == 2) ? bit : 0ull;
+            Q3 |= (b == 3) ? bit : 0ull;
+            b = (b < 4) ? 3 - b : 4u;
             w0 |= (u64)a << (8 * q);
             w1 |= (u64)b << (8 * q);
         }
-        const u32 wi = 8 * j + w;
+        const u32 wi = 8 * j + (u32)w;
         if (wi < words) {
             c0[wi] = w0;
             c1[wi] = w1;
         }
     }
+    const u64 P[4] = {P0, P1, P2, P3}, Q[4] = {Q0, Q1, Q2, Q3};
     u64* p0f = B.planes + ((size_t)t0 * 2 + DIR_FWD) * 4 * B.nw;
     u64* p0b = B.planes + ((size_t)t0 * 2 + DIR_BWD) * 4 * B.nw;
     u64* p1f = B.planes + ((size_t)t1 * 2 + DIR_FWD) * 4 * B.nw;
     u64* p1b = B.planes + ((size_t)t1 * 2 + DIR_BWD) * 4 * B.nw;
+#pragma unroll
     for (u32 c = 0; c < 4; c++) {
         p0f[c * B.nw + j] = P[c];
         p0b[c * B.nw + j] = Q[c];
@@ -81,14 +139,22 @@ CLB_HD void prepTask(const Batch& B, u32 task, u32 firstRead) {
     }
 }
 
-// indexinterface.h:590-595
-CLB_HD RangePair lookUpKmer(const IndexView& ix, const u8* p) {
-    u32 code = 0;
+// indexinterface.h:590-595.  The K byte codes at pat[pos, pos + K) come out of
+// (at most) three 8-byte words of the code row (rowWords words, 8-byte aligned).
+CLB_HD RangePair lookUpKmer(const IndexView& ix, const u8* pat, u32 pos, u32 rowWords) {
+    const u64* src = (const u64*)pat;
+    const u32 w0 = pos >> 3, last = rowWords - 1;
+    const u64 x0 = src[w0], x1 = src[tmin(w0 + 1, last)], x2 = src[tmin(w0 + 2, last)];
+    u32 code = 0, bad = 0;
     for (u32 i = 0; i < ix.K; i++) {
-        if (p[i] > 3)
-            return emptyPair();
-        code = (code << 2) | p[i];
+        const u32 q = (pos & 7) + i;
+        const u64 xw = (q < 8) ? x0 : ((q < 16) ? x1 : x2);
+        const u32 c = (u32)(xw >> ((q & 7) * 8)) & 0xFFu;
+        bad |= (c > 3) ? 1u : 0u;
+        code = (code << 2) | (c & 3u);
     }
+    if (bad)
+        return emptyPair();
     return ix.kmer[code];
 }
 CLB_HD bool addChar(const IndexView& ix, int dir, bool uni, u32 c, RangePair& r, LocalCtr& lc) {
@@ -143,18 +209,19 @@ struct PartScratch {
     static CLB_HD size_t bytesPerWorker(u32 P) { return (size_t)P * 8 * sizeof(u32); }
 };
 
-CLB_HD void calcExactRanges(const IndexView& ix, const u8* pat, u32 P, const PartScratch& ps, LocalCtr& lc) {
+CLB_HD void calcExactRanges(const IndexView& ix, const u8* pat, u32 rowWords, u32 P, const PartScratch& ps,
+                            LocalCtr& lc) {
     const u32 ws = ix.K;
     for (u32 i = 0; i < P; ++i) {
         u32 size = ps.e(i) <= ps.b(i) ? 0 : ps.e(i) - ps.b(i);
         u32 start = ps.b(i) + ((size >= ws) ? ws : 0);
-        RangePair init = (size >= ws) ? lookUpKmer(ix, pat + ps.b(i)) : completeRange(ix);
+        RangePair init = (size >= ws) ? lookUpKmer(ix, pat, ps.b(i), rowWords) : completeRange(ix);
         ps.setEmr(i, matchString(ix, DIR_FWD, false, pat, start, ps.e(i), DIR_FWD, init, lc));
     }
     u32 lb = ps.b(P - 1), le = ps.e(P - 1);
     u32 size = le <= lb ? 0 : le - lb;
     u32 end = (size >= ws) ? le - ws : le;
-    RangePair init = (size >= ws) ? lookUpKmer(ix, pat + end) : completeRange(ix);
+    RangePair init = (size >= ws) ? lookUpKmer(ix, pat, end, rowWords) : completeRange(ix);
     ps.setEmr(P - 1, matchString(ix, DIR_BWD, true, pat, lb, end, DIR_BWD, init, lc));
 }
 
@@ -171,6 +238,7 @@ struct PartState {
     u32* patS;
     u32 patStride;
     const u8* pat;
+    u32 rowWords; // 8-byte words per code row
     u32 t, pSize, j;
     u32 stepping; // 1: greedy steps outstanding
 };
@@ -197,7 +265,7 @@ CLB_HD void dynSeed(const IndexView& ix, const DevStrategy& st, u32 P, PartState
     ps.b(P - 1) = pSize - wSize;
     ps.e(P - 1) = pSize;
     for (u32 i = 0; i < P; i++)
-        ps.setEmr(i, useK ? lookUpKmer(ix, pat + ps.b(i)) : rangeOfSingleChar(ix, pat[ps.b(i)]));
+        ps.setEmr(i, useK ? lookUpKmer(ix, pat, ps.b(i), S.rowWords) : rangeOfSingleChar(ix, pat[ps.b(i)]));
     u32 matched = P * (u32)wSize;
     if (matched == 0) { // seedIfNoKmers, :255-271
         u32 size = (pSize >= 4 * P) ? 4 : 1;
@@ -303,6 +371,7 @@ CLB_HD void loadParts(const PartInfo& pi, const PartScratch& ps, u32 P) {
 CLB_HD void partStart(const IndexView& ix, const DevStrategy& st, const Batch& B, u32 t, PartState& S, LocalCtr& lc) {
     S.t = t;
     S.pat = seqCodes(B, t);
+    S.rowWords = B.seqStride / 8;
     S.pSize = seqLen(B, t);
     S.stepping = 0;
     const u32 pSize = S.pSize;
@@ -343,7 +412,7 @@ CLB_HD void partStart(const IndexView& ix, const DevStrategy& st, const Batch& B
         ps.b(P - 1) = (u32)dmul(st.begins[P - 2], (double)(int)pSize);
         ps.e(P - 1) = pSize;
     }
-    calcExactRanges(ix, S.pat, P, ps, lc);
+    calcExactRanges(ix, S.pat, S.rowWords, P, ps, lc);
     storeParts(pi, ps, P);
 }
 // stage 1b: the greedy steps of a task seeded by partStart
