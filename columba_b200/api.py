@@ -47,7 +47,7 @@ class ClbError(RuntimeError):
 EXPORTS = ["clb_abi_version", "clb_device_count", "clb_index_load", "clb_index_free", "clb_index_text_length",
            "clb_index_num_seqs", "clb_index_seq_name", "clb_index_seq_start", "clb_index_device_bytes",
            "clb_ctx_create", "clb_ctx_free", "clb_last_error", "clb_ctx_set_strategy", "clb_ctx_set_options",
-           "clb_ctx_set_stream", "clb_ctx_supports_distance", "clb_ctx_num_parts", "clb_map_batch", "clb_map_batch_device", "clb_occ4",
+           "clb_ctx_set_stream", "clb_ctx_set_trim_max", "clb_ctx_supports_distance", "clb_ctx_num_parts", "clb_map_batch", "clb_map_batch_device", "clb_occ4",
            "clb_extend", "clb_find_sa", "clb_kmer_lookup", "clb_build_index"]
 
 _libs = {}
@@ -82,6 +82,7 @@ def load_library(path=None):
     lib.clb_ctx_set_strategy.argtypes = [vp, C.c_char_p, C.c_char_p, C.c_char_p]
     lib.clb_ctx_set_options.argtypes = [vp, C.c_int, C.c_int]
     lib.clb_ctx_set_stream.argtypes = [vp, vp]
+    lib.clb_ctx_set_trim_max.argtypes = [vp, C.c_int]
     lib.clb_ctx_supports_distance.argtypes = [vp, C.c_int]
     lib.clb_ctx_num_parts.argtypes = [vp, C.c_int]
     lib.clb_map_batch.argtypes = [vp, vp, vp, C.c_uint32, C.c_int, C.c_int, C.POINTER(ClbResult)]
@@ -204,6 +205,10 @@ class Mapper:
     def set_stream(self, cuda_stream):
         """cuda_stream: integer cudaStream_t handle (0/None: the context's own stream)."""
         self._check(self.lib.clb_ctx_set_stream(self.h, C.c_void_p(cuda_stream or None)))
+
+    def set_trim_max(self, largest_stratum):
+        """largestStratum of findSeqName (0: the batch's max_dist); BEST mode sets its cut-off."""
+        self._check(self.lib.clb_ctx_set_trim_max(self.h, int(largest_stratum)))
 
     def supports(self, k):
         return bool(self.lib.clb_ctx_supports_distance(self.h, k))

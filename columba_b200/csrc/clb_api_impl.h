@@ -145,6 +145,12 @@ int clb_ctx_set_options(clb_ctx* c, int metric, int partitioning) {
     c->opt.partStrategy = (clb::u32)partitioning;
     return CLB_OK;
 }
+int clb_ctx_set_trim_max(clb_ctx* c, int largest_stratum) {
+    if (!c || largest_stratum < 0 || largest_stratum > (int)clb::CLB_MAX_K)
+        return CLB_E_INVALID;
+    c->opt.trimMax = (clb::u32)largest_stratum;
+    return CLB_OK;
+}
 int clb_ctx_set_stream(clb_ctx* c, void* cuda_stream) {
     if (!c)
         return CLB_E_INVALID;

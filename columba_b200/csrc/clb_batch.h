@@ -139,6 +139,7 @@ struct Batch {
     u32 maxLen;            // longest read of the batch
     u32 k;                 // maximal distance
     u32 minD;              // minimal distance (BEST mode strata)
+    u32 trimMax;           // largest distance accepted when clipping at a sequence boundary (findSeqName's largestStratum)
     u32 metric;            // METRIC_*
     u32 partStrategy;      // PART_*
     u32 cigW;              // CIGAR slots per occurrence (2k+2)

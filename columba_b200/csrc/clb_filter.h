@@ -365,7 +365,7 @@ CLB_HD void txPerReadTask(const IndexView& ix, const Batch& B, u32 r, FilterScra
             if (pending)
                 lc.c[CIGARS_IN_INDEX]++; // computed by the reference, then superseded by the trimmed alignment
             u32 nb, ne;
-            const u32 largest = B.k;
+            const u32 largest = B.trimMax; // ALL mode: k; BEST mode: the cut-off (indexinterface.cpp:799-897)
             if ((ix.seqStart[index + 1] - o.b) <= largest) {
                 index++;
                 nb = ix.seqStart[index];

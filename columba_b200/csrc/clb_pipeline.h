@@ -56,6 +56,7 @@ struct MapOptions {
     u32 metric = METRIC_EDIT;
     u32 partStrategy = PART_DYNAMIC;
     u32 noCigar = 0;
+    u32 trimMax = 0; // largest distance of an alignment clipped at a sequence boundary (0: k); BEST mode: the cut-off
 };
 
 // host array that the backend allocates (page-locked on the GPU, so that the
@@ -144,7 +145,9 @@ template <typename BE> struct Pipeline {
         B.minD = opt.minD;
         B.metric = opt.metric;
         B.partStrategy = opt.partStrategy;
-        B.cigW = 2 * opt.k + 2;
+        const u32 kk = tmax<u32>(opt.k, opt.trimMax);
+        B.trimMax = kk;
+        B.cigW = 2 * kk + 2;
         B.noCigarFlag = opt.noCigar;
         const u32 T = 2 * R;
         // host reads go up in slices on the copy stream; the preparation kernel of a
@@ -282,7 +285,7 @@ template <typename BE> struct Pipeline {
             be.mark(STG_SEARCH);
         }
         // ---- stage 3
-        const u32 vRows = maxLen + 3 * opt.k + 8;
+        const u32 vRows = maxLen + 3 * kk + 8;
         {
             const bool wide = !use64(2 * opt.k + 1, opt.k);
             const u32 nw = be.workers(WK_VERIFY), ls = be.laneStride();

@@ -119,6 +119,12 @@ const char* clb_last_error(const clb_ctx*); /* ctx may be NULL: last error of in
  * data_dir: directory holding the built-in tables (columba_b200/schemes). */
 int clb_ctx_set_strategy(clb_ctx*, const char* kind, const char* arg, const char* data_dir);
 int clb_ctx_set_options(clb_ctx*, int metric, int partitioning);
+/* Largest distance accepted for an alignment that is clipped at a sequence
+ * boundary (largestStratum of IndexInterface::findSeqName,
+ * src/indexinterface.cpp:799-897): 0 = the batch's max_dist (ALL mode); BEST
+ * mode passes its cut-off (src/searchstrategy.cpp:537-568).  A clipped
+ * alignment can therefore have a distance above max_dist. */
+int clb_ctx_set_trim_max(clb_ctx*, int largest_stratum);
 /* Run this context's copies and kernels on the caller's CUDA stream
  * (cudaStream_t, e.g. torch.cuda.current_stream().cuda_stream) instead of the
  * context's own stream; NULL restores the own stream. */
