@@ -120,9 +120,8 @@ CLB_HD u32 findCigarFast(const IndexView& ix, const Batch& B, const PartSeq& ps,
     const u32 n = ps.len + 1, Wv = score, Wh = score, sh0 = K::DIAG_R0 - Wv;
     u64 HP = (~0ull) << K::LEFT, HN = ~HP;
     band[0] = bandPack(HP, 0, sh0);
-    u64 Mc[4];
-    for (u32 c = 0; c < 4; c++)
-        Mc[c] = matchVec<u64>(ps, 0, c);
+    u64 M0 = matchVec<u64>(ps, 0, 0), M1 = matchVec<u64>(ps, 0, 1), M2 = matchVec<u64>(ps, 0, 2),
+        M3 = matchVec<u64>(ps, 0, 3);
     u64 tcur = textWindow64(ix, b) << 2, tnxt = textWindow64(ix, b + K::BLOCK - 1);
     for (u32 i = 1; i <= refLen; i++) {
         const u32 l = i % K::BLOCK;
@@ -131,10 +130,12 @@ CLB_HD u32 findCigarFast(const IndexView& ix, const Batch& B, const PartSeq& ps,
             HN >>= K::BLOCK;
             tcur = tnxt;
             tnxt = textWindow64(ix, b + i + K::BLOCK - 1);
-            for (u32 c = 0; c < 4; c++)
-                Mc[c] = matchVec<u64>(ps, i / K::BLOCK, c);
+            M0 = matchVec<u64>(ps, i / K::BLOCK, 0);
+            M1 = matchVec<u64>(ps, i / K::BLOCK, 1);
+            M2 = matchVec<u64>(ps, i / K::BLOCK, 2);
+            M3 = matchVec<u64>(ps, i / K::BLOCK, 3);
         }
-        const u64 M = Mc[(u32)(tcur >> (2 * l)) & 3u];
+        const u64 M = pickM(M0, M1, M2, M3, (u32)(tcur >> (2 * l)) & 3u);
         const u64 D0 = bandRow(HP, HN, M);
         band[i] = bandPack(HP, M | ~D0, l + sh0);
     }

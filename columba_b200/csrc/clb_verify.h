@@ -160,6 +160,12 @@ CLB_HD u64 bandRow(u64& HP, u64& HN, u64 M) {
     HN = D0 & (VP << 1);
     return D0;
 }
+// match vector of character code y (0..3) out of four registers (a dynamically
+// indexed array would live in local memory)
+CLB_HD u64 pickM(u64 m0, u64 m1, u64 m2, u64 m3, u32 y) {
+    const u64 a = (y & 1u) ? m1 : m0, b = (y & 1u) ? m3 : m2;
+    return (y & 2u) ? b : a;
+}
 CLB_HD u64 bandPack(u64 HP, u64 X, u32 sh) { return (u64)(u32)(HP >> sh) | ((u64)(u32)(X >> sh) << 32); }
 
 // 64-bit fast path of verifyWindow: the row state (HP, HN, RAC, score) stays in
@@ -219,9 +225,8 @@ CLB_HD bool verifyWindowFast(const IndexView& ix, const Batch& B, u32 t, const B
         bs.cp[bs.cpStride] = HN;
         if (firstRow == 0)
             eds[0] = (u8)edAtCol(0);
-        u64 Mc[4];
-        for (u32 c = 0; c < 4; c++)
-            Mc[c] = matchVec<u64>(ps, 0, c);
+        u64 M0 = matchVec<u64>(ps, 0, 0), M1 = matchVec<u64>(ps, 0, 1), M2 = matchVec<u64>(ps, 0, 2),
+            M3 = matchVec<u64>(ps, 0, 3);
         // text of the rows of a block as one 64-bit window (row i <-> bits 2 * (i % 32));
         // the next block's window is fetched a block ahead, at the same iteration
         // in every lane
@@ -237,13 +242,15 @@ CLB_HD bool verifyWindowFast(const IndexView& ix, const Batch& B, u32 t, const B
                 HN >>= K::BLOCK;
                 RAC >>= K::BLOCK;
                 const u32 b = i / K::BLOCK;
-                for (u32 c = 0; c < 4; c++)
-                    Mc[c] = matchVec<u64>(ps, b, c);
+                M0 = matchVec<u64>(ps, b, 0);
+                M1 = matchVec<u64>(ps, b, 1);
+                M2 = matchVec<u64>(ps, b, 2);
+                M3 = matchVec<u64>(ps, b, 3);
                 bs.cp[(size_t)(2 * b) * bs.cpStride] = HP;
                 bs.cp[(size_t)(2 * b + 1) * bs.cpStride] = HN;
             }
             const u32 Y = (u32)(tcur >> (2 * l)) & 3u;
-            const u64 M = Mc[Y];
+            const u64 M = pickM(M0, M1, M2, M3, Y);
             const u64 D0 = bandRow(HP, HN, M);
             const u32 diagBit = l + K::DIAG_R0;
             score += (D0 >> diagBit) & 1ull ? 0u : 1u;
@@ -318,9 +325,8 @@ CLB_HD bool verifyWindowFast(const IndexView& ix, const Batch& B, u32 t, const B
         if (cb != ringBlock) {
             // rows of block cb again, from its checkpoint
             u64 hp = bs.cp[(size_t)(2 * cb) * bs.cpStride], hn = bs.cp[(size_t)(2 * cb + 1) * bs.cpStride];
-            u64 Mr[4];
-            for (u32 c = 0; c < 4; c++)
-                Mr[c] = matchVec<u64>(ps, cb, c);
+            const u64 R0 = matchVec<u64>(ps, cb, 0), R1 = matchVec<u64>(ps, cb, 1), R2 = matchVec<u64>(ps, cb, 2),
+                      R3 = matchVec<u64>(ps, cb, 3);
             u32 i0 = cb * K::BLOCK;
             if (cb == 0) {
                 bs.ring[0] = bandPack(hp, 0, sh0);
@@ -330,7 +336,7 @@ CLB_HD bool verifyWindowFast(const IndexView& ix, const Batch& B, u32 t, const B
             const u64 tw = (cb == 0) ? textWindow64(ix, start) << 2 : textWindow64(ix, start + cb * K::BLOCK - 1);
             for (u32 q = i0; q <= i1; q++) {
                 const u32 l = q % K::BLOCK;
-                const u64 M = Mr[(u32)(tw >> (2 * l)) & 3u];
+                const u64 M = pickM(R0, R1, R2, R3, (u32)(tw >> (2 * l)) & 3u);
                 const u64 D0 = bandRow(hp, hn, M);
                 bs.ring[(size_t)l * bs.ringStride] = bandPack(hp, M | ~D0, l + sh0);
             }
