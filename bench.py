@@ -378,8 +378,17 @@ def main():
         "text_filter": stats["TEXT_OCCS"] * (24 + 8) * 2 + counters["TOTAL_UNIQUE_MATCHES"] * 44,
     }
     achieved = alg[dom] / (stage[dom] / 1e3) / 1e9 if stage[dom] > 0 else 0.0
+    # dram__bytes_read.sum + dram__bytes_write.sum per launch of the stage's kernels, from the committed
+    # `ncu --set full` capture of this same command (profiles/r1_traffic.json; null when there is none)
+    traffic = None
+    try:
+        tj = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))
+        if tj.get("reads_per_step") == n and tj.get("ref_bp") == args.ref_bp:
+            traffic = tj["stage_dram_bytes"].get(dom)
+    except (OSError, ValueError, KeyError):
+        pass
     roofline = {"kernel": dom, "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                 "kernel_ms": stage[dom], "algorithmic_bytes": alg[dom],
                 "rank_lookups_per_s": stats["RANK_LOOKUPS"] / (ms_per_step / 1e3),
                 "rank_roofline_frac_of_8TBs": stats["RANK_LOOKUPS"] * 32 / (ms_per_step / 1e3) / 8e12}
