@@ -105,7 +105,10 @@ __global__ void __launch_bounds__(128) clb_kernel_stepped(const K k, u32 nMax, c
     bool have = false, done = false;
     for (;;) {
         const unsigned need = __ballot_sync(0xFFFFFFFFu, !have && !done);
-        if (need) {
+        const unsigned busy = __ballot_sync(0xFFFFFFFFu, have);
+        // start() and finish() run with only the refilling lanes: wait until a
+        // quarter of the warp is idle (or nothing is left to step)
+        if (need && (__popc(need) >= 8 || busy == 0)) {
             const int leader = __ffs(need) - 1;
             u32 base = 0;
             if ((int)lane == leader)
