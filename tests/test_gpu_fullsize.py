@@ -158,3 +158,83 @@ def test_sample_equals_reference(full):
         exp = orc.tuples(names, [reads[r].tobytes().decode() for r in idx], K)
     assert len(got) == len(exp)
     assert got == exp
+
+
+def test_hamming_250bp_k5_sample_equals_reference(full, cuda_lib):
+    """configs[4] shape on the 4.6 Mbp reference: 250 bp reads, Hamming distance
+    k = 5, custom pigeonhole scheme, dynamic partitioning; 200 000 reads on the
+    GPU, every 10th against the unmodified reference binary."""
+    import gen_data
+    import sam_tuples
+    if not os.path.exists(REF_DEV):
+        pytest.skip("reference binary did not travel")
+    n = 200_000
+    reads = gen_data.gen_reads_fast([full["text"]], n, 250, 250, "hamming", 5, over_e=7)
+    scheme = os.path.join(gu.GOLD, "schemes", "pigeon5")
+    m = cb.Mapper(full["ix"], ("custom", scheme), "hamming", "dynamic")
+    off = (np.arange(n + 1, dtype=np.int64) * 250).astype(np.uint32)
+    res = m.map_batch(reads.reshape(-1), off, 5)
+    assert res.counters["NUMBER_OF_READS"] == n
+    assert res.counters["MAPPED_READS"] >= 0.9 * n
+    idx = np.arange(0, n, 10)
+    names = ["r%d" % i for i in range(len(idx))]
+    got = []
+    for j, r in enumerate(idx):
+        s, c = int(res.read_start[r]), int(res.read_count[r])
+        for i in range(s, s + c):
+            o = res.occ[i]
+            got.append((names[j], 16 if o["strand"] else 0, full["ix"].seq_names[int(o["seq_id"])], int(o["pos"]) + 1,
+                        int(o["dist"]), cb.cigar_string(res.cigar[i, :int(o["n_cigar"])])))
+    got.sort()
+    fq = os.path.join(full["dir"], "sample_ham.fq")
+    gen_data.write_fastq_matrix(fq, reads[idx])
+    sam = os.path.join(full["dir"], "sample_ham.sam")
+    p = subprocess.run([REF_DEV, "-r", full["base"], "-f", fq, "-a", "all", "-m", "hamming", "-e", "5", "-c",
+                        scheme + "/", "-nD", "-t", str(os.cpu_count() or 1), "-o", sam], capture_output=True, text=True)
+    assert p.returncode == 0, p.stdout[-400:] + p.stderr[-400:]
+    exp = sam_tuples.sam_tuples(sam)
+    m.close()
+    assert len(got) == len(exp)
+    assert got == exp
+
+
+def test_best_mode_sample_equals_reference(full):
+    """BEST mode (minimal identity 95 %: strata up to k = 7) on 20 000 reads of the
+    bench batch against `columba -a best` of the unmodified reference."""
+    import gen_data
+    import sam_tuples
+    from columba_b200 import host
+    if not os.path.exists(REF_DEV):
+        pytest.skip("reference binary did not travel")
+    n = 20_000
+    reads = full["reads"][:n]
+    seqs = [reads[i].tobytes().decode() for i in range(n)]
+    names = ["r%d" % i for i in range(n)]
+    m = cb.Mapper(full["ix"])
+    occs, found = host.map_best(m, seqs, 95, 0)
+    m.close()
+    got = host.best_tuples(occs, found, names, full["ix"].seq_names)
+    fq = os.path.join(full["dir"], "sample_best.fq")
+    gen_data.write_fastq_matrix(fq, reads)
+    sam = os.path.join(full["dir"], "sample_best.sam")
+    p = subprocess.run([REF_DEV, "-r", full["base"], "-f", fq, "-a", "best", "-I", "95", "-t", str(os.cpu_count() or 1),
+                        "-o", sam], capture_output=True, text=True)
+    assert p.returncode == 0, p.stdout[-400:] + p.stderr[-400:]
+    exp = sam_tuples.sam_tuples(sam)
+    # the primary record among co-optimal alignments is the reference's choice; compare per read the
+    # distance, and the full tuple whenever the read has a single best alignment
+    eg = {t[0]: t for t in got}
+    ee = {t[0]: t for t in exp}
+    assert set(eg) == set(ee)
+    n_single = 0
+    for i, nm in enumerate(names):
+        if nm not in ee:
+            continue
+        assert eg[nm][4] == ee[nm][4], nm
+        if len(occs[i]) == 1:
+            assert eg[nm] == ee[nm], nm
+            n_single += 1
+        else:
+            cand = {(16 if o[0] else 0, full["ix"].seq_names[o[1]], o[2] + 1, o[5], o[6]) for o in occs[i]}
+            assert tuple(ee[nm][1:]) in cand, nm
+    assert n_single > 0.9 * len(ee)
