@@ -224,6 +224,66 @@ __global__ void __launch_bounds__(256) clb_scan_tiles(const u32* __restrict__ in
     }
 }
 
+// Cooperative sort of the long per-read segments of txIdx (same order as the
+// per-read kernel's own sort: TxLess is a total order).  A CTA looks at 256
+// reads at a time, collects the ones with more than TXBIG_MIN and at most
+// TXBIG_MAX occurrences and sorts each of them with a bitonic network in
+// shared memory (padded with sentinels to a power of two).
+static const u32 TXBIG_MIN = 64, TXBIG_MAX = 8192;
+__global__ void __launch_bounds__(256) clb_sort_big_segments(const Batch B, u32 R) {
+    __shared__ u32 keys[TXBIG_MAX];
+    __shared__ u32 big[256];
+    __shared__ u32 nBig;
+    TxLess less;
+    less.d = B.textOccs.data;
+    for (u32 base = blockIdx.x * 256; base < R; base += gridDim.x * 256) {
+        if (threadIdx.x == 0)
+            nBig = 0;
+        __syncthreads();
+        const u32 r = base + threadIdx.x;
+        if (r < R) {
+            const u32 n = B.txStart[r + 1] - B.txStart[r];
+            if (n > TXBIG_MIN && n <= TXBIG_MAX)
+                big[atomicAdd(&nBig, 1u)] = r;
+        }
+        __syncthreads();
+        const u32 nb = nBig;
+        for (u32 q = 0; q < nb; q++) {
+            const u32 rr = big[q];
+            u32* idx = B.txIdx + B.txStart[rr];
+            const u32 n = B.txStart[rr + 1] - B.txStart[rr];
+            u32 N = 1;
+            while (N < n)
+                N <<= 1;
+            for (u32 i = threadIdx.x; i < N; i += 256)
+                keys[i] = i < n ? idx[i] : 0xFFFFFFFFu;
+            __syncthreads();
+            for (u32 k = 2; k <= N; k <<= 1)
+                for (u32 j = k >> 1; j > 0; j >>= 1) {
+                    for (u32 i = threadIdx.x; i < N; i += 256) {
+                        const u32 l = i ^ j;
+                        if (l > i) {
+                            const u32 a = keys[i], b = keys[l];
+                            // sentinel = +infinity
+                            const bool ba = (a == 0xFFFFFFFFu) ? false : ((b == 0xFFFFFFFFu) ? false : less(b, a));
+                            const bool gt = (a == 0xFFFFFFFFu && b != 0xFFFFFFFFu) || ba; // a > b
+                            const bool asc = (i & k) == 0;
+                            if (gt == asc) {
+                                keys[i] = b;
+                                keys[l] = a;
+                            }
+                        }
+                    }
+                    __syncthreads();
+                }
+            for (u32 i = threadIdx.x; i < n; i += 256)
+                idx[i] = keys[i];
+            __syncthreads();
+        }
+        __syncthreads();
+    }
+}
+
 struct CudaBackend {
     int device;
     int numSMs = 0;
@@ -388,6 +448,13 @@ struct CudaBackend {
         CLB_CUDA(cudaGetLastError());
         launches++;
     }
+    u32 sortBigSegments(const Batch& B, u32 R) {
+        clb_sort_big_segments<<<(u32)numSMs * 4, 256, 0, stream>>>(B, R);
+        CLB_CUDA(cudaGetLastError());
+        launches++;
+        return TXBIG_MIN; // segments above TXBIG_MAX are left to the per-read kernel's own sort
+    }
+    u32 sortBigMax() const { return TXBIG_MAX; }
     void exclusiveScan(const u32* in, u32* out, u32 n) {
         const u32 nb = (n + SCAN_TILE - 1) / SCAN_TILE;
         if (nb > scanCap) {

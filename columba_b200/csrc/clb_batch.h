@@ -168,6 +168,7 @@ struct Batch {
     u32* txFill;    // R
     u32* txIdx;     // textOccs.cap
     u32* txTmp;     // textOccs.cap : merge-sort scratch
+    u32 txPresorted, txPresortedMax; // segments with (txPresorted, txPresortedMax] entries were sorted by the backend's cooperative sort
     u32* outCount;  // R+1 : surviving occurrences per read
     u32* outStart;  // R+1
     DevList<OutOcc> out;

@@ -294,7 +294,8 @@ CLB_HD void txPerReadTask(const IndexView& ix, const Batch& B, u32 r, FilterScra
     TextOccRec* d = B.textOccs.data;
     TxLess less;
     less.d = d;
-    heapSortIdx(idx, n, less);
+    if (n <= B.txPresorted || n > B.txPresortedMax) // the others: see Backend::sortBigSegments
+        heapSortIdx(idx, n, less);
     u32 m = 0;
     for (u32 i = 0; i < n; i++) {
         if (m > 0) {

@@ -6,6 +6,7 @@
 //   void* alloc(size_t), void free(void*), void zero(void*, size_t),
 //   void* hostAlloc(size_t), void hostFree(void*)  (result arrays on the host),
 //   void d2hAsync(dst, src, n) (completed by sync()),
+//   u32 sortBigSegments(B, R): sorts txIdx segments longer than the returned bound (0xFFFFFFFF: none),
 //   void copyBegin(), void copySlice(dst, src, n, slice), void copyWait(slice)  (host-to-device copies that
 //   overlap the kernels: slice s is usable by work launched after copyWait(s)),
 //   void h2d(void* dst, const void* src, size_t), void d2h(void* dst, const void* src, size_t),
@@ -322,6 +323,10 @@ template <typename BE> struct Pipeline {
             be.exclusiveScan(B.txCount, B.txStart, R);
             TxScatterKernel d2{B};
             be.launch(d2, capTx, &M->nTx, WK_LIGHT);
+            // reads inside repeats have thousands of occurrences: their segments are sorted
+            // by whole CTAs first (the per-read kernel sorts the small ones itself)
+            B.txPresorted = be.sortBigSegments(B, R);
+            B.txPresortedMax = be.sortBigMax();
             TxPerReadKernel d3{ix, B, (u8*)bSlabFilter.p, sb, vRows};
             be.launch(d3, R, nullptr, WK_FILTER);
             CigarJobKernel d4{ix, B, (u8*)bSlabFilter.p, sb, vRows};

@@ -25,6 +25,8 @@ struct HostEmuBackend {
     void h2d(void* d, const void* s, size_t n) { std::memcpy(d, s, n); }
     void d2h(void* d, const void* s, size_t n) { std::memcpy(d, s, n); }
     void sync() {}
+    u32 sortBigSegments(const Batch&, u32) { return 0xFFFFFFFFu; }
+    u32 sortBigMax() const { return 0xFFFFFFFFu; }
     void d2hAsync(void* d, const void* s, size_t n) { std::memcpy(d, s, n); }
     void copyBegin() {}
     void copySlice(void* d, const void* s, size_t n, u32) { std::memcpy(d, s, n); }
