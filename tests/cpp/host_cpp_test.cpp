@@ -1,0 +1,59 @@
+// Test program of the C++ host layer (include/columba_b200.hpp): maps a FASTQ
+// file in ALL or BEST mode and prints canonical tuples.  Linked against the
+// CUDA library on the GPU box and against the host emulation of the kernels
+// (same C ABI) in the CPU tests.
+//   host_cpp_test <index base> <fastq> <schemes dir> all <k> | best <min identity>
+#include <fstream>
+#include <iostream>
+
+#include "columba_b200.hpp"
+
+int main(int argc, char** argv) {
+    if (argc < 6) {
+        std::cerr << "usage: host_cpp_test base fastq schemes all|best value\n";
+        return 2;
+    }
+    try {
+        clb::FMIndex index(argv[1]);
+        clb::SearchStrategy strategy(index, "named", "columba", argv[3]);
+        std::vector<std::string> names, reads;
+        std::ifstream f(argv[2]);
+        std::string l1, l2, l3, l4;
+        while (std::getline(f, l1) && std::getline(f, l2) && std::getline(f, l3) && std::getline(f, l4)) {
+            names.push_back(l1.substr(1, l1.find_first_of(" \t") == std::string::npos ? std::string::npos
+                                                                                       : l1.find_first_of(" \t") - 1));
+            for (auto& c : l2)
+                c = (char)toupper(c);
+            reads.push_back(l2);
+        }
+        clb::Counters counters;
+        std::vector<std::vector<clb::TextOcc>> occ;
+        const std::string mode = argv[4];
+        const uint32_t v = (uint32_t)std::stoul(argv[5]);
+        if (mode == "all")
+            strategy.matchApproxBatch(reads, v, counters, occ);
+        else
+            strategy.matchBestBatch(reads, v, 0, counters, occ);
+        const auto& sn = index.getSeqNames();
+        for (size_t i = 0; i < reads.size(); i++) {
+            if (mode == "best" && !occ[i].empty()) { // the primary alignment: distance, then text order
+                auto best = std::min_element(occ[i].begin(), occ[i].end(), [](const clb::TextOcc& a, const clb::TextOcc& b) {
+                    if (a.distance != b.distance) return a.distance < b.distance;
+                    if (a.indexBegin != b.indexBegin) return a.indexBegin < b.indexBegin;
+                    return (a.end - a.begin) < (b.end - b.begin);
+                });
+                std::vector<clb::TextOcc> one(1, *best);
+                occ[i].swap(one);
+            }
+            for (const auto& t : occ[i])
+                std::cout << names[i] << '\t' << (t.strand == clb::REVERSE_C_STRAND ? 16 : 0) << '\t' << sn[t.seqID] << '\t'
+                          << t.begin + 1 << '\t' << t.distance << '\t' << t.cigar << '\n';
+        }
+        std::cerr << "reads " << counters.get(CLB_CTR_NUMBER_OF_READS) << " mapped " << counters.get(CLB_CTR_MAPPED_READS)
+                  << "\n";
+    } catch (std::exception& e) {
+        std::cerr << "error: " << e.what() << "\n";
+        return 1;
+    }
+    return 0;
+}
