@@ -13,6 +13,7 @@
 namespace clb {
 
 // per (read,strand) partitioning result: parts + exact ranges + chosen scheme
+// (the form the search kernel works with; in HBM it is kept as PartStore)
 struct PartInfo {
     u16 begin[MAXP];
     u16 end[MAXP];
@@ -20,9 +21,42 @@ struct PartInfo {
     u8 scheme; // index into DevStrategy::sc
     u8 valid;  // 0: read too short for partitioning
     u16 len;
+};
+// header of a (read,strand) in the PartStore
+struct PartHdr {
+    u16 len;
     u16 matched;  // characters matched by the seeding (dynamic partitioning)
+    u8 scheme;
+    u8 valid;
     u8 stepping;  // 1: the greedy steps of the dynamic partitioning are still to be done
     u8 pad;
+};
+// Partitioning results of all T (read,strand) sequences of a batch in HBM,
+// structure of arrays over t: the kernels of stage 1 run one thread per t, so
+// the lanes of a warp read and write consecutive elements (coalesced) instead
+// of one 328-byte record each.
+struct PartStore {
+    u32* be;        // [part * T + t] : begin | end << 16
+    RangePair* emr; // [part * T + t]
+    PartHdr* hdr;   // [t]
+    u32 T;
+    static CLB_HD size_t bytes(u32 T, u32 P) {
+        return (size_t)T * P * (sizeof(u32) + sizeof(RangePair)) + (size_t)T * sizeof(PartHdr) + 64;
+    }
+    CLB_HD PartInfo load(u32 t, u32 P) const {
+        PartInfo pi;
+        const PartHdr h = hdr[t];
+        pi.scheme = h.scheme;
+        pi.valid = h.valid;
+        pi.len = h.len;
+        for (u32 i = 0; i < P; i++) {
+            const u32 v = be[(size_t)i * T + t];
+            pi.begin[i] = (u16)v;
+            pi.end[i] = (u16)(v >> 16);
+            pi.emr[i] = emr[(size_t)i * T + t];
+        }
+        return pi;
+    }
 };
 
 // one search of the chosen scheme for one (read,strand)
@@ -149,7 +183,7 @@ struct Batch {
     u32 seqStride;
     u64* planes;           // 2R x 2 dirs x 4 chars x nw words
     u32 nw;
-    PartInfo* parts;
+    PartStore parts;
     // lists
     DevList<SearchTask> tasks;
     DevList<Cand> cands;

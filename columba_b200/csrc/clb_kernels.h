@@ -101,7 +101,7 @@ template <typename W> struct SearchKernel {
     }
     CLB_HD void run(State& s, u32 i) const {
         const SearchTask task = B.tasks.data[i];
-        const PartInfo& pi = B.parts[task.t];
+        const PartInfo pi = B.parts.load(task.t, st->P);
         const DevSearch& se = st->sc[pi.scheme].s[task.search];
         SearchCtx<W> X(ix, B, se, pi, s.sc, s.lc, task.t, task.search);
         s.lc.s[ST_SEARCH_TASKS]++;

@@ -347,18 +347,18 @@ CLB_HD bool dynStep(const IndexView& ix, const DevStrategy& st, u32 P, PartState
     return S.j >= S.pSize;
 }
 
-CLB_HD void storeParts(PartInfo& pi, const PartScratch& ps, u32 P) {
+CLB_HD void storeParts(const PartStore& st, u32 t, const PartScratch& ps, u32 P) {
     for (u32 i = 0; i < P; i++) {
-        pi.begin[i] = (u16)ps.b(i);
-        pi.end[i] = (u16)ps.e(i);
-        pi.emr[i] = ps.emr(i);
+        st.be[(size_t)i * st.T + t] = (ps.b(i) & 0xFFFFu) | (ps.e(i) << 16);
+        st.emr[(size_t)i * st.T + t] = ps.emr(i);
     }
 }
-CLB_HD void loadParts(const PartInfo& pi, const PartScratch& ps, u32 P) {
+CLB_HD void loadParts(const PartStore& st, u32 t, const PartScratch& ps, u32 P) {
     for (u32 i = 0; i < P; i++) {
-        ps.b(i) = pi.begin[i];
-        ps.e(i) = pi.end[i];
-        ps.setEmr(i, pi.emr[i]);
+        const u32 v = st.be[(size_t)i * st.T + t];
+        ps.b(i) = v & 0xFFFFu;
+        ps.e(i) = v >> 16;
+        ps.setEmr(i, st.emr[(size_t)i * st.T + t]);
     }
 }
 
@@ -376,26 +376,30 @@ CLB_HD void partStart(const IndexView& ix, const DevStrategy& st, const Batch& B
     S.stepping = 0;
     const u32 pSize = S.pSize;
     const u32 P = st.P;
-    PartInfo& pi = B.parts[t];
-    pi.len = (u16)pSize;
-    pi.valid = 0;
-    pi.scheme = 0;
+    PartHdr h;
+    h.len = (u16)pSize;
+    h.matched = 0;
+    h.scheme = 0;
+    h.valid = 0;
+    h.stepping = 0;
+    h.pad = 0;
     if (P >= pSize || P == 1) { // searchstrategy.cpp:141-156: no partitioning possible
         atomOr(B.err, ERR_SHORT_READ);
+        B.parts.hdr[t] = h;
         return;
     }
-    pi.valid = 1;
-    pi.stepping = 0;
-    pi.matched = 0;
+    h.valid = 1;
     const PartScratch& ps = S.ps;
     if (B.partStrategy == PART_DYNAMIC) {
         dynSeed(ix, st, P, S, lc);
         S.stepping = 1;
-        pi.stepping = 1;
-        pi.matched = (u16)S.j;
-        storeParts(pi, ps, P);
+        h.stepping = 1;
+        h.matched = (u16)S.j;
+        B.parts.hdr[t] = h;
+        storeParts(B.parts, t, ps, P);
         return;
     }
+    B.parts.hdr[t] = h;
     if (B.partStrategy == PART_UNIFORM) { // :194-209
         for (u32 i = 0; i < P; i++) {
             ps.b(i) = (u32)dmul(ddiv(dmul((double)(int)i, 1.0), (double)P), (double)pSize);
@@ -413,11 +417,11 @@ CLB_HD void partStart(const IndexView& ix, const DevStrategy& st, const Batch& B
         ps.e(P - 1) = pSize;
     }
     calcExactRanges(ix, S.pat, S.rowWords, P, ps, lc);
-    storeParts(pi, ps, P);
+    storeParts(B.parts, t, ps, P);
 }
 // stage 1b: the greedy steps of a task seeded by partStart
 CLB_HD void greedyStart(const DevStrategy& st, const Batch& B, u32 t, PartState& S) {
-    const PartInfo& pi = B.parts[t];
+    const PartHdr pi = B.parts.hdr[t];
     S.t = t;
     S.stepping = 0;
     if (!pi.valid || !pi.stepping)
@@ -436,15 +440,15 @@ CLB_HD void greedyStart(const DevStrategy& st, const Batch& B, u32 t, PartState&
             S.patS[j * S.patStride] = (u32)x;
         }
     }
-    loadParts(pi, S.ps, st.P);
+    loadParts(B.parts, t, S.ps, st.P);
     for (u32 i = 0; i < st.P; i++)
         S.ps.setKey(i, partKey(st, S.ps, st.P, i));
     S.stepping = 1;
 }
 CLB_HD void greedyFinish(const DevStrategy& st, const Batch& B, PartState& S) {
-    PartInfo& pi = B.parts[S.t];
+    PartHdr& pi = B.parts.hdr[S.t];
     if (pi.valid && pi.stepping) {
-        storeParts(pi, S.ps, st.P);
+        storeParts(B.parts, S.t, S.ps, st.P);
         pi.stepping = 0;
     }
 }
@@ -463,11 +467,11 @@ CLB_HD bool partStep(const IndexView& ix, const DevStrategy& st, PartState& S, L
 CLB_HD void partFinish(const IndexView& ix, const DevStrategy& st, const Batch& B, u32 t, PartState& S, LocalCtr& lc,
                        unsigned act) {
     const u32 P = st.P;
-    PartInfo& pi = B.parts[t];
+    PartHdr& pi = B.parts.hdr[t];
     const bool valid = pi.valid != 0;
     const PartScratch& ps = S.ps;
     if (valid)
-        loadParts(pi, ps, P);
+        loadParts(B.parts, t, ps, P);
     // slots for all immediate-switch candidates of the warp at once
     u32 nCand = 0;
     if (valid)

@@ -176,10 +176,13 @@ template <typename BE> struct Pipeline {
         B.nw = (maxLen + 63) / 64 + 1;
         bCodes.ensure(be, (size_t)T * B.seqStride);
         bPlanes.ensure(be, (size_t)T * 2 * 4 * B.nw * 8);
-        bParts.ensure(be, (size_t)T * sizeof(PartInfo));
+        bParts.ensure(be, PartStore::bytes(T, st.P));
         B.codes = (u8*)bCodes.p;
         B.planes = (u64*)bPlanes.p;
-        B.parts = (PartInfo*)bParts.p;
+        B.parts.T = T;
+        B.parts.emr = (RangePair*)bParts.p;
+        B.parts.be = (u32*)(B.parts.emr + (size_t)T * st.P);
+        B.parts.hdr = (PartHdr*)(B.parts.be + (size_t)T * st.P);
         const u32 P = st.P;
         u32 maxSearches = 0;
         for (u32 i = 0; i < st.nSchemes; i++)
