@@ -188,6 +188,9 @@ struct Batch {
     DevList<SearchTask> tasks;
     DevList<Cand> cands;
     DevList<u32> extra;    // candidates with more than one cluster centre (second verification pass)
+    u32* candStart;        // cands.cap : start of the verification window in the text (edit distance)
+    u32* candMult;         // cands.cap : number of candidates a unique candidate stands for
+    DevList<u32> uniq;     // candidates with distinct (sequence, window): the ones that are verified
     DevList<FMOccRec> fmOccs;
     DevList<TextOccRec> textOccs;
     u16* textCig;          // textOccs.cap x cigW

@@ -170,13 +170,34 @@ struct VerifyKernel {
             verifyEditTask(ix, B, B.extra.data[i], s.vs, s.lc, 1);
             return;
         }
-        s.lc.s[ST_CANDIDATES]++;
-        if (B.metric == METRIC_EDIT)
-            verifyEditTask(ix, B, i, s.vs, s.lc, 0);
-        else
+        if (B.metric == METRIC_EDIT) {
+            verifyEditTask(ix, B, B.uniq.data[i], s.vs, s.lc, 0);
+        } else {
+            s.lc.s[ST_CANDIDATES]++;
             verifyHammingTask(ix, B, i, s.lc);
+        }
     }
     CLB_HD void end(State& s) const { s.lc.flush(B.counters, B.stats); }
+};
+
+// stage 3a / 3b (edit distance)
+struct LocateKernel {
+    IndexView ix;
+    Batch B;
+    typedef WorkerCtr State;
+    CLB_HD void begin(State& s, u32) const { s.lc.clear(); }
+    CLB_HD void run(State& s, u32 i) const { locateTask(ix, B, i, s.lc); }
+    CLB_HD void end(State& s) const { s.lc.flush(B.counters, B.stats); }
+};
+struct DedupKernel {
+    Batch B;
+    u32 enable;
+    struct State {};
+    CLB_HD void begin(State&, u32) const {}
+    CLB_HD u32 total() const { return tmin(*B.cands.count, B.cands.cap); }
+    CLB_HD void run(State&, u32 i) const { dedupTask(B, i, total(), enable != 0, 1u); }
+    CLB_HD void run(State&, u32 i, unsigned act) const { dedupTask(B, i, total(), enable != 0, act); }
+    CLB_HD void end(State&) const {}
 };
 
 // grouping by read: count / scatter

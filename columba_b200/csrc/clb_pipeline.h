@@ -104,7 +104,7 @@ template <typename BE> struct MapResult {
 template <typename BE> struct Pipeline {
     BE& be;
     IndexView ix;
-    DevBuf<BE> bReads, bOff, bCodes, bPlanes, bParts, bTasks, bCands, bExtra, bFm, bTx, bTxCig, bOut, bOutCig, bCigJobs, bPerRead, bIdx,
+    DevBuf<BE> bReads, bOff, bCodes, bPlanes, bParts, bTasks, bCands, bCandAux, bExtra, bFm, bTx, bTxCig, bOut, bOutCig, bCigJobs, bPerRead, bIdx,
         bMisc, bSlabPart, bSlabSearch, bSlabVerify, bSlabVerifyWide, bSlabFilter, bStrategy;
     // list capacities (per read multipliers, grown after an overflow)
     double candPerRead = 24, fmPerRead = 4, txPerRead = 24, outPerRead = 8;
@@ -113,7 +113,7 @@ template <typename BE> struct Pipeline {
 
     Pipeline(BE& b) : be(b) {}
     ~Pipeline() {
-        DevBuf<BE>* all[] = {&bReads, &bOff, &bCodes, &bPlanes, &bParts, &bTasks, &bCands, &bExtra, &bFm, &bTx, &bTxCig, &bCigJobs, &bOut,
+        DevBuf<BE>* all[] = {&bReads, &bOff, &bCodes, &bPlanes, &bParts, &bTasks, &bCands, &bCandAux, &bExtra, &bFm, &bTx, &bTxCig, &bCigJobs, &bOut,
                              &bOutCig, &bPerRead, &bIdx, &bMisc, &bSlabPart, &bSlabSearch, &bSlabVerify, &bSlabVerifyWide, &bSlabFilter,
                              &bStrategy};
         for (auto* d : all)
@@ -125,7 +125,7 @@ template <typename BE> struct Pipeline {
         u64 counters[N_COUNTERS];
         u64 stats[N_STATS];
         u32 err;
-        u32 nTasks, nCands, nFm, nTx, nOut, nExtra, nCigJobs;
+        u32 nTasks, nCands, nFm, nTx, nOut, nExtra, nCigJobs, nUniq;
         u32 nT, nR; // 2R and R as device-side task counts
     };
 
@@ -200,6 +200,7 @@ template <typename BE> struct Pipeline {
                   capOut = capOf(outPerRead);
         bTasks.ensure(be, (size_t)capTasks * sizeof(SearchTask));
         bCands.ensure(be, (size_t)capCands * sizeof(Cand));
+        bCandAux.ensure(be, (size_t)capCands * 3 * sizeof(u32));
         const u32 capExtra = capCands / 4 + 1024;
         bExtra.ensure(be, (size_t)capExtra * sizeof(u32));
         bFm.ensure(be, (size_t)capFm * sizeof(FMOccRec));
@@ -218,6 +219,9 @@ template <typename BE> struct Pipeline {
         be.h2d(bMisc.p, &hm, sizeof(hm));
         B.tasks.data = (SearchTask*)bTasks.p; B.tasks.count = &M->nTasks; B.tasks.cap = capTasks;
         B.cands.data = (Cand*)bCands.p; B.cands.count = &M->nCands; B.cands.cap = capCands;
+        B.candStart = (u32*)bCandAux.p;
+        B.candMult = B.candStart + capCands;
+        B.uniq.data = B.candMult + capCands; B.uniq.count = &M->nUniq; B.uniq.cap = capCands;
         B.extra.data = (u32*)bExtra.p; B.extra.count = &M->nExtra; B.extra.cap = capExtra;
         B.fmOccs.data = (FMOccRec*)bFm.p; B.fmOccs.count = &M->nFm; B.fmOccs.cap = capFm;
         B.textOccs.data = (TextOccRec*)bTx.p; B.textOccs.count = &M->nTx; B.textOccs.cap = capTx;
@@ -299,7 +303,15 @@ template <typename BE> struct Pipeline {
             if (wide)
                 bSlabVerifyWide.ensure(be, wb * nw);
             VerifyKernel k3{ix, B, (u8*)bSlabVerify.p, gb, vRows, ls, wide ? (u8*)bSlabVerifyWide.p : (u8*)0, wb, 0};
-            be.launch(k3, capCands, &M->nCands, WK_VERIFY);
+            if (opt.metric == METRIC_EDIT) {
+                LocateKernel l1{ix, B};
+                be.launch(l1, capCands, &M->nCands, WK_LIGHT);
+                DedupKernel l2{B, wide ? 0u : 1u};
+                be.launch(l2, capCands, &M->nCands, WK_LIGHT);
+                be.launch(k3, capCands, &M->nUniq, WK_VERIFY);
+            } else {
+                be.launch(k3, capCands, &M->nCands, WK_VERIFY);
+            }
             if (opt.metric == METRIC_EDIT) { // remaining centres of the candidates that have several
                 VerifyKernel k3x = k3;
                 k3x.pass = 1;

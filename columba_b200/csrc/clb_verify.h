@@ -181,7 +181,7 @@ CLB_HD u64 bandPack(u64 HP, u64 X, u32 sh) { return (u64)(u32)(HP >> sh) | ((u64
 template <typename Sink>
 CLB_HD bool verifyWindowFast(const IndexView& ix, const Batch& B, u32 t, const BandStore& bs, u32 start, u32 end,
                              u32 nZeros, u32 maxED, u32 minED, u16* ops, u32 opsCap, LocalCtr& lc, bool& considered,
-                             Sink& sink, unsigned wm, u32 firstCentre, u32 maxCentres, u32& totalCentres) {
+                             Sink& sink, unsigned wm, u32 firstCentre, u32 maxCentres, u32& totalCentres, u32 mult) {
     typedef BPC<u64> K;
     const PartSeq ps = fullSeq(B, t);
     const u32 n = ps.len + 1;
@@ -380,7 +380,7 @@ CLB_HD bool verifyWindowFast(const IndexView& ix, const Batch& B, u32 t, const B
                 nops = 0xFFFFFFFFu;
             else
                 cigReverse(ops, nops);
-            lc.c[CIGARS_IN_TEXT_VERIFICATION]++;
+            lc.c[CIGARS_IN_TEXT_VERIFICATION] += mult;
             VerifyHit h;
             h.b = start + ti;
             h.e = start + r;
@@ -394,20 +394,58 @@ CLB_HD bool verifyWindowFast(const IndexView& ix, const Batch& B, u32 t, const B
     return nCentres > 0;
 }
 
-// stage 3 task (edit distance).  pass 0: the candidate's first cluster centre
+// stage 3a (edit distance): text position of a candidate -> start of its
+// verification window (getBeginPositions, fmindex.h:366-382)
+CLB_HD void locateTask(const IndexView& ix, const Batch& B, u32 ci, LocalCtr& lc) {
+    const Cand c = B.cands.data[ci];
+    const u32 pos = findSA(ix, c.row, lc.s[ST_LF_STEPS]);
+    const u32 sum = pos + c.add;
+    B.candStart[ci] = sum >= c.sub ? sum - c.sub : 0u;
+    lc.s[ST_CANDIDATES]++;
+}
+// stage 3b: the seeds of a read that lie on the same diagonal lead to the SAME
+// verification (same sequence, same window, same matrix): the reference runs
+// it once per seed, here the first candidate of such a group within an
+// aligned block of 32 candidates is verified once and stands for `mult` of
+// them in the counters (the duplicates would produce identical occurrences,
+// which the per-read filter removes anyway).
+CLB_HD void dedupTask(const Batch& B, u32 ci, u32 n, bool enable, unsigned act) {
+    const Cand c = B.cands.data[ci];
+    const u32 s = B.candStart[ci];
+    bool leader = true;
+    u32 mult = 1;
+    if (enable) {
+        const u32 b0 = ci & ~31u, b1 = tmin(b0 + 32u, n);
+        for (u32 j = b0; j < b1; j++) {
+            if (j == ci)
+                continue;
+            const Cand o = B.cands.data[j];
+            const bool same = o.t == c.t && B.candStart[j] == s && o.fixedStart == c.fixedStart && o.maxED == c.maxED &&
+                              o.minED == c.minED;
+            if (same && j < ci)
+                leader = false;
+            mult += (same && j > ci) ? 1u : 0u;
+        }
+    }
+    const u32 at = B.uniq.warpReserve(leader ? 1u : 0u, act, B.err, ERR_CAND_OVERFLOW);
+    if (leader && at != 0xFFFFFFFFu) {
+        B.uniq.data[at] = ci;
+        B.candMult[ci] = mult;
+    }
+}
+
+// stage 3c task (edit distance).  pass 0: the candidate's first cluster centre
 // (all of them on the 128-bit path); candidates with more centres go to the
 // `extra` list, whose entries pass 1 verifies again for the remaining centres.
 CLB_HD void verifyEditTask(const IndexView& ix, const Batch& B, u32 ci, VerifyScratch& vs, LocalCtr& lc, u32 pass) {
     const Cand c = B.cands.data[ci];
-    u64 lfDummy = 0;
-    u32 pos = findSA(ix, c.row, pass == 0 ? lc.s[ST_LF_STEPS] : lfDummy);
-    u32 sum = pos + c.add;
-    u32 start = sum >= c.sub ? sum - c.sub : 0u;
+    const u32 start = B.candStart[ci];
+    const u32 mult = B.candMult[ci];
     const u32 maxED = c.maxED, minED = c.minED;
     const u32 nZeros = c.fixedStart ? 1u : 2 * maxED + 1;
     const u32 len = seqLen(B, c.t);
     if (pass == 0)
-        lc.c[IN_TEXT_STARTED]++;
+        lc.c[IN_TEXT_STARTED] += mult;
     const u32 first = pass == 0 ? 0u : 1u;
     CandSink sink(B, c, first);
     bool considered = true, ok;
@@ -419,16 +457,16 @@ CLB_HD void verifyEditTask(const IndexView& ix, const Batch& B, u32 ci, VerifySc
     if (fast) {
         u32 total = 0;
         ok = verifyWindowFast(ix, B, c.t, vs.bs, start, end, nZeros, maxED, minED, vs.ops, B.cigW, lc, considered,
-                              sink, fm, first, pass == 0 ? 1u : 0xFFFFu, total);
+                              sink, fm, first, pass == 0 ? 1u : 0xFFFFu, total, mult);
         if (pass == 0 && total > 1)
             B.extra.push(ci, B.err, ERR_CAND_OVERFLOW);
-    } else {
+    } else { // (mult is 1: no grouping when 128-bit matrices can occur)
         ok = verifyWindow<u128>(ix, B, c.t, (Row<u128>*)vs.rows, start, end, nZeros, maxED, minED, vs.ops, B.cigW, lc,
                                 considered, sink);
     }
     if (pass == 0 && !ok && considered)
-        lc.c[ABORTED_IN_TEXT_VERIF]++;
-    lc.c[TOTAL_REPORTED_POSITIONS] += sink.sub - first;
+        lc.c[ABORTED_IN_TEXT_VERIF] += mult;
+    lc.c[TOTAL_REPORTED_POSITIONS] += (u64)(sink.sub - first) * mult;
     lc.s[ST_TEXT_OCCS] += sink.sub - first;
 }
 
