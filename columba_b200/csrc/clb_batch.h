@@ -117,8 +117,33 @@ template <typename T> struct DevList {
     T* data;
     u32* count; // device counter
     u32 cap;
+    // slots for the lanes of a warp that happen to arrive together come from one
+    // atomic (every list has ONE counter: millions of single atomics on it would
+    // serialise in the L2)
+    CLB_HD u32 grab(u32 n) const {
+#if defined(__CUDA_ARCH__)
+        const unsigned m = __match_any_sync(__activemask(), (unsigned long long)count);
+        const int lane = threadIdx.x & 31, leader = __ffs(m) - 1;
+        u32 off = 0, total = 0;
+        for (unsigned mm = m; mm; mm &= mm - 1) {
+            const int b = __ffs(mm) - 1;
+            const u32 v = __shfl_sync(m, n, b);
+            total += v;
+            off += (b < lane) ? v : 0u;
+        }
+        u32 base = 0;
+        if (lane == leader && total)
+            base = atomicAdd(count, total);
+        base = __shfl_sync(m, base, leader);
+        return base + off;
+#else
+        u32 o = *count;
+        *count = o + n;
+        return o;
+#endif
+    }
     CLB_HD u32 push(const T& v, u32* err, u32 errBit) const {
-        u32 i = atomAdd<u32>(count, 1u);
+        u32 i = grab(1u);
         if (i >= cap) {
             atomOr(err, errBit);
             return 0xFFFFFFFFu;
@@ -156,7 +181,7 @@ template <typename T> struct DevList {
     }
     // reserve n consecutive slots; returns first index or 0xFFFFFFFF
     CLB_HD u32 reserve(u32 n, u32* err, u32 errBit) const {
-        u32 i = atomAdd<u32>(count, n);
+        u32 i = grab(n);
         if (i + n > cap || i + n < i) {
             atomOr(err, errBit);
             return 0xFFFFFFFFu;

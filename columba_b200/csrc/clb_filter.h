@@ -283,18 +283,18 @@ struct TrimSink {
 };
 
 // stage 6 task: filter the text occurrences of read r and write the output
-CLB_HD void txPerReadTask(const IndexView& ix, const Batch& B, u32 r, FilterScratch& fs, LocalCtr& lc) {
+// `act`: the lanes of the warp that run this function side by side (they meet
+// again before the output slots are reserved, so that one atomic serves them all)
+CLB_HD void txPerReadTask(const IndexView& ix, const Batch& B, u32 r, FilterScratch& fs, LocalCtr& lc, unsigned act) {
     const u32 s0 = B.txStart[r], s1 = B.txStart[r + 1];
     B.outStart[r] = 0;
     B.outCount[r] = 0;
-    if (s1 == s0)
-        return;
     u32* idx = B.txIdx + s0;
     const u32 n = s1 - s0;
     TextOccRec* d = B.textOccs.data;
     TxLess less;
     less.d = d;
-    if (n <= B.txPresorted || n > B.txPresortedMax) // the others: see Backend::sortBigSegments
+    if (n > 1 && (n <= B.txPresorted || n > B.txPresortedMax)) // the others: see Backend::sortBigSegments
         heapSortIdx(idx, n, less);
     u32 m = 0;
     for (u32 i = 0; i < n; i++) {
@@ -328,8 +328,9 @@ CLB_HD void txPerReadTask(const IndexView& ix, const Batch& B, u32 r, FilterScra
             idx[nOut++] = idx[i];
         }
     }
+    warpSync(act);
     u32 at = B.out.reserve(nOut, B.err, ERR_OUT_OVERFLOW);
-    if (at == 0xFFFFFFFFu)
+    if (at == 0xFFFFFFFFu || nOut == 0)
         return;
     u32 w = 0;
     for (u32 i = 0; i < nOut; i++) {

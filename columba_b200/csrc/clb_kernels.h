@@ -266,8 +266,9 @@ struct TxPerReadKernel {
     u32 rowsCap;
     typedef FilterState State;
     CLB_HD void begin(State& s, u32 worker) const { carveFilter(s, slabs + (size_t)worker * slabBytes, B.cigW, rowsCap); }
-    CLB_HD void run(State& s, u32 r) const {
-        txPerReadTask(ix, B, r, s.fs, s.lc);
+    CLB_HD void run(State& s, u32 r) const { run(s, r, 1u); }
+    CLB_HD void run(State& s, u32 r, unsigned act) const {
+        txPerReadTask(ix, B, r, s.fs, s.lc, act);
         u32 n = B.outCount[r];
         if (n) {
             s.lc.c[MAPPED_READS]++;
