@@ -71,55 +71,98 @@ CLB_HD u32 asciiCodeFast(u32 c) {
     return ok ? (((c >> 1) ^ (c >> 2)) & 3u) : 4u;
 }
 
+// Four characters per 32-bit word (SWAR).  nzBytes: 0x80 in every byte of z
+// that is not zero (exact, no carries between bytes).
+CLB_HD u32 nzBytes(u32 z) { return (((z & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | z) & 0x80808080u; }
+// code2: per byte the 2-bit code of A/C/G/T (either case); valid: 0x80 in every
+// byte that holds one of ACGTacgt (same mapping as asciiCodeFast)
+CLB_HD void asciiCodes4(u32 w, u32& code2, u32& valid) {
+    const u32 u = w & 0xDFDFDFDFu;
+    code2 = ((w >> 1) ^ (w >> 2)) & 0x03030303u;
+    const u32 bad = nzBytes(u ^ 0x41414141u) & nzBytes(u ^ 0x43434343u) & nzBytes(u ^ 0x47474747u) &
+                    nzBytes(u ^ 0x54545454u);
+    valid = bad ^ 0x80808080u;
+}
+// the four byte-LSBs of x as a nibble at bit 4 * slot of a 32-bit word
+// (x * 0x00204081 puts bit 8i at 21 + i; the partial products do not overlap)
+CLB_HD u32 gatherNibble(u32 x, int slot) {
+    const u32 t = x * 0x00204081u;
+    const int sh = 4 * slot;
+    return (sh <= 21 ? (t >> (21 - sh)) : (t << (sh - 21))) & (0xFu << sh);
+}
+CLB_HD u32 byteRev32(u32 v) {
+#if defined(__CUDA_ARCH__)
+    return __byte_perm(v, 0, 0x0123);
+#else
+    return __builtin_bswap32(v);
+#endif
+}
+CLB_HD u64 bitRev64(u64 v) {
+#if defined(__CUDA_ARCH__)
+    return ((u64)__brev((u32)v) << 32) | (u64)__brev((u32)(v >> 32));
+#else
+    u64 r = 0;
+    for (int i = 0; i < 64; i++)
+        r |= ((v >> i) & 1ull) << (63 - i);
+    return r;
+#endif
+}
+// 64 characters (16 words): bit i of lo / hi / ok = code bit 0 / code bit 1 /
+// "is ACGT" of character i; cw = codes as bytes (4 = not ACGT), cmp = the same
+// for the complemented codes
+template <bool complement> CLB_HD void codes64(const u32 U[16], u64& lo, u64& hi, u64& ok, u32 cw[16]) {
+    u32 l[2] = {0, 0}, h[2] = {0, 0}, v[2] = {0, 0};
+#pragma unroll
+    for (int m = 0; m < 16; m++) {
+        u32 c2, val;
+        asciiCodes4(U[m], c2, val);
+        const u32 vb = val >> 7;
+        l[m >> 3] |= gatherNibble(c2 & 0x01010101u, m & 7);
+        h[m >> 3] |= gatherNibble((c2 >> 1) & 0x01010101u, m & 7);
+        v[m >> 3] |= gatherNibble(vb, m & 7);
+        const u32 code = complement ? (c2 ^ 0x03030303u) : c2;
+        cw[m] = (code & (vb * 3u)) | ((val ^ 0x80808080u) >> 5);
+    }
+    lo = (u64)l[0] | ((u64)l[1] << 32);
+    hi = (u64)h[0] | ((u64)h[1] << 32);
+    ok = (u64)v[0] | ((u64)v[1] << 32);
+}
+
 // stage 0: codes of both strands of a read (strand 1 = reverse complement,
 // nucleotide.h) and their "equals A/C/G/T" bit planes, forward and reversed.
 // One task = 64 characters of one read: the planes of the reverse complement
 // are the complement-swapped planes of the read, so both strands come out of
-// one pass; codes are written as 8-byte words, planes from registers.
+// one pass.  Four characters per instruction: codes and validity per 32-bit
+// word, code bits gathered into 64-bit masks, planes derived from the masks.
 CLB_HD void prepTask(const Batch& B, u32 task, u32 firstRead) {
     const u32 nc = B.nw - 1; // chunks of 64 characters
     const u32 r = firstRead + task / nc, j = task % nc;
     const u32 off = B.readOff[r], len = B.readOff[r + 1] - off;
     const u32 t0 = 2 * r, t1 = 2 * r + 1;
     const u8* rd = B.readsAscii + off;
-    u64 P0 = 0, P1 = 0, P2 = 0, P3 = 0, Q0 = 0, Q1 = 0, Q2 = 0, Q3 = 0;
     u64* c0 = (u64*)(B.codes + (size_t)t0 * B.seqStride);
     u64* c1 = (u64*)(B.codes + (size_t)t1 * B.seqStride);
     const u32 words = B.seqStride / 8;
-    u32 F[16], G[16];
+    u32 F[16], G[16], cf[16], cg[16];
     loadWindow64(rd, (i32)(64 * j), len, F);                   // read[64j + i]
     loadWindow64(rd, (i32)len - 64 - (i32)(64 * j), len, G);   // G byte 63 - i = read[len - 1 - (64j + i)]
+    u64 lo, hi, ok, glo, ghi, gok;
+    codes64<false>(F, lo, hi, ok, cf);
+    codes64<true>(G, glo, ghi, gok, cg);
+    glo = bitRev64(glo);
+    ghi = bitRev64(ghi);
+    gok = bitRev64(gok);
+    const u64 P[4] = {ok & ~hi & ~lo, ok & ~hi & lo, ok & hi & ~lo, ok & hi & lo};
+    const u64 Q[4] = {gok & ~ghi & ~glo, gok & ~ghi & glo, gok & ghi & ~glo, gok & ghi & glo};
 #pragma unroll
     for (int w = 0; w < 8; w++) {
-        u64 w0 = 0, w1 = 0;
-#pragma unroll
-        for (int q = 0; q < 8; q++) {
-            const int i = 8 * w + q;
-            const bool in = 64 * j + (u32)i < len;
-            const u32 fa = (F[i >> 2] >> (8 * (i & 3))) & 0xFFu;
-            const u32 gb = (G[(63 - i) >> 2] >> (8 * ((63 - i) & 3))) & 0xFFu;
-            const u32 a = in ? asciiCodeFast(fa) : 4u;
-            u32 b = in ? asciiCodeFast(gb) : 4u;
-            const u64 bit = 1ull << i;
-            P0 |= (a == 0) ? bit : 0ull;
-            P1 |= (a == 1) ? bit : 0ull;
-            P2 |= (a == 2) ? bit : 0ull;
-            P3 |= (a == 3) ? bit : 0ull;
-            Q0 |= (b == 0) ? bit : 0ull;
-            Q1 |= (b == 1) ? bit : 0ull;
-            Q2 |= (b == 2) ? bit : 0ull;
-            Q3 |= (b == 3) ? bit : 0ull;
-            b = (b < 4) ? 3 - b : 4u;
-            w0 |= (u64)a << (8 * q);
-            w1 |= (u64)b << (8 * q);
-        }
         const u32 wi = 8 * j + (u32)w;
         if (wi < words) {
-            c0[wi] = w0;
-            c1[wi] = w1;
+            c0[wi] = (u64)cf[2 * w] | ((u64)cf[2 * w + 1] << 32);
+            // bytes q = 0..7 of the reverse complement = G bytes 63 - 8w - q
+            c1[wi] = (u64)byteRev32(cg[15 - 2 * w]) | ((u64)byteRev32(cg[14 - 2 * w]) << 32);
         }
     }
-    const u64 P[4] = {P0, P1, P2, P3}, Q[4] = {Q0, Q1, Q2, Q3};
     u64* p0f = B.planes + ((size_t)t0 * 2 + DIR_FWD) * 4 * B.nw;
     u64* p0b = B.planes + ((size_t)t0 * 2 + DIR_BWD) * 4 * B.nw;
     u64* p1f = B.planes + ((size_t)t1 * 2 + DIR_FWD) * 4 * B.nw;
