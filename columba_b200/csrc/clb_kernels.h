@@ -30,7 +30,7 @@ struct PartBase {
     Batch B;
     u32 P;       // parts (st->P, known to the host)
     u8* slabs;   // scratch of the workers when there is no shared memory (host emulation), else null
-    u32 patWords; // words per worker for the sequence as 4-bit codes in shared memory (0: not staged)
+    u32 patWords; // words per worker for the sequence as 2-bit codes in shared memory (0: not staged)
 };
 struct PartWorkerState {
     LocalCtr lc;
@@ -43,17 +43,15 @@ struct PartWorkerState {
         return (PartScratch::bytesPerWorker(a.P) + (size_t)a.patWords * sizeof(u32)) * nThreads;               \
     }                                                                                                          \
     CLB_HD void bindShared(State& s, u8* smem, u32 tid, u32 nThreads) const {                                  \
-        s.ps.ps.w = (u32*)smem + tid;                                                                          \
-        s.ps.ps.stride = nThreads;                                                                             \
-        s.ps.patS = a.patWords ? (u32*)smem + (size_t)a.P * 8 * nThreads + tid : (u32*)0;                      \
+        s.ps.ps.bind(smem, nThreads, tid, a.P);                                                                \
+        s.ps.patS = a.patWords ? (u32*)smem + (size_t)a.P * 7 * nThreads + tid : (u32*)0;                      \
         s.ps.patStride = nThreads;                                                                             \
     }                                                                                                          \
     CLB_HD void begin(State& s, u32 worker) const {                                                            \
         s.lc.clear();                                                                                          \
         s.ps.patS = (u32*)0;                                                                                   \
         s.ps.patStride = 1;                                                                                    \
-        s.ps.ps.w = a.slabs ? (u32*)(a.slabs + (size_t)worker * PartScratch::bytesPerWorker(a.P)) : (u32*)0;   \
-        s.ps.ps.stride = 1;                                                                                    \
+        s.ps.ps.bind(a.slabs ? a.slabs + (size_t)worker * PartScratch::bytesPerWorker(a.P) : (u8*)0, 1, 0, a.P); \
     }                                                                                                          \
     CLB_HD void end(State& s) const { s.lc.flush(a.B.counters, a.B.stats); }
 

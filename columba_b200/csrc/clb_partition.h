@@ -223,33 +223,71 @@ CLB_HD RangePair matchString(const IndexView& ix, int dir, bool uni, const u8* p
     return r;
 }
 
-// Working state of one partitioning task: per part begin, end, exact range
-// (4 words) and greedy key (2 words) = 8 words, element j of a worker at
-// w[j * stride].  On the GPU w points into shared memory (stride = threads per
-// CTA: conflict free, and no local-memory traffic through L2); the host
+// Working state of one partitioning task: per part the exact range (16 B), the
+// greedy key (8 B) and begin / end (2 x 2 B).  The workers of a group (the
+// threads of a CTA; 1 in the host emulation) interleave element-wise in three
+// arrays [P x stride] so that a range is ONE 128-bit and a key or a begin/end
+// ONE 64-bit (begin/end: 32-bit) shared-memory access without bank conflicts.  On the GPU the
+// region is shared memory (no local-memory traffic through L2); the host
 // emulation uses a slab.
 struct PartScratch {
-    u32* w;
+    u8* em;  // RangePair of part i at em + i * stride * 16
+    u8* kq;  // key at kq + i * stride * 8
+    u8* be;  // (begin, end) as two u16 at be + i * stride * 4
     u32 stride;
-    CLB_HD u32& at(u32 i, u32 f) const {
-#if defined(__CUDA_ARCH__)
-        __builtin_assume(__isShared(w)); // the CUDA backend always binds shared memory: LDS/STS, 32-bit addresses
-#endif
-        return w[(i * 8 + f) * stride];
+    CLB_HD void bind(u8* base, u32 nWorkers, u32 slot, u32 P) {
+        stride = nWorkers;
+        em = base + (size_t)slot * 16;
+        kq = base + (size_t)P * nWorkers * 16 + (size_t)slot * 8;
+        be = base + (size_t)P * nWorkers * 24 + (size_t)slot * 4;
     }
-    CLB_HD u32& b(u32 i) const { return at(i, 0); }
-    CLB_HD u32& e(u32 i) const { return at(i, 1); }
-    CLB_HD RangePair emr(u32 i) const { return mkPair(at(i, 2), at(i, 3), at(i, 4), at(i, 5)); }
+    CLB_HD u32* emW(u32 i) const {
+#if defined(__CUDA_ARCH__)
+        __builtin_assume(__isShared(em)); // the CUDA backend always binds shared memory: LDS/STS, 32-bit addresses
+#endif
+        return (u32*)(em + i * stride * 16u);
+    }
+    CLB_HD u32* keyW(u32 i) const {
+#if defined(__CUDA_ARCH__)
+        __builtin_assume(__isShared(kq));
+#endif
+        return (u32*)(kq + i * stride * 8u);
+    }
+    CLB_HD u16* beW(u32 i) const {
+#if defined(__CUDA_ARCH__)
+        __builtin_assume(__isShared(be));
+#endif
+        return (u16*)(be + i * stride * 4u);
+    }
+    CLB_HD u16& b(u32 i) const { return beW(i)[0]; }
+    CLB_HD u16& e(u32 i) const { return beW(i)[1]; }
+    // begin in the low, end in the high half
+    CLB_HD u32 be32(u32 i) const { return *(const u32*)beW(i); }
+    CLB_HD RangePair emr(u32 i) const {
+#if defined(__CUDA_ARCH__)
+        const uint4 v = *(const uint4*)emW(i);
+        return mkPair(v.x, v.y, v.z, v.w);
+#else
+        const u32* w = emW(i);
+        return mkPair(w[0], w[1], w[2], w[3]);
+#endif
+    }
     CLB_HD void setEmr(u32 i, const RangePair& r) const {
-        at(i, 2) = r.sa.b; at(i, 3) = r.sa.e; at(i, 4) = r.rev.b; at(i, 5) = r.rev.e;
+#if defined(__CUDA_ARCH__)
+        *(uint4*)emW(i) = make_uint4(r.sa.b, r.sa.e, r.rev.b, r.rev.e);
+#else
+        u32* w = emW(i);
+        w[0] = r.sa.b; w[1] = r.sa.e; w[2] = r.rev.b; w[3] = r.rev.e;
+#endif
     }
     CLB_HD u32 width(u32 i) const {
-        const u32 sb = at(i, 2), se = at(i, 3);
+        const u64 v = *(const u64*)emW(i); // sa.b, sa.e
+        const u32 sb = (u32)v, se = (u32)(v >> 32);
         return se <= sb ? 0u : se - sb;
     }
-    CLB_HD u64 key(u32 i) const { return (u64)at(i, 6) | ((u64)at(i, 7) << 32); }
-    CLB_HD void setKey(u32 i, u64 k) const { at(i, 6) = (u32)k; at(i, 7) = (u32)(k >> 32); }
-    static CLB_HD size_t bytesPerWorker(u32 P) { return (size_t)P * 8 * sizeof(u32); }
+    CLB_HD u64 key(u32 i) const { return *(const u64*)keyW(i); }
+    CLB_HD void setKey(u32 i, u64 k) const { *(u64*)keyW(i) = k; }
+    static CLB_HD size_t bytesPerWorker(u32 P) { return (size_t)P * 28; }
 };
 
 CLB_HD void calcExactRanges(const IndexView& ix, const u8* pat, u32 rowWords, u32 P, const PartScratch& ps,
@@ -276,10 +314,12 @@ CLB_HD void calcExactRanges(const IndexView& ix, const u8* pat, u32 rowWords, u3
 // task while the other lanes keep stepping.
 struct PartState {
     PartScratch ps;
-    // the sequence as 4-bit codes, 8 per word, in shared memory (word j at
-    // patS[j * patStride]); null: read the byte codes from global memory
+    // the sequence as 2-bit codes, 16 per word, in shared memory (word j at
+    // patS[j * patStride]); null, or patN set (the sequence holds a character
+    // other than ACGT): read the byte codes from global memory
     u32* patS;
     u32 patStride;
+    u32 patN;
     const u8* pat;
     u32 rowWords; // 8-byte words per code row
     u32 t, pSize, j;
@@ -351,9 +391,10 @@ CLB_HD bool dynStep(const IndexView& ix, const DevStrategy& st, u32 P, PartState
         }
         return true;
     }
-    const u32 pb = ps.b(p), pe = ps.e(p);
     const u32 pl = (p == 0) ? 0 : p - 1, pr = (p == P - 1) ? p : p + 1;
-    const u32 el = ps.e(pl), br = ps.b(pr); // end of the left / begin of the right neighbour
+    const u32 beP = ps.be32(p), beL = ps.be32(pl), beR = ps.be32(pr);
+    const u32 pb = beP & 0xFFFFu, pe = beP >> 16;
+    const u32 el = beL >> 16, br = beR & 0xFFFFu; // end of the left / begin of the right neighbour
     const bool noL = (p == 0) || pb == el;
     const bool noR = (p == P - 1) || pe == br;
     // both neighbours exist when neither side is closed
@@ -362,16 +403,16 @@ CLB_HD bool dynStep(const IndexView& ix, const DevStrategy& st, u32 P, PartState
     const bool fwd = (dir == DIR_FWD);
     const u32 cpos = fwd ? pe : pb - 1;
     u32 c;
-    if (S.patS) {
+    if (S.patS && !S.patN) {
 #if defined(__CUDA_ARCH__)
         __builtin_assume(__isShared(S.patS));
 #endif
-        c = (S.patS[(cpos >> 3) * S.patStride] >> ((cpos & 7) * 4)) & 15u;
+        c = (S.patS[(cpos >> 4) * S.patStride] >> ((cpos & 15) * 2)) & 3u;
     } else {
         c = S.pat[cpos];
     }
     const u32 nb = fwd ? pb : pb - 1, ne = fwd ? pe + 1 : pe;
-    ps.at(p, fwd ? 1u : 0u) = fwd ? ne : nb;
+    ps.beW(p)[fwd ? 1 : 0] = (u16)(fwd ? ne : nb);
     RangePair r = ps.emr(p);
     addChar(ix, dir, p == P - 1, c, r, lc);
     ps.setEmr(p, r);
@@ -383,7 +424,9 @@ CLB_HD bool dynStep(const IndexView& ix, const DevStrategy& st, u32 P, PartState
     const u32 q = fwd ? pr : pl;
     const bool touch = fwd ? (p != P - 1 && ne == br) : (p != 0 && nb == el);
     const u32 q2 = fwd ? ((q == P - 1) ? q : q + 1) : ((q == 0) ? q : q - 1); // the neighbour's other neighbour
-    const bool closed = fwd ? (q == P - 1 || ps.e(q) == ps.b(q2)) : (q == 0 || ps.b(q) == ps.e(q2));
+    const u32 beQ2 = ps.be32(q2);
+    // (q != p whenever `touch` holds, so the neighbour's begin / end read above are current)
+    const bool closed = fwd ? (q == P - 1 || (beR >> 16) == (beQ2 & 0xFFFFu)) : (q == 0 || (beL & 0xFFFFu) == (beQ2 >> 16));
     if (touch && closed)
         ps.setKey(q, 0ull);
     S.j++;
@@ -472,16 +515,27 @@ CLB_HD void greedyStart(const DevStrategy& st, const Batch& B, u32 t, PartState&
     S.pat = seqCodes(B, t);
     S.pSize = pi.len;
     S.j = pi.matched;
-    if (S.patS) { // 8 byte codes -> 8 nibbles (the code rows are 8-byte aligned and padded)
+    S.patN = 0;
+    if (S.patS) { // 8 byte codes -> 8 x 2 bits (the code rows are 8-byte aligned and padded)
         const u64* src = (const u64*)S.pat;
         const u32 nwords = (S.pSize + 7) / 8;
+        u64 bad = 0;
+        u32 acc = 0;
         for (u32 j = 0; j < nwords; j++) {
-            u64 x = src[j] & 0x0F0F0F0F0F0F0F0Full;
-            x = (x | (x >> 4)) & 0x00FF00FF00FF00FFull;
-            x = (x | (x >> 8)) & 0x0000FFFF0000FFFFull;
-            x = (x | (x >> 16)) & 0x00000000FFFFFFFFull;
-            S.patS[j * S.patStride] = (u32)x;
+            const u64 v = src[j];
+            const u32 rest = S.pSize - 8 * j; // characters of the sequence in this word (>= 1)
+            bad |= v & 0x0404040404040404ull & (rest >= 8 ? ~0ull : ((1ull << (8 * rest)) - 1ull));
+            u64 x = v & 0x0303030303030303ull;
+            x = (x | (x >> 6)) & 0x000F000F000F000Full;
+            x = (x | (x >> 12)) & 0x000000FF000000FFull;
+            x = (x | (x >> 24)) & 0xFFFFull;
+            acc |= (u32)x << (16 * (j & 1));
+            if ((j & 1) || j + 1 == nwords) {
+                S.patS[(j >> 1) * S.patStride] = acc;
+                acc = 0;
+            }
         }
+        S.patN = bad ? 1u : 0u;
     }
     loadParts(B.parts, t, S.ps, st.P);
     for (u32 i = 0; i < st.P; i++)
@@ -548,7 +602,7 @@ CLB_HD void partFinish(const IndexView& ix, const DevStrategy& st, const Batch& 
                 c.fixedStart = 1;
             }
             for (u32 row = 0; row < width; row++) {
-                c.row = ps.at(i, 2) + row;
+                c.row = ps.emW(i)[0] + row;
                 c.order = emit++;
                 if (at != 0xFFFFFFFFu)
                     B.cands.data[at++] = c;

@@ -265,7 +265,7 @@ template <typename BE> struct Pipeline {
             if (opt.partStrategy == PART_DYNAMIC) {
                 // the greedy steps read one character of the sequence per step: stage it on chip
                 PartBase pg = pb;
-                pg.patWords = (!fw && maxLen <= 512) ? (maxLen + 7) / 8 : 0;
+                pg.patWords = (!fw && maxLen <= 512) ? (maxLen + 15) / 16 : 0;
                 GreedyKernel k1b{pg};
                 be.launch(k1b, T, nullptr, WK_LIGHT);
             }
