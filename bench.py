@@ -178,6 +178,7 @@ def main():
     ap.add_argument("--k", type=int, default=4)
     ap.add_argument("--cpu-sample", type=int, default=200_000, help="reads of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-numa-bind", action="store_true", help="do not bind the process to the GPU's local CPUs")
     ap.add_argument("--host-threads", type=int, default=2, help="host threads (one context each) of the e2e leg")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
@@ -223,6 +224,8 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device (the product has no CPU fallback)")
     torch.cuda.set_device(local)
+    from columba_b200.parallel import bind_to_gpu_numa_node
+    numa_cpus = None if args.no_numa_bind else bind_to_gpu_numa_node(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
@@ -401,7 +404,8 @@ def main():
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u64", "data": "synthetic", "config": config,
             "e2e": {"value": e2e_val, "unit": "reads/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "ms_per_step": ms2 / args.steps, "host_threads": n_thr, "wall_ms_per_step": wall2 / args.steps},
+                    "ms_per_step": ms2 / args.steps, "host_threads": n_thr, "wall_ms_per_step": wall2 / args.steps,
+                    "host_cpus_bound_to_gpu_node": len(numa_cpus) if numa_cpus else 0},
             "gpu_launches": launches, "clocks": clocks, "clocks_e2e": clocks2, "roofline": roofline,
             "stage_ms": stage, "stats_per_step": stats, "counters": counters,
             "wall_ms_per_step": wall / args.steps, "index_device_bytes": ix.device_bytes}

@@ -24,6 +24,33 @@ def shard_batches(n_reads, rank, world, batch=BATCH_READS):
     return out
 
 
+def bind_to_gpu_numa_node(device):
+    """Restricts this process to the CPUs NVML reports as local to the GPU, so
+    that the page-locked read / result buffers allocated afterwards (first
+    touch) live on the GPU's NUMA node and its copies do not cross the socket
+    interconnect.  With several GPUs per host this is what keeps the end-to-end
+    rate from being bound by the host.  Returns the CPU list, or None when the
+    affinity is unknown or outside the CPUs this process may use."""
+    import os
+    try:
+        import pynvml
+        import torch
+        pynvml.nvmlInit()
+        try:
+            h = pynvml.nvmlDeviceGetHandleByUUID("GPU-" + str(torch.cuda.get_device_properties(device).uuid))
+        except Exception:
+            h = pynvml.nvmlDeviceGetHandleByIndex(device)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+        cpus = {64 * i + b for i, w in enumerate(words) for b in range(64) if (int(w) >> b) & 1}
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return sorted(cpus)
+    except Exception:
+        return None
+
+
 def _dist():
     import torch.distributed as dist
     return dist if dist.is_available() and dist.is_initialized() else None
