@@ -68,9 +68,8 @@ CLB_HD BwtRec loadRec(const BwtRec* p) {
 #endif
 }
 
-// occ of A,C,G,T in BWT[0,p)
-CLB_HD void occ4raw(const BwtRec* rec, u32 dollarPos, u32 p, u32 o[4]) {
-    BwtRec r = loadRec(rec + (p >> 6));
+// occ of A,C,G,T in BWT[0,p) out of the record r of p's block
+CLB_HD void occ4rec(const BwtRec& r, u32 dollarPos, u32 p, u32 o[4]) {
     u32 off = p & 63;
     u64 m = (1ull << off) - 1ull;
     u64 lo = r.lo & m, hi = r.hi & m;
@@ -83,7 +82,25 @@ CLB_HD void occ4raw(const BwtRec* rec, u32 dollarPos, u32 p, u32 o[4]) {
     o[2] = r.cnt[2] + nG;
     o[3] = r.cnt[3] + nT;
 }
+// occ of A,C,G,T in BWT[0,p)
+CLB_HD void occ4raw(const BwtRec* rec, u32 dollarPos, u32 p, u32 o[4]) {
+    const BwtRec r = loadRec(rec + (p >> 6));
+    occ4rec(r, dollarPos, p, o);
+}
 CLB_HD void occ4(const BwtView& v, u32 p, u32 o[4]) { occ4raw(v.rec, v.dollarPos, p, o); }
+// occ at both ends of a range [b, e].  Once a range is narrower than a block
+// (after the k-mer seed almost always) both ends sit in the same 32-byte
+// record, and the second load -- for scattered ranges a wavefront of the L1
+// data pipe per lane, the resource that bounds the extension kernels -- is
+// skipped.
+CLB_HD void occ4pair(const BwtRec* rec, u32 dollarPos, u32 b, u32 e, u32 ob[4], u32 oe[4]) {
+    const BwtRec rb = loadRec(rec + (b >> 6));
+    BwtRec re = rb;
+    if ((b >> 6) != (e >> 6))
+        re = loadRec(rec + (e >> 6));
+    occ4rec(rb, dollarPos, b, ob);
+    occ4rec(re, dollarPos, e, oe);
+}
 // symbol (0..3) of BWT[p]; caller handles p == dollarPos
 CLB_HD u32 bwtSym(const BwtRec& r, u32 off) {
     return (u32)((r.lo >> off) & 1) | ((u32)((r.hi >> off) & 1) << 1);
@@ -97,8 +114,7 @@ CLB_HD void extendAll(const IndexView& ix, int dir, bool uniBack, const RangePai
     const BwtView& bw = (dir == DIR_BWD) ? ix.fwd : ix.rev;
     const Range t = (dir == DIR_BWD) ? p.sa : p.rev;
     u32 ob[4], oe[4];
-    occ4(bw, t.b, ob);
-    occ4(bw, t.e, oe);
+    occ4pair(bw.rec, bw.dollarPos, t.b, t.e, ob, oe);
     u32 s = (dir == DIR_BWD) ? p.rev.b : p.sa.b;
     u32 x = (t.b <= bw.dollarPos && bw.dollarPos < t.e) ? 1u : 0u;
     for (int c = 0; c < 4; c++) {
@@ -133,8 +149,7 @@ CLB_HD bool extendOne(const IndexView& ix, int dir, bool uniBack, u32 c, RangePa
     const u32 tb = bwd ? r.sa.b : r.rev.b, te = bwd ? r.sa.e : r.rev.e;
     const u32 s = bwd ? r.rev.b : r.sa.b;
     u32 ob[4], oe[4];
-    occ4raw(rec, dollar, tb, ob);
-    occ4raw(rec, dollar, te, oe);
+    occ4pair(rec, dollar, tb, te, ob, oe);
     u32 x = (tb <= dollar && dollar < te) ? 1u : 0u;
     x += (c > 0) ? oe[0] - ob[0] : 0u;
     x += (c > 1) ? oe[1] - ob[1] : 0u;
