@@ -149,3 +149,50 @@ def pair_occurrences(up, down, min_frag, max_frag):
             if down[d][4] >= b:  # the downstream mate does not start before the upstream one
                 out.append((i, d, int(des[j] - b)))
     return out
+
+
+MAX_MAPQ = 60  # definitions.h:49
+_COMP = bytes.maketrans(b"ACGTacgt", b"TGCAtgca")
+
+
+def map_q(distance, n_hits, min_score):
+    """TextOcc::getMapQ, src/indexhelpers.h:378-388"""
+    if distance != min_score:
+        return 0
+    if n_hits == 1:
+        return MAX_MAPQ
+    import math
+    return int(round(-10.0 * math.log10(1.0 - 1.0 / n_hits)))
+
+
+def sam_single_end(res, read_names, seqs, quals, seq_names, unmapped=True):
+    """The SAM body the reference writes for a chunk of single-end reads in ALL
+    mode, from a batch result: generateOutputSingleEnd
+    (src/searchstrategy.cpp:1824-1902, stable sort by distance: the first
+    occurrence is the primary one), generateSE_SAM (src/searchstrategy.h:1633-1641),
+    TextOcc::generateSAMSingleEnd (src/indexhelpers.cpp:56-87), flags
+    getFlagsSE (src/indexhelpers.h:321-331), unmapped records
+    createUnmappedRecordSE.  Sequence and quality are printed for the primary
+    record only (reverse-complemented / reversed on the reverse strand).
+    Returns the lines in read order."""
+    out = []
+    for r, name in enumerate(read_names):
+        occ = _occs_of(res, r)
+        qual = quals[r] if quals is not None and quals[r] else "*"
+        if not occ:
+            if unmapped:
+                out.append("%s\t4\t*\t0\t0\t*\t*\t0\t0\t%s\t%s\tPG:Z:Columba\n" % (name, seqs[r], qual))
+            continue
+        occ = sorted(occ, key=lambda t: t[5])  # stable: text order within one distance
+        min_score = occ[0][5]
+        n_hits = sum(1 for t in occ if t[5] == min_score)
+        for i, (strand, seq_id, pos, end, index_begin, dist, cigar) in enumerate(occ):
+            flag = (16 if strand else 0) | (0 if i == 0 else 256)
+            if i == 0:
+                s = seqs[r].encode().translate(_COMP)[::-1].decode() if strand else seqs[r]
+                q = (qual[::-1] if strand and qual != "*" else qual)
+            else:
+                s, q = "*", "*"
+            out.append("%s\t%d\t%s\t%d\t%d\t%s\t*\t0\t0\t%s\t%s\tAS:i:%d\tNM:i:%d\tPG:Z:Columba\n" % (
+                name, flag, seq_names[seq_id], pos + 1, map_q(dist, n_hits, min_score), cigar, s, q, dist, dist))
+    return out
