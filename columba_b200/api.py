@@ -32,7 +32,7 @@ OCC_DTYPE = np.dtype([("read", "<u4"), ("seq_id", "<u4"), ("pos", "<u4"), ("end"
 
 
 class ClbResult(C.Structure):
-    _fields_ = [("n_reads", C.c_uint32), ("n_occ", C.c_uint32), ("occ", C.c_void_p), ("cigar", C.c_void_p),
+    _fields_ = [("n_reads", C.c_uint32), ("n_groups", C.c_uint32), ("n_occ", C.c_uint32), ("occ", C.c_void_p), ("cigar", C.c_void_p),
                 ("cigar_stride", C.c_uint32), ("read_start", C.c_void_p), ("read_count", C.c_void_p),
                 ("counters", C.c_uint64 * N_COUNTERS), ("stats", C.c_uint64 * N_STATS),
                 ("stage_ms", C.c_float * N_STAGES), ("total_ms", C.c_float), ("gpu_launches", C.c_uint32)]
@@ -47,7 +47,7 @@ class ClbError(RuntimeError):
 EXPORTS = ["clb_abi_version", "clb_device_count", "clb_index_load", "clb_index_free", "clb_index_text_length",
            "clb_index_num_seqs", "clb_index_seq_name", "clb_index_seq_start", "clb_index_device_bytes",
            "clb_ctx_create", "clb_ctx_free", "clb_last_error", "clb_ctx_set_strategy", "clb_ctx_set_options",
-           "clb_ctx_set_stream", "clb_ctx_set_trim_max", "clb_ctx_supports_distance", "clb_ctx_num_parts", "clb_map_batch", "clb_map_batch_device", "clb_occ4",
+           "clb_ctx_set_stream", "clb_ctx_set_trim_max", "clb_ctx_set_filter_per_strand", "clb_ctx_supports_distance", "clb_ctx_num_parts", "clb_map_batch", "clb_map_batch_device", "clb_occ4",
            "clb_extend", "clb_find_sa", "clb_kmer_lookup", "clb_build_index"]
 
 _libs = {}
@@ -83,6 +83,7 @@ def load_library(path=None):
     lib.clb_ctx_set_options.argtypes = [vp, C.c_int, C.c_int]
     lib.clb_ctx_set_stream.argtypes = [vp, vp]
     lib.clb_ctx_set_trim_max.argtypes = [vp, C.c_int]
+    lib.clb_ctx_set_filter_per_strand.argtypes = [vp, C.c_int]
     lib.clb_ctx_supports_distance.argtypes = [vp, C.c_int]
     lib.clb_ctx_num_parts.argtypes = [vp, C.c_int]
     lib.clb_map_batch.argtypes = [vp, vp, vp, C.c_uint32, C.c_int, C.c_int, C.POINTER(ClbResult)]
@@ -122,6 +123,7 @@ class BatchResult:
 
     def __init__(self, r, fetched=True):
         self.n_reads = r.n_reads
+        self.n_groups = r.n_groups
         self.counters = dict(zip(COUNTER_NAMES, list(r.counters)))
         self.stats = dict(zip(STAT_NAMES, list(r.stats)))
         self.stage_ms = dict(zip(STAGE_NAMES, list(r.stage_ms)))
@@ -134,8 +136,8 @@ class BatchResult:
                 if n else np.zeros(0, OCC_DTYPE)
             self.cigar = np.frombuffer((C.c_uint16 * (n * r.cigar_stride)).from_address(r.cigar), dtype=np.uint16) \
                 .reshape(n, r.cigar_stride).copy() if n else np.zeros((0, r.cigar_stride), np.uint16)
-            self.read_start = np.frombuffer((C.c_uint32 * r.n_reads).from_address(r.read_start), dtype=np.uint32).copy()
-            self.read_count = np.frombuffer((C.c_uint32 * r.n_reads).from_address(r.read_count), dtype=np.uint32).copy()
+            self.read_start = np.frombuffer((C.c_uint32 * r.n_groups).from_address(r.read_start), dtype=np.uint32).copy()
+            self.read_count = np.frombuffer((C.c_uint32 * r.n_groups).from_address(r.read_count), dtype=np.uint32).copy()
         else:
             self.occ = None
 
@@ -209,6 +211,11 @@ class Mapper:
     def set_trim_max(self, largest_stratum):
         """largestStratum of findSeqName (0: the batch's max_dist); BEST mode sets its cut-off."""
         self._check(self.lib.clb_ctx_set_trim_max(self.h, int(largest_stratum)))
+
+    def set_filter_per_strand(self, per_strand):
+        """BEST mode filters each strand on its own (src/searchstrategy.cpp:777-811); results then come in
+        2 * n_reads groups (2 * read + strand)."""
+        self._check(self.lib.clb_ctx_set_filter_per_strand(self.h, int(bool(per_strand))))
 
     def supports(self, k):
         return bool(self.lib.clb_ctx_supports_distance(self.h, k))

@@ -151,6 +151,12 @@ int clb_ctx_set_trim_max(clb_ctx* c, int largest_stratum) {
     c->opt.trimMax = (clb::u32)largest_stratum;
     return CLB_OK;
 }
+int clb_ctx_set_filter_per_strand(clb_ctx* c, int per_strand) {
+    if (!c)
+        return CLB_E_INVALID;
+    c->opt.perStrand = per_strand ? 1u : 0u;
+    return CLB_OK;
+}
 int clb_ctx_set_stream(clb_ctx* c, void* cuda_stream) {
     if (!c)
         return CLB_E_INVALID;
@@ -179,6 +185,7 @@ static int clbFinish(clb_ctx* c, clb::u32 err, uint32_t n_reads, clb_result* out
     if (out) {
         memset(out, 0, sizeof(*out));
         out->n_reads = n_reads;
+        out->n_groups = c->opt.perStrand ? 2 * n_reads : n_reads;
         memcpy(out->counters, c->res.counters, sizeof(out->counters));
         memcpy(out->stats, c->res.stats, sizeof(out->stats));
         out->cigar_stride = c->res.cigW;
@@ -199,6 +206,19 @@ static int clbFinish(clb_ctx* c, clb::u32 err, uint32_t n_reads, clb_result* out
     return CLB_OK;
 }
 static int clbPrepare(clb_ctx* c, int max_dist, int min_dist) {
+    if (max_dist == 0) { // exact stratum: no search scheme involved (src/searchstrategy.cpp:499-510)
+        memset(&c->flat[0], 0, sizeof(clb::DevStrategy));
+        c->flat[0].supported = 1;
+        c->flat[0].P = 1;
+        c->opt.k = 0;
+        c->opt.minD = 0;
+        c->opt.noCigar = c->index->dix->view.noCigar;
+        if (c->uploadedK != 0) {
+            c->pipe->uploadStrategy(c->flat[0]);
+            c->uploadedK = 0;
+        }
+        return CLB_OK;
+    }
     if (!c->haveStrategy) {
         c->err = "no search strategy set (clb_ctx_set_strategy)";
         return CLB_E_INVALID;

@@ -203,6 +203,10 @@ struct Batch {
     u32 partStrategy;      // PART_*
     u32 cigW;              // CIGAR slots per occurrence (2k+2)
     u32 noCigarFlag;       // -nC: do not keep CIGAR strings
+    u32 grpShift;          // 1: occurrences are grouped and filtered per read (ALL mode, searchstrategy.cpp:495-535);
+                           // 0: per (read, strand), as BEST mode maps and filters each strand (:777-811)
+    u32 G;                 // number of groups: R (grpShift 1) or 2R
+    u32 noFilter;          // exact stratum (indexinterface.cpp:947-1014): no unique, no redundancy filter
     // derived per (read,strand)
     u8* codes;             // 2R x seqStride codes (0..3 ACGT, 4 other)
     u32 seqStride;
@@ -242,6 +246,7 @@ struct Batch {
     u32* err;
 };
 
+CLB_HD u32 groupOf(const Batch& B, u32 t) { return t >> B.grpShift; }
 CLB_HD const u8* seqCodes(const Batch& B, u32 t) { return B.codes + (size_t)t * B.seqStride; }
 CLB_HD u32 seqLen(const Batch& B, u32 t) { return B.readOff[(t >> 1) + 1] - B.readOff[t >> 1]; }
 // planes of sequence t in direction d (DIR_FWD: as is, DIR_BWD: reversed)

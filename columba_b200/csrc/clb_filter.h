@@ -298,7 +298,7 @@ CLB_HD void txPerReadTask(const IndexView& ix, const Batch& B, u32 r, FilterScra
         heapSortIdx(idx, n, less);
     u32 m = 0;
     for (u32 i = 0; i < n; i++) {
-        if (m > 0) {
+        if (m > 0 && !B.noFilter) {
             const TextOccRec &a = d[idx[m - 1]], &b = d[idx[i]];
             if (a.b == b.b && a.e == b.e && a.dist == b.dist)
                 continue;
@@ -307,7 +307,7 @@ CLB_HD void txPerReadTask(const IndexView& ix, const Batch& B, u32 r, FilterScra
     }
     const bool edit = B.metric == METRIC_EDIT;
     u32 nOut = m;
-    if (edit) { // redundancy filter, indexinterface.cpp:1451-1485
+    if (edit && !B.noFilter) { // redundancy filter, indexinterface.cpp:1451-1485
         const u32 maxDiff = 2 * B.k;
         u32 prevBegin = 0xFFFFFFFFu, prevDepth = 0xFFFFFFFFu, prevED = B.k + 1;
         nOut = 0;
@@ -350,7 +350,7 @@ CLB_HD void txPerReadTask(const IndexView& ix, const Batch& B, u32 r, FilterScra
         }
         u32 index = lo - 1;
         OutOcc out;
-        out.read = r;
+        out.read = B.grpShift ? r : (r >> 1);
         out.strand = (u8)(o.t & 1);
         u32 ncig = o.ncig;
         const u16* src = cig;
@@ -412,6 +412,83 @@ CLB_HD void txPerReadTask(const IndexView& ix, const Batch& B, u32 r, FilterScra
     }
     B.outStart[r] = at;
     B.outCount[r] = w;
+}
+
+// Exact stratum of read r, both strands: IndexInterface::exactMatchesOutput
+// src/indexinterface.cpp:947-1014 + verifyInTextExact :918-943.  Backward
+// exact match on the forward BWT until the range is no wider than the switch
+// point, then the rest of the read is compared with the text.  No redundancy
+// filter applies to these occurrences (B.noFilter).  The reference's counter
+// arithmetic is reproduced as it stands: in ALL mode both strands append to
+// the same vector and `p.size() - tOcc.size()` / `tOcc.size()` use its
+// cumulative size (unsigned wrap-around included).
+CLB_HD void exactTask(const IndexView& ix, const Batch& B, u32 r, LocalCtr& lc) {
+    u32 cumul = 0; // size of the reference's tOcc vector
+    for (u32 strand = 0; strand < 2; strand++) {
+        const u32 t = 2 * r + strand;
+        const u32 len = seqLen(B, t);
+        if (B.grpShift == 0)
+            cumul = 0; // BEST mode keeps one vector per strand
+        if (len == 0)
+            continue;
+        const u8* codes = seqCodes(B, t);
+        RangePair rg = completeRange(ix);
+        u32 i = len;
+        bool dead = false;
+        for (; i-- > 0;) {
+            const u32 c = codes[i];
+            if (c > 3) {
+                dead = true;
+                break;
+            }
+            lc.s[ST_RANK_LOOKUPS] += 2;
+            if (!extendOne(ix, DIR_BWD, true, c, rg)) {
+                dead = true;
+                break;
+            }
+            lc.c[NODE_COUNTER]++;
+            if (rg.sa.width() <= ix.switchPoint)
+                break;
+        }
+        if (dead)
+            continue;
+        const bool verify = (i != 0xFFFFFFFFu);
+        const u32 remaining = verify ? i : 0u;
+        const u32 w = rg.sa.width();
+        u32 found = 0;
+        for (u32 q = 0; q < w; q++) {
+            const u32 pos = findSA(ix, rg.sa.b + q, lc.s[ST_LF_STEPS]);
+            if (pos < remaining)
+                continue;
+            const u32 b = pos - remaining;
+            bool ok = true;
+            for (u32 j = 0; j < remaining && ok; j++)
+                ok = textAt(ix, b + j) == codes[j];
+            if (!ok)
+                continue;
+            TextOccRec o;
+            o.t = t;
+            o.b = b;
+            o.e = b + len;
+            o.order = q;
+            o.order2 = 0;
+            o.dist = 0;
+            o.cls = 0;
+            o.pad = 0;
+            o.ncig = B.noCigarFlag ? 0 : 1;
+            const u32 at = B.textOccs.push(o, B.err, ERR_TEXTOCC_OVERFLOW);
+            if (at != 0xFFFFFFFFu && o.ncig)
+                B.textCig[(size_t)at * B.cigW] = (u16)((len << 2) | CIG_M);
+            found++;
+        }
+        cumul += found;
+        if (verify) {
+            lc.c[IN_TEXT_STARTED] += w;
+            lc.c[ABORTED_IN_TEXT_VERIF] += (u64)w - (u64)cumul; // wraps like the reference's size_t arithmetic
+        }
+        lc.c[TOTAL_REPORTED_POSITIONS] += cumul;
+        lc.s[ST_TEXT_OCCS] += found;
+    }
 }
 
 // CIGAR of one surviving index occurrence (out[j]); one task per job so that

@@ -10,8 +10,14 @@
 //   .pos / .sna  src/buildindex.cpp:361-381 (read: src/indexinterface.cpp:161-191)
 // Error messages follow the reference's (std::runtime_error texts).
 #pragma once
+#include "clb_gidx.h"
 #include "clb_kernels.h"
 #include "clb_pipeline.h"
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
+#include <cstdlib>
 #include <fstream>
 #include <stdexcept>
 #include <string>
@@ -27,6 +33,7 @@ struct HostIndexMeta {
     u32 K = 0;
     u32 saSparse = 0;
     size_t deviceBytes = 0;
+    bool fromGidx = false;
 };
 
 template <typename T> static bool readWholeFile(const std::string& fn, std::vector<T>& v) {
@@ -104,9 +111,88 @@ template <typename BE> struct DeviceIndex {
         return (const T*)d;
     }
 
+    const void* uploadRaw(const void* src, size_t bytes) {
+        void* d = be.alloc(bytes ? bytes : 16);
+        allocs.push_back(d);
+        if (bytes)
+            be.h2d(d, src, bytes);
+        meta.deviceBytes += bytes;
+        return d;
+    }
+    // the .gidx sidecar (clb_gidx.h): the device layout as written by
+    // clb_gpu_build; returns false when there is none for this sparseness
+    bool loadGidx(const std::string& base, u32 saSparse) {
+        const std::string fn = base + ".gidx";
+        if (getenv("CLB_NO_GIDX")) // tests: force the re-packing path
+            return false;
+        int fd = ::open(fn.c_str(), O_RDONLY);
+        if (fd < 0)
+            return false;
+        struct stat sb;
+        if (fstat(fd, &sb) != 0 || (size_t)sb.st_size < sizeof(GidxHeader)) {
+            ::close(fd);
+            throw std::runtime_error("Corrupt index sidecar: " + fn);
+        }
+        const size_t fileBytes = (size_t)sb.st_size;
+        void* mp = mmap(nullptr, fileBytes, PROT_READ, MAP_PRIVATE, fd, 0);
+        ::close(fd);
+        if (mp == MAP_FAILED)
+            throw std::runtime_error("Cannot map file: " + fn);
+        struct Unmap {
+            void* p;
+            size_t n;
+            ~Unmap() { munmap(p, n); }
+        } guard{mp, fileBytes};
+        madvise(mp, fileBytes, MADV_SEQUENTIAL);
+        const u8* m8 = (const u8*)mp;
+        const GidxHeader& H = *(const GidxHeader*)mp;
+        if (memcmp(H.magic, CLB_GIDX_MAGIC, 8) != 0 || H.version != CLB_GIDX_VERSION || H.fileBytes != fileBytes)
+            throw std::runtime_error("Corrupt index sidecar (header): " + fn);
+        if (H.saSparse != saSparse)
+            return false; // built for another sparseness: fall back to the reference's files
+        auto inside = [&](u64 off, u64 bytes) { return off <= fileBytes && bytes <= fileBytes - off; };
+        if (!inside(H.offSeqStart, (u64)(H.numSeq + 1) * 4) || !inside(H.offNames, H.namesBytes) ||
+            !inside(H.offFwd, H.nRec * sizeof(BwtRec)) || !inside(H.offRev, H.nRec * sizeof(BwtRec)) ||
+            !inside(H.offSsaRec, H.nSsaRec * sizeof(SsaRec)) || !inside(H.offSsa, H.nSsa * 4) ||
+            !inside(H.offText, H.nTextWords * 4) || H.nRec != (u64)H.textLength / 64 + 1 ||
+            H.nTextWords < (u64)H.textLength / 16 + 8)
+            throw std::runtime_error("Corrupt index sidecar (sections): " + fn);
+        view.textLength = H.textLength;
+        for (int a = 0; a < 5; a++)
+            view.C[a] = H.C[a];
+        meta.textLength = view.textLength;
+        memcpy(meta.C, view.C, sizeof(meta.C));
+        view.text = (const u32*)uploadRaw(m8 + H.offText, H.nTextWords * 4);
+        view.fwd.rec = (const BwtRec*)uploadRaw(m8 + H.offFwd, H.nRec * sizeof(BwtRec));
+        view.fwd.dollarPos = H.dollarFwd;
+        view.rev.rec = (const BwtRec*)uploadRaw(m8 + H.offRev, H.nRec * sizeof(BwtRec));
+        view.rev.dollarPos = H.dollarRev;
+        view.ssaRec = (const SsaRec*)uploadRaw(m8 + H.offSsaRec, H.nSsaRec * sizeof(SsaRec));
+        view.ssa = (const u32*)uploadRaw(m8 + H.offSsa, H.nSsa * 4);
+        meta.saSparse = saSparse;
+        meta.seqStart.assign((const u32*)(m8 + H.offSeqStart), (const u32*)(m8 + H.offSeqStart) + H.numSeq + 1);
+        view.seqStart = upload(meta.seqStart);
+        view.numSeq = H.numSeq;
+        const char* nm = (const char*)(m8 + H.offNames);
+        for (u64 o = 0; o < H.namesBytes && meta.seqNames.size() < H.numSeq;) {
+            std::string s(nm + o);
+            o += s.size() + 1;
+            meta.seqNames.push_back(s);
+        }
+        be.sync(); // the copies read the mapping
+        meta.fromGidx = true;
+        return true;
+    }
+
     void load(const std::string& base, u32 saSparse, u32 K, u32 inTextSwitch, bool noCigar) {
         if (K > 13)
             throw std::runtime_error("k-mer size too large for the dense k-mer table (max 13)");
+        if (loadGidx(base, saSparse)) {
+            view.switchPoint = inTextSwitch;
+            view.noCigar = noCigar;
+            buildKmerTable(K);
+            return;
+        }
         { // .meta
             std::ifstream m(base + ".meta");
             if (m) {

@@ -115,6 +115,16 @@ template <typename W> struct SearchKernel {
     CLB_HD void end(State& s) const { s.lc.flush(B.counters, B.stats); }
 };
 
+// exact stratum (k = 0): one task per read, both strands
+struct ExactKernel {
+    IndexView ix;
+    Batch B;
+    typedef WorkerCtr State;
+    CLB_HD void begin(State& s, u32) const { s.lc.clear(); }
+    CLB_HD void run(State& s, u32 r) const { exactTask(ix, B, r, s.lc); }
+    CLB_HD void end(State& s) const { s.lc.flush(B.counters, B.stats); }
+};
+
 // stage 3
 struct VerifyKernel {
     IndexView ix;
@@ -203,7 +213,7 @@ struct FmCountKernel {
     Batch B;
     struct State {};
     CLB_HD void begin(State&, u32) const {}
-    CLB_HD void run(State&, u32 i) const { atomAdd<u32>(B.fmCount + (B.fmOccs.data[i].t >> 1), 1u); }
+    CLB_HD void run(State&, u32 i) const { atomAdd<u32>(B.fmCount + groupOf(B, B.fmOccs.data[i].t), 1u); }
     CLB_HD void end(State&) const {}
 };
 struct FmScatterKernel {
@@ -211,7 +221,7 @@ struct FmScatterKernel {
     struct State {};
     CLB_HD void begin(State&, u32) const {}
     CLB_HD void run(State&, u32 i) const {
-        u32 r = B.fmOccs.data[i].t >> 1;
+        u32 r = groupOf(B, B.fmOccs.data[i].t);
         B.fmIdx[B.fmStart[r] + atomAdd<u32>(B.fmFill + r, 1u)] = i;
     }
     CLB_HD void end(State&) const {}
@@ -220,7 +230,7 @@ struct TxCountKernel {
     Batch B;
     struct State {};
     CLB_HD void begin(State&, u32) const {}
-    CLB_HD void run(State&, u32 i) const { atomAdd<u32>(B.txCount + (B.textOccs.data[i].t >> 1), 1u); }
+    CLB_HD void run(State&, u32 i) const { atomAdd<u32>(B.txCount + groupOf(B, B.textOccs.data[i].t), 1u); }
     CLB_HD void end(State&) const {}
 };
 struct TxScatterKernel {
@@ -228,7 +238,7 @@ struct TxScatterKernel {
     struct State {};
     CLB_HD void begin(State&, u32) const {}
     CLB_HD void run(State&, u32 i) const {
-        u32 r = B.textOccs.data[i].t >> 1;
+        u32 r = groupOf(B, B.textOccs.data[i].t);
         B.txIdx[B.txStart[r] + atomAdd<u32>(B.txFill + r, 1u)] = i;
     }
     CLB_HD void end(State&) const {}
@@ -268,6 +278,12 @@ struct TxPerReadKernel {
     CLB_HD void run(State& s, u32 r, unsigned act) const {
         txPerReadTask(ix, B, r, s.fs, s.lc, act);
         u32 n = B.outCount[r];
+        if (B.grpShift == 0) { // per-strand groups (BEST mode strata): MAPPED_READS is the host loop's business
+            if (!(r & 1u))
+                s.lc.c[NUMBER_OF_READS]++;
+            s.lc.c[TOTAL_UNIQUE_MATCHES] += n;
+            return;
+        }
         if (n) {
             s.lc.c[MAPPED_READS]++;
             s.lc.c[TOTAL_UNIQUE_MATCHES] += n;

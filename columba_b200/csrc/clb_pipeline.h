@@ -58,6 +58,7 @@ struct MapOptions {
     u32 partStrategy = PART_DYNAMIC;
     u32 noCigar = 0;
     u32 trimMax = 0; // largest distance of an alignment clipped at a sequence boundary (0: k); BEST mode: the cut-off
+    u32 perStrand = 0; // 1: group and filter the occurrences per (read, strand) instead of per read (BEST mode)
 };
 
 // host array that the backend allocates (page-locked on the GPU, so that the
@@ -150,6 +151,10 @@ template <typename BE> struct Pipeline {
         B.trimMax = kk;
         B.cigW = 2 * kk + 2;
         B.noCigarFlag = opt.noCigar;
+        B.grpShift = opt.perStrand ? 0u : 1u;
+        B.G = opt.perStrand ? 2 * R : R;
+        B.noFilter = (opt.k == 0) ? 1u : 0u;
+        const u32 G = B.G;
         const u32 T = 2 * R;
         // host reads go up in slices on the copy stream; the preparation kernel of a
         // slice starts as soon as its bytes have arrived (see stage 0 below)
@@ -232,8 +237,8 @@ template <typename BE> struct Pipeline {
         B.counters = M->counters;
         B.stats = M->stats;
         B.err = &M->err;
-        // per-read arrays: 9 x (R+1)
-        const size_t pr = (size_t)(R + 1);
+        // per-group arrays: 9 x (G+1)
+        const size_t pr = (size_t)(G + 1);
         bPerRead.ensure(be, pr * 9 * 4);
         be.zero(bPerRead.p, pr * 9 * 4);
         u32* q = (u32*)bPerRead.p;
@@ -255,6 +260,17 @@ template <typename BE> struct Pipeline {
                 be.launch(k0, (sliceEnd[sl] - r0) * (B.nw - 1), nullptr, WK_LIGHT);
             }
             be.mark(STG_PREP);
+        }
+        const u32 vRows = maxLen + 3 * kk + 8;
+        if (opt.k == 0) {
+            // exact stratum: backward exact match + text compare, one task per read
+            ExactKernel e0{ix, B};
+            be.mark(STG_PARTITION);
+            be.launch(e0, R, nullptr, WK_FILTER);
+            be.mark(STG_SEARCH);
+            be.mark(STG_VERIFY);
+        } else {
+        {
             // shared memory on the GPU; a slab for backends without it
             const u32 fw = be.fallbackWorkers();
             if (fw)
@@ -293,7 +309,6 @@ template <typename BE> struct Pipeline {
             be.mark(STG_SEARCH);
         }
         // ---- stage 3
-        const u32 vRows = maxLen + 3 * kk + 8;
         {
             const bool wide = !use64(2 * opt.k + 1, opt.k);
             const u32 nw = be.workers(WK_VERIFY), ls = be.laneStride();
@@ -319,6 +334,7 @@ template <typename BE> struct Pipeline {
             }
             be.mark(STG_VERIFY);
         }
+        } // k > 0
         // ---- stages 4-6
         {
             size_t sb = (((size_t)B.cigW * 2 * 2 + 63) & ~(size_t)63) + (size_t)vRows * sizeof(Row<u128>);
@@ -327,23 +343,23 @@ template <typename BE> struct Pipeline {
             bSlabFilter.ensure(be, sb * nw);
             FmCountKernel c1{B};
             be.launch(c1, capFm, &M->nFm, WK_LIGHT);
-            be.exclusiveScan(B.fmCount, B.fmStart, R);
+            be.exclusiveScan(B.fmCount, B.fmStart, G);
             FmScatterKernel c2{B};
             be.launch(c2, capFm, &M->nFm, WK_LIGHT);
             FmPerReadKernel c3{ix, B, (u8*)bSlabFilter.p, sb, vRows};
-            be.launch(c3, R, nullptr, WK_FILTER);
+            be.launch(c3, G, nullptr, WK_FILTER);
             be.mark(STG_FM);
             TxCountKernel d1{B};
             be.launch(d1, capTx, &M->nTx, WK_LIGHT);
-            be.exclusiveScan(B.txCount, B.txStart, R);
+            be.exclusiveScan(B.txCount, B.txStart, G);
             TxScatterKernel d2{B};
             be.launch(d2, capTx, &M->nTx, WK_LIGHT);
             // reads inside repeats have thousands of occurrences: their segments are sorted
             // by whole CTAs first (the per-read kernel sorts the small ones itself)
-            B.txPresorted = be.sortBigSegments(B, R);
+            B.txPresorted = be.sortBigSegments(B, G);
             B.txPresortedMax = be.sortBigMax();
             TxPerReadKernel d3{ix, B, (u8*)bSlabFilter.p, sb, vRows};
-            be.launch(d3, R, nullptr, WK_FILTER);
+            be.launch(d3, G, nullptr, WK_FILTER);
             CigarJobKernel d4{ix, B, (u8*)bSlabFilter.p, sb, vRows};
             be.launch(d4, capOut, &M->nCigJobs, WK_FILTER);
             be.mark(STG_TEXT);
@@ -370,14 +386,14 @@ template <typename BE> struct Pipeline {
                 u32 n = hm.nOut;
                 res->occ.resize(be, n);
                 res->cig.resize(be, (size_t)n * B.cigW);
-                res->outStart.resize(be, R);
-                res->outCount.resize(be, R);
+                res->outStart.resize(be, G);
+                res->outCount.resize(be, G);
                 if (n) {
                     be.d2hAsync(res->occ.data(), bOut.p, (size_t)n * sizeof(OutOcc));
                     be.d2hAsync(res->cig.data(), bOutCig.p, (size_t)n * B.cigW * 2);
                 }
-                be.d2hAsync(res->outStart.data(), B.outStart, (size_t)R * 4);
-                be.d2hAsync(res->outCount.data(), B.outCount, (size_t)R * 4);
+                be.d2hAsync(res->outStart.data(), B.outStart, (size_t)G * 4);
+                be.d2hAsync(res->outCount.data(), B.outCount, (size_t)G * 4);
                 be.sync();
             }
         }

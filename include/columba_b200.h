@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define CLB_ABI_VERSION 1
+#define CLB_ABI_VERSION 2
 
 enum {
     CLB_OK = 0,
@@ -78,12 +78,14 @@ typedef struct clb_occ {
  * index_begin; the reference sorts by distance just before writing SAM). */
 typedef struct clb_result {
     uint32_t n_reads;
+    uint32_t n_groups;            /* entries of read_start / read_count: n_reads, or 2 * n_reads with group
+                                     2 * read + strand after clb_ctx_set_filter_per_strand(ctx, 1) */
     uint32_t n_occ;               /* entries in occ[] (some may be unused gaps) */
     const clb_occ* occ;
     const uint16_t* cigar;        /* n_occ x cigar_stride, run = (len << 2) | op, op 0=M 1=I 2=D */
     uint32_t cigar_stride;
-    const uint32_t* read_start;   /* n_reads */
-    const uint32_t* read_count;   /* n_reads : per-read hit counts */
+    const uint32_t* read_start;   /* n_groups */
+    const uint32_t* read_count;   /* n_groups : hit counts */
     uint64_t counters[CLB_N_COUNTERS];
     uint64_t stats[CLB_N_STATS];
     float stage_ms[CLB_N_STAGES]; /* device time per stage (CUDA events) */
@@ -125,6 +127,13 @@ int clb_ctx_set_options(clb_ctx*, int metric, int partitioning);
  * mode passes its cut-off (src/searchstrategy.cpp:537-568).  A clipped
  * alignment can therefore have a distance above max_dist. */
 int clb_ctx_set_trim_max(clb_ctx*, int largest_stratum);
+/* BEST mode maps and filters the two strands of a read separately
+ * (SearchStrategy::processSeq -> mapRead, src/searchstrategy.cpp:777-811,
+ * src/searchstrategy.h:490-517), ALL mode filters them together
+ * (matchApproxAllMap, src/searchstrategy.cpp:495-535).  per_strand = 1 makes
+ * the following batches group, de-duplicate and filter the occurrences per
+ * (read, strand); clb_result then has 2 * n_reads groups. */
+int clb_ctx_set_filter_per_strand(clb_ctx*, int per_strand);
 /* Run this context's copies and kernels on the caller's CUDA stream
  * (cudaStream_t, e.g. torch.cuda.current_stream().cuda_stream) instead of the
  * context's own stream; NULL restores the own stream. */
@@ -135,7 +144,10 @@ int clb_ctx_num_parts(const clb_ctx*, int k); /* calculateNumParts */
 /* ---- the hot path (replaces SearchStrategy::matchApproxAllMap for a whole
  * chunk, src/searchstrategy.cpp:495-535).  reads: concatenated ASCII reads,
  * offsets: n_reads+1 offsets into it.  HOST pointers; copies are part of the
- * call.  max_dist = -e, min_dist = minimal distance to report (0 in ALL mode). */
+ * call.  max_dist = -e, min_dist = minimal distance to report (0 in ALL mode).
+ * max_dist = 0 is the exact stratum (IndexInterface::exactMatchesOutput,
+ * src/indexinterface.cpp:947-1014): every exact occurrence of either strand,
+ * no redundancy filter, no search scheme needed. */
 int clb_map_batch(clb_ctx*, const uint8_t* reads, const uint32_t* offsets, uint32_t n_reads, int max_dist,
                   int min_dist, clb_result* out);
 /* Same with DEVICE pointers for reads/offsets; with fetch == 0 the occurrence
