@@ -48,7 +48,7 @@ EXPORTS = ["clb_abi_version", "clb_device_count", "clb_index_load", "clb_index_f
            "clb_index_num_seqs", "clb_index_seq_name", "clb_index_seq_start", "clb_index_device_bytes",
            "clb_ctx_create", "clb_ctx_free", "clb_last_error", "clb_ctx_set_strategy", "clb_ctx_set_options",
            "clb_ctx_set_stream", "clb_ctx_set_trim_max", "clb_ctx_set_filter_per_strand", "clb_ctx_supports_distance", "clb_ctx_num_parts", "clb_map_batch", "clb_map_batch_device", "clb_occ4",
-           "clb_extend", "clb_find_sa", "clb_kmer_lookup", "clb_build_index"]
+           "clb_extend", "clb_find_sa", "clb_kmer_lookup", "clb_build_index", "clb_gather_ceiling"]
 
 _libs = {}
 
@@ -94,6 +94,8 @@ def load_library(path=None):
     lib.clb_find_sa.argtypes = [vp, vp, C.c_uint32, vp]
     lib.clb_kmer_lookup.argtypes = [vp, vp, C.c_uint32, vp]
     lib.clb_build_index.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_char_p, C.c_size_t]
+    if hasattr(lib, "clb_gather_ceiling"):  # CUDA library only (the CPU unit-test harness has no such kernel)
+        lib.clb_gather_ceiling.argtypes = [vp, C.c_uint64, C.POINTER(C.c_float), C.POINTER(C.c_uint64)]
     _libs[path] = lib
     return lib
 
@@ -244,6 +246,13 @@ class Mapper:
         self._check(self.lib.clb_map_batch_device(self.h, d_reads_ptr, d_offsets_ptr, n_reads, max_read_len,
                                                   max_dist, min_dist, int(fetch), C.byref(r)))
         return BatchResult(r, fetched=fetch)
+
+    def gather_ceiling(self, n_lookups=1 << 28):
+        """Measured random 32-byte gather rate on the loaded index: (lookups/s, GB/s)."""
+        ms, done = C.c_float(), C.c_uint64()
+        self._check(self.lib.clb_gather_ceiling(self.h, n_lookups, C.byref(ms), C.byref(done)))
+        rate = done.value / (ms.value / 1e3)
+        return rate, rate * 32 / 1e9
 
     # unit-level entry points
     def occ4(self, positions, reverse=False):

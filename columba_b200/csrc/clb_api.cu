@@ -143,6 +143,34 @@ __global__ void __launch_bounds__(128) clb_kernel_stepped(const K k, u32 nMax, c
 template <class K> constexpr auto isStepped(int) -> decltype(K::kStepped) { return K::kStepped; }
 template <class K> constexpr bool isStepped(long) { return false; }
 
+// Warp-task functors (K::kWarpTask): a task is run by all 32 lanes of a warp
+// together (K::runWarp); warps claim tasks one at a time from a global counter.
+template <class K>
+__global__ void __launch_bounds__(128) clb_kernel_warp(const K k, u32 nMax, const u32* __restrict__ nDev, u32* workCtr) {
+    u32 n = nMax;
+    if (nDev) {
+        u32 v = *nDev;
+        n = v < nMax ? v : nMax;
+    }
+    const u32 warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const u32 lane = threadIdx.x & 31;
+    typename K::State st;
+    k.begin(st, warp);
+    for (;;) {
+        u32 i = 0;
+        if (lane == 0)
+            i = atomicAdd(workCtr, 1u);
+        i = __shfl_sync(0xFFFFFFFFu, i, 0);
+        if (i >= n)
+            break;
+        k.runWarp(st, i);
+        __syncwarp();
+    }
+    k.end(st);
+}
+template <class K> constexpr auto isWarpTask(int) -> decltype(K::kWarpTask) { return K::kWarpTask; }
+template <class K> constexpr bool isWarpTask(long) { return false; }
+
 // exclusive scan of n u32 values (out[n] = total) in three launches:
 // per-tile sums, scan of the tile sums by one block, per-tile scan + offset.
 static const u32 SCAN_TILE = 2048; // 256 threads x 8 values
@@ -403,7 +431,8 @@ struct CudaBackend {
     void copyWait(u32 slice) { CLB_CUDA(cudaStreamWaitEvent(stream, evCopy[slice], 0)); }
     u32 blocksFor(int kind) const {
         switch (kind) {
-        case WK_SEARCH: return (u32)numSMs * 2;   // x128 threads: 256 workers per SM (large slabs)
+        case WK_SEARCH: return (u32)numSMs * 4;   // x128 threads: 16 warps per SM, one task per warp
+        case WK_SEARCH_HEAVY: return (u32)numSMs; // 4 warps per SM with large scratch
         case WK_VERIFY: return (u32)numSMs * 8;
         case WK_FILTER: return (u32)numSMs * 4;
         default: return (u32)numSMs * 16;
@@ -416,7 +445,9 @@ struct CudaBackend {
         if (nMax == 0)
             return;
         void (*fn)(const K, u32, const u32*, u32*);
-        if constexpr (isStepped<K>(0))
+        if constexpr (isWarpTask<K>(0))
+            fn = clb_kernel_warp<K>;
+        else if constexpr (isStepped<K>(0))
             fn = clb_kernel_stepped<K>;
         else
             fn = clb_kernel<K>;
@@ -516,3 +547,65 @@ struct CudaBackend {
 #define CLB_BE clb::CudaBackend
 #include "clb_api_impl.h"
 #include "clb_index_build.h"
+
+// ---- measured ceiling of the path's roofline unit: independent random 32-byte
+// rank-record reads from the forward BWT records of the loaded index, 8 in flight per thread
+namespace clb {
+__global__ void __launch_bounds__(256) clb_gather_kernel(const BwtRec* __restrict__ rec, u32 nRec, u32 perThread,
+                                                         u64 seed, u64* sink) {
+    const u64 tid = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    u64 x = seed ^ (tid * 0x9E3779B97F4A7C15ull);
+    u64 acc = 0;
+    for (u32 i = 0; i < perThread; i += 8) {
+        u32 idx[8];
+#pragma unroll
+        for (int q = 0; q < 8; q++) {
+            x ^= x << 13;
+            x ^= x >> 7;
+            x ^= x << 17;
+            idx[q] = (u32)(((x >> 32) * (u64)nRec) >> 32);
+        }
+#pragma unroll
+        for (int q = 0; q < 8; q++) {
+            const BwtRec r = loadRec(rec + idx[q]);
+            acc += r.lo ^ r.hi ^ r.cnt[0] ^ r.cnt[3];
+        }
+    }
+    if (acc == 0x1234567ull)
+        *sink = acc;
+}
+} // namespace clb
+
+extern "C" int clb_gather_ceiling(clb_ctx* c, uint64_t n_lookups, float* ms_out, uint64_t* done_out) {
+    if (!c || !ms_out || !done_out || n_lookups == 0)
+        return CLB_E_INVALID;
+    try {
+        using namespace clb;
+        CudaBackend& be = *c->be;
+        CLB_CUDA(cudaSetDevice(be.device));
+        const IndexView ix = c->pipe->ix;
+        const u32 nRec = ix.textLength / 64 + 1;
+        const u32 blocks = (u32)be.numSMs * 8, threads = blocks * 256;
+        u32 per = (u32)((n_lookups + threads - 1) / threads);
+        per = (per + 7) & ~7u;
+        u64* sink = (u64*)be.alloc(8);
+        cudaEvent_t e0, e1;
+        CLB_CUDA(cudaEventCreate(&e0));
+        CLB_CUDA(cudaEventCreate(&e1));
+        clb_gather_kernel<<<blocks, 256, 0, be.stream>>>(ix.fwd.rec, nRec, 64, 1, sink); // warm-up
+        CLB_CUDA(cudaEventRecord(e0, be.stream));
+        clb_gather_kernel<<<blocks, 256, 0, be.stream>>>(ix.fwd.rec, nRec, per, 0x5DEECE66Dull, sink);
+        CLB_CUDA(cudaEventRecord(e1, be.stream));
+        CLB_CUDA(cudaEventSynchronize(e1));
+        CLB_CUDA(cudaGetLastError());
+        CLB_CUDA(cudaEventElapsedTime(ms_out, e0, e1));
+        *done_out = (uint64_t)per * threads;
+        cudaEventDestroy(e0);
+        cudaEventDestroy(e1);
+        be.free(sink);
+    } catch (std::exception& e) {
+        c->err = e.what();
+        return CLB_E_CUDA;
+    }
+    return CLB_OK;
+}

@@ -215,6 +215,7 @@ struct Batch {
     PartStore parts;
     // lists
     DevList<SearchTask> tasks;
+    DevList<u32> heavy;    // tasks whose frontier did not fit the warp's scratch (second search launch)
     DevList<Cand> cands;
     DevList<u32> extra;    // candidates with more than one cluster centre (second verification pass)
     u32* candStart;        // cands.cap : start of the verification window in the text (edit distance)

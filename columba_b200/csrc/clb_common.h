@@ -34,6 +34,13 @@ CLB_HD int popc64(u64 x) {
     return __builtin_popcountll(x);
 #endif
 }
+CLB_HD int ctz64(u64 x) { // x != 0
+#if defined(__CUDA_ARCH__)
+    return __ffsll((long long)x) - 1;
+#else
+    return __builtin_ctzll(x);
+#endif
+}
 CLB_HD int popcw(u64 x) { return popc64(x); }
 CLB_HD int popcw(u128 x) { return popc64((u64)x) + popc64((u64)(x >> 64)); }
 

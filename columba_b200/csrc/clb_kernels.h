@@ -5,7 +5,7 @@
 // same functors in a loop on the CPU to unit-test the kernel logic.
 #pragma once
 #include "clb_filter.h"
-#include "clb_search.h"
+#include "clb_frontier.h"
 
 namespace clb {
 
@@ -81,38 +81,85 @@ struct EmitKernel {
     CLB_HD void run(State& s, u32 t, unsigned act) const { partFinish(a.ix, *a.st, a.B, t, s.ps, s.lc, act); }
 };
 
-// stage 2
-template <typename W> struct SearchKernel {
+// stage 2: one warp per (read, strand, search) task (clb_frontier.h).  A task
+// whose frontier outgrows the warp's scratch is queued in B.heavy and run again
+// by a second launch of this kernel (heavy = 1) with large scratch.
+template <typename W> struct FrontierKernel {
+    static const bool kWarpTask = true;
     IndexView ix;
     const DevStrategy* st;
     Batch B;
     u8* slabs;
-    size_t slabBytes;
-    u32 stackCap, rowsCap, nFrames;
+    size_t slabBytes; // per warp
+    u32 heavy;
     struct State {
-        LocalCtr lc;
-        SearchScratch<W> sc;
+        LV<FCounters> ctr;
+        LV<u64> started, immediate;
+        u64 tasks;
+        u8* scr;
     };
-    CLB_HD void begin(State& s, u32 worker) const {
-        s.lc.clear();
-        s.sc = carveSearchScratch<W>(slabs + (size_t)worker * slabBytes, stackCap, rowsCap, nFrames);
+    CLB_HD void begin(State& s, u32 warp) const {
+        CLB_LANES(l) {
+            s.ctr[l].nodes = s.ctr[l].lookups = s.ctr[l].rows = s.ctr[l].fmOccs = 0;
+            s.started[l] = 0;
+            s.immediate[l] = 0;
+        }
+        s.tasks = 0;
+        s.scr = slabs + (size_t)warp * slabBytes;
     }
-    CLB_HD void run(State& s, u32 i) const {
-        const SearchTask task = B.tasks.data[i];
+    CLB_HD void runWarp(State& s, u32 i) const {
+        const u32 ti = heavy ? B.heavy.data[i] : i;
+        const SearchTask task = B.tasks.data[ti];
         const PartInfo pi = B.parts.load(task.t, st->P);
         const DevSearch& se = st->sc[pi.scheme].s[task.search];
-        SearchCtx<W> X(ix, B, se, pi, s.sc, s.lc, task.t, task.search);
-        s.lc.s[ST_SEARCH_TASKS]++;
-        const u64 before = s.lc.s[ST_RANK_LOOKUPS];
-        if (B.metric == METRIC_EDIT)
-            editSearchTask<W>(X);
-        else
-            hammingSearchTask<W>(X);
-        s.lc.s[ST_SEARCH_LOOKUPS] += s.lc.s[ST_RANK_LOOKUPS] - before;
-        if (X.err)
-            atomOr(B.err, X.err);
+        Frontier<W> F(ix, B, se, pi, task.t, task.search, s.scr, (u32)slabBytes);
+        LV<u64> started, immediate;
+        CLB_LANES(l) {
+            started[l] = 0;
+            immediate[l] = 0;
+        }
+        const bool ok = F.run(started, immediate);
+        if (!ok) {
+            CLB_LANES(l) {
+                if (l == 0) {
+                    if (F.err == ERR_STACK_OVERFLOW && !heavy)
+                        B.heavy.push(ti, B.err, ERR_TASK_OVERFLOW);
+                    else
+                        atomOr(B.err, F.err);
+                }
+            }
+            return;
+        }
+        s.tasks++;
+        CLB_LANES(l) {
+            s.ctr[l].nodes += F.ctr[l].nodes;
+            s.ctr[l].lookups += F.ctr[l].lookups;
+            s.ctr[l].rows += F.ctr[l].rows;
+            s.ctr[l].fmOccs += F.ctr[l].fmOccs;
+            s.started[l] += started[l];
+            s.immediate[l] += immediate[l];
+        }
     }
-    CLB_HD void end(State& s) const { s.lc.flush(B.counters, B.stats); }
+    CLB_HD void end(State& s) const {
+        CLB_LANES(l) {
+            if (s.ctr[l].nodes)
+                atomAdd64(B.counters + NODE_COUNTER, s.ctr[l].nodes);
+            if (s.ctr[l].lookups) {
+                atomAdd64(B.stats + ST_RANK_LOOKUPS, s.ctr[l].lookups);
+                atomAdd64(B.stats + ST_SEARCH_LOOKUPS, s.ctr[l].lookups);
+            }
+            if (s.ctr[l].rows)
+                atomAdd64(B.stats + ST_SEARCH_ROWS, s.ctr[l].rows);
+            if (s.ctr[l].fmOccs)
+                atomAdd64(B.stats + ST_FM_OCCS, s.ctr[l].fmOccs);
+            if (s.started[l])
+                atomAdd64(B.counters + SEARCH_STARTED, s.started[l]);
+            if (s.immediate[l])
+                atomAdd64(B.counters + IMMEDIATE_SWITCH, s.immediate[l]);
+            if (l == 0 && s.tasks)
+                atomAdd64(B.stats + ST_SEARCH_TASKS, s.tasks);
+        }
+    }
 };
 
 // exact stratum (k = 0): one task per read, both strands

@@ -28,7 +28,7 @@ struct BackendError : public std::runtime_error {
     explicit BackendError(const std::string& m) : std::runtime_error(m) {}
 };
 
-enum { WK_LIGHT = 0, WK_SEARCH = 1, WK_VERIFY = 2, WK_FILTER = 3 };
+enum { WK_LIGHT = 0, WK_SEARCH = 1, WK_VERIFY = 2, WK_FILTER = 3, WK_SEARCH_HEAVY = 4 };
 enum { STG_PREP, STG_PARTITION, STG_SEARCH, STG_VERIFY, STG_FM, STG_TEXT, N_STAGES };
 
 template <typename BE> struct DevBuf {
@@ -109,6 +109,7 @@ template <typename BE> struct Pipeline {
         bMisc, bSlabPart, bSlabSearch, bSlabVerify, bSlabVerifyWide, bSlabFilter, bStrategy;
     // list capacities (per read multipliers, grown after an overflow)
     double candPerRead = 24, fmPerRead = 4, txPerRead = 24, outPerRead = 8;
+    size_t searchSlabBytes = (size_t)256 << 10, heavySlabBytes = (size_t)32 << 20; // scratch per warp of the search
     u32 minCap = 1 << 16;
     std::string lastError;
 
@@ -126,7 +127,7 @@ template <typename BE> struct Pipeline {
         u64 counters[N_COUNTERS];
         u64 stats[N_STATS];
         u32 err;
-        u32 nTasks, nCands, nFm, nTx, nOut, nExtra, nCigJobs, nUniq;
+        u32 nTasks, nCands, nFm, nTx, nOut, nExtra, nCigJobs, nUniq, nHeavy;
         u32 nT, nR; // 2R and R as device-side task counts
     };
 
@@ -203,7 +204,7 @@ template <typename BE> struct Pipeline {
         const u32 capTasks = T * maxSearches + 16;
         const u32 capCands = capOf(candPerRead), capFm = capOf(fmPerRead), capTx = capOf(txPerRead),
                   capOut = capOf(outPerRead);
-        bTasks.ensure(be, (size_t)capTasks * sizeof(SearchTask));
+        bTasks.ensure(be, (size_t)capTasks * (sizeof(SearchTask) + sizeof(u32)));
         bCands.ensure(be, (size_t)capCands * sizeof(Cand));
         bCandAux.ensure(be, (size_t)capCands * 3 * sizeof(u32));
         const u32 capExtra = capCands / 4 + 1024;
@@ -223,6 +224,7 @@ template <typename BE> struct Pipeline {
         hm.nR = R;
         be.h2d(bMisc.p, &hm, sizeof(hm));
         B.tasks.data = (SearchTask*)bTasks.p; B.tasks.count = &M->nTasks; B.tasks.cap = capTasks;
+        B.heavy.data = (u32*)(B.tasks.data + capTasks); B.heavy.count = &M->nHeavy; B.heavy.cap = capTasks;
         B.cands.data = (Cand*)bCands.p; B.cands.count = &M->nCands; B.cands.cap = capCands;
         B.candStart = (u32*)bCandAux.p;
         B.candMult = B.candStart + capCands;
@@ -291,20 +293,26 @@ template <typename BE> struct Pipeline {
         }
         // ---- stage 2
         {
+            // one warp per task; a second launch with large scratch takes the tasks whose frontier
+            // outgrew the first launch's
             const bool wide = opt.k > BPC<u64>::MAX_ED;
-            const u32 rowsCap = maxLen + P * (2 * opt.k + (wide ? 70 : 40)) + 8;
-            const u32 stackCap = 3 * rowsCap + 8;
-            const u32 nw = be.workers(WK_SEARCH);
+            const u32 nWarps = be.workers(WK_SEARCH) / be.laneStride();
+            const u32 nHeavyWarps = be.workers(WK_SEARCH_HEAVY) / be.laneStride();
+            const size_t minSlab = ((size_t)(maxLen + 128) * 4 * (P + 2) + 65536 + 255) & ~(size_t)255;
+            const size_t sb = tmax<size_t>(searchSlabBytes, minSlab), hb = tmax<size_t>(heavySlabBytes, sb);
+            bSlabSearch.ensure(be, tmax<size_t>(sb * nWarps, hb * nHeavyWarps));
             if (wide) {
-                size_t sb = searchScratchBytes<u128>(stackCap, rowsCap, P);
-                bSlabSearch.ensure(be, sb * nw);
-                SearchKernel<u128> k2{ix, dst, B, (u8*)bSlabSearch.p, sb, stackCap, rowsCap, P};
+                FrontierKernel<u128> k2{ix, dst, B, (u8*)bSlabSearch.p, sb, 0};
                 be.launch(k2, capTasks, &M->nTasks, WK_SEARCH);
+                k2.slabBytes = hb;
+                k2.heavy = 1;
+                be.launch(k2, capTasks, &M->nHeavy, WK_SEARCH_HEAVY);
             } else {
-                size_t sb = searchScratchBytes<u64>(stackCap, rowsCap, P);
-                bSlabSearch.ensure(be, sb * nw);
-                SearchKernel<u64> k2{ix, dst, B, (u8*)bSlabSearch.p, sb, stackCap, rowsCap, P};
+                FrontierKernel<u64> k2{ix, dst, B, (u8*)bSlabSearch.p, sb, 0};
                 be.launch(k2, capTasks, &M->nTasks, WK_SEARCH);
+                k2.slabBytes = hb;
+                k2.heavy = 1;
+                be.launch(k2, capTasks, &M->nHeavy, WK_SEARCH_HEAVY);
             }
             be.mark(STG_SEARCH);
         }
@@ -375,6 +383,8 @@ template <typename BE> struct Pipeline {
             txPerRead = tmax(txPerRead * 2, (double)hm.nTx / R * 1.25 + 1);
         if (err & ERR_OUT_OVERFLOW)
             outPerRead = tmax(outPerRead * 2, (double)hm.nOut / R * 1.25);
+        if ((err & ERR_STACK_OVERFLOW) && heavySlabBytes < ((size_t)2 << 30))
+            heavySlabBytes *= 4; // a heavy search task outgrew even the large scratch
         if (minCap < (1u << 22) && (err & (ERR_CAND_OVERFLOW | ERR_FMOCC_OVERFLOW | ERR_TEXTOCC_OVERFLOW | ERR_OUT_OVERFLOW)))
             minCap *= 4;
         if (res) {
@@ -403,7 +413,7 @@ template <typename BE> struct Pipeline {
     // run with automatic re-run after list overflows
     u32 run(const DevStrategy& st, const u8* reads, const u32* off, u32 R, u32 maxLen, size_t totalBytes,
             bool readsOnDevice, const MapOptions& opt, MapResult<BE>* res, bool fetch) {
-        const u32 retry = ERR_CAND_OVERFLOW | ERR_FMOCC_OVERFLOW | ERR_TEXTOCC_OVERFLOW | ERR_OUT_OVERFLOW;
+        const u32 retry = ERR_CAND_OVERFLOW | ERR_FMOCC_OVERFLOW | ERR_TEXTOCC_OVERFLOW | ERR_OUT_OVERFLOW | ERR_STACK_OVERFLOW;
         u32 err = 0;
         for (int attempt = 0; attempt < 8; attempt++) {
             err = runOnce(st, reads, off, R, maxLen, totalBytes, readsOnDevice, opt, res, fetch);

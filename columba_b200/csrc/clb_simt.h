@@ -1,0 +1,104 @@
+// columba_b200 -- warp-cooperative code that also compiles for the CPU
+// unit-test harness (tests/hostemu).
+//
+// A warp-cooperative routine is written as a sequence of lane-parallel regions
+//     CLB_LANES(l) { ... per-lane work, lane index l ... }
+// separated by warp collectives (vote, scan, sync).  Values that live across
+// regions and differ per lane are LV<T> variables, indexed by the lane: on the
+// device an LV<T> is one register set per thread and a region runs once in
+// every thread of the warp; in the host emulation an LV<T> is an array of 32
+// and a region is a loop over the 32 lanes.  Everything outside a region is
+// warp-uniform: the device executes it redundantly in all lanes (it must not
+// have side effects other than writing the same value), the host once.
+#pragma once
+#include "clb_common.h"
+
+namespace clb {
+
+enum { GRP = 32 };
+
+#if defined(__CUDA_ARCH__)
+template <typename T> struct LV {
+    T v;
+    __device__ __forceinline__ T& operator[](int) { return v; }
+    __device__ __forceinline__ const T& operator[](int) const { return v; }
+};
+#define CLB_LANES(l) for (int l = (int)(threadIdx.x & 31u), l##_go = 1; l##_go; l##_go = 0)
+__device__ __forceinline__ void grpSync() { __syncwarp(); }
+__device__ __forceinline__ u32 grpBallot(const LV<u32>& p) { return __ballot_sync(0xFFFFFFFFu, p.v != 0); }
+// exclusive prefix sum over the lanes; returns the total
+__device__ __forceinline__ u32 grpExScan(const LV<u32>& x, LV<u32>& out) {
+    const u32 lane = threadIdx.x & 31u;
+    u32 incl = x.v;
+#pragma unroll
+    for (u32 o = 1; o < 32; o <<= 1) {
+        const u32 t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+        if (lane >= o)
+            incl += t;
+    }
+    out.v = incl - x.v;
+    return __shfl_sync(0xFFFFFFFFu, incl, 31);
+}
+__device__ __forceinline__ u32 grpSum(const LV<u32>& x) {
+    u32 s = x.v;
+#pragma unroll
+    for (u32 o = 16; o > 0; o >>= 1)
+        s += __shfl_xor_sync(0xFFFFFFFFu, s, o);
+    return s;
+}
+__device__ __forceinline__ u32 grpMax(const LV<u32>& x) {
+    u32 s = x.v;
+#pragma unroll
+    for (u32 o = 16; o > 0; o >>= 1) {
+        const u32 t = __shfl_xor_sync(0xFFFFFFFFu, s, o);
+        s = t > s ? t : s;
+    }
+    return s;
+}
+__device__ __forceinline__ u32 grpBcast(const LV<u32>& x, int src) { return __shfl_sync(0xFFFFFFFFu, x.v, src); }
+__device__ __forceinline__ u32 atomMinU32(u32* p, u32 v) { return atomicMin(p, v); }
+#else
+template <typename T> struct LV {
+    T v[GRP];
+    T& operator[](int l) { return v[l]; }
+    const T& operator[](int l) const { return v[l]; }
+};
+#define CLB_LANES(l) for (int l = 0; l < GRP; l++)
+inline void grpSync() {}
+inline u32 grpBallot(const LV<u32>& p) {
+    u32 m = 0;
+    for (int l = 0; l < GRP; l++)
+        m |= (p.v[l] != 0 ? 1u : 0u) << l;
+    return m;
+}
+inline u32 grpExScan(const LV<u32>& x, LV<u32>& out) {
+    u32 run = 0;
+    for (int l = 0; l < GRP; l++) {
+        const u32 v = x.v[l];
+        out.v[l] = run;
+        run += v;
+    }
+    return run;
+}
+inline u32 grpSum(const LV<u32>& x) {
+    u32 s = 0;
+    for (int l = 0; l < GRP; l++)
+        s += x.v[l];
+    return s;
+}
+inline u32 grpMax(const LV<u32>& x) {
+    u32 s = 0;
+    for (int l = 0; l < GRP; l++)
+        s = x.v[l] > s ? x.v[l] : s;
+    return s;
+}
+inline u32 grpBcast(const LV<u32>& x, int src) { return x.v[src]; }
+inline u32 atomMinU32(u32* p, u32 v) {
+    const u32 o = *p;
+    if (v < o)
+        *p = v;
+    return o;
+}
+#endif
+
+} // namespace clb

@@ -166,6 +166,10 @@ int clb_extend(clb_ctx*, int mode, const uint32_t* parents, uint32_t n, uint32_t
 int clb_find_sa(clb_ctx*, const uint32_t* rows, uint32_t n, uint32_t* out);
 int clb_kmer_lookup(clb_ctx*, const uint32_t* codes, uint32_t n, uint32_t* out4);
 
+/* Measured ceiling of the path's roofline unit: n_lookups independent random 32-byte rank-record reads from
+ * the loaded index (8 in flight per thread); *ms = kernel time (CUDA events), *done = reads issued. */
+int clb_gather_ceiling(clb_ctx*, uint64_t n_lookups, float* ms, uint64_t* done);
+
 /* ---- index construction for synthetic benchmarks (host, not the hot path;
  * writes the reference's file formats, src/buildindex.cpp) ---- */
 int clb_build_index(const char* fasta, const char* base, int sa_sparse, char* err, size_t err_len);

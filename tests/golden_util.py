@@ -45,14 +45,30 @@ def scheme_arg(params):
     return kind, arg
 
 
-def golden_fasta():
+def golden_fasta(name="g1"):
     os.makedirs(WORK, exist_ok=True)
-    fa = os.path.join(WORK, "g1.fa")
+    fa = os.path.join(WORK, name + ".fa")
     if not os.path.exists(fa):
-        with gzip.open(os.path.join(GOLD, "g1.fa.gz"), "rb") as i, open(fa + ".tmp", "wb") as o:
+        with gzip.open(os.path.join(GOLD, name + ".fa.gz"), "rb") as i, open(fa + ".tmp", "wb") as o:
             o.write(i.read())
         os.replace(fa + ".tmp", fa)
     return fa
+
+
+def reads_file(p):
+    """FASTQ of a case: g1_<reads>.fq.gz, or <reads>.fq.gz for the sets with their own reference."""
+    return os.path.join(GOLD, ("%s.fq.gz" % p["reads"]) if "fasta" in p else ("g1_%s.fq.gz" % p["reads"]))
+
+
+def index_of(p, lib_path):
+    """Index basename of a case's reference (built on first use by the product's host-side index writer)."""
+    import columba_b200 as cb
+    name = p.get("fasta", "g1")
+    fa = golden_fasta(name)
+    base = os.path.join(WORK, name)
+    if not os.path.exists(base + ".rev.brt") or not os.path.exists(base + ".meta"):
+        cb.build_index(fa, base, 4, lib_path=lib_path)
+    return base
 
 
 # counters of the reference's -v report -> names in our counter block

@@ -36,12 +36,18 @@ struct HostEmuBackend {
     void* hostAlloc(size_t n) { return std::malloc(n ? n : 16); }
     void hostFree(void* p) { std::free(p); }
     u32 fallbackWorkers() const { return 1; }
+    template <class K> static constexpr auto isWarpTask(int) -> decltype(K::kWarpTask) { return K::kWarpTask; }
+    template <class K> static constexpr bool isWarpTask(long) { return false; }
     template <class K> void launch(const K& k, u32 nMax, const u32* nDev, int) {
         u32 n = nDev ? (*nDev < nMax ? *nDev : nMax) : nMax;
         typename K::State st;
         k.begin(st, 0);
-        for (u32 i = 0; i < n; i++)
-            k.run(st, i);
+        for (u32 i = 0; i < n; i++) {
+            if constexpr (isWarpTask<K>(0))
+                k.runWarp(st, i); // the 32 lanes of the warp are emulated inside (clb_simt.h)
+            else
+                k.run(st, i);
+        }
         k.end(st);
         launches++;
     }

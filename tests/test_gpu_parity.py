@@ -17,10 +17,11 @@ CASES = gu.cases()
 def gpu_indexes(golden_index, cuda_lib):
     cache = {}
 
-    def get(kmer, in_text):
-        if (kmer, in_text) not in cache:
-            cache[(kmer, in_text)] = cb.Index(golden_index, 4, kmer, in_text, device=0, lib_path=cuda_lib)
-        return cache[(kmer, in_text)]
+    def get(kmer, in_text, p=None):
+        base = gu.index_of(p or {}, cuda_lib)
+        if (base, kmer, in_text) not in cache:
+            cache[(base, kmer, in_text)] = cb.Index(base, 4, kmer, in_text, device=0, lib_path=cuda_lib)
+        return cache[(base, kmer, in_text)]
     yield get
     for ix in cache.values():
         ix.close()
@@ -29,9 +30,9 @@ def gpu_indexes(golden_index, cuda_lib):
 @pytest.mark.parametrize("case", sorted(CASES))
 def test_gpu_matches_reference_golden(case, gpu_indexes):
     p = CASES[case]
-    ix = gpu_indexes(p.get("kmer", 10), p.get("in_text", 4))
+    ix = gpu_indexes(p.get("kmer", 10), p.get("in_text", 4), p)
     m = cb.Mapper(ix, gu.scheme_arg(p), p.get("metric", "edit"), p.get("partition", "dynamic"))
-    names, seqs = gu.read_fastq_gz(os.path.join(gu.GOLD, "g1_%s.fq.gz" % p["reads"]))
+    names, seqs = gu.read_fastq_gz(gu.reads_file(p))
     reads, off = cb.Mapper.pack(seqs)
     res = m.map_batch(reads, off, p["k"])
     exp, ctr = gu.expected(case)

@@ -26,10 +26,11 @@ def test_index_writer_is_byte_identical_to_reference(golden_index):
 def emu_indexes(golden_index, hostemu_lib):
     cache = {}
 
-    def get(kmer, in_text):
-        if (kmer, in_text) not in cache:
-            cache[(kmer, in_text)] = cb.Index(golden_index, 4, kmer, in_text, lib_path=hostemu_lib)
-        return cache[(kmer, in_text)]
+    def get(kmer, in_text, p=None):
+        base = gu.index_of(p or {}, hostemu_lib)
+        if (base, kmer, in_text) not in cache:
+            cache[(base, kmer, in_text)] = cb.Index(base, 4, kmer, in_text, lib_path=hostemu_lib)
+        return cache[(base, kmer, in_text)]
     yield get
     for ix in cache.values():
         ix.close()
@@ -38,9 +39,9 @@ def emu_indexes(golden_index, hostemu_lib):
 @pytest.mark.parametrize("case", sorted(CASES))
 def test_kernel_logic_matches_reference_golden(case, emu_indexes):
     p = CASES[case]
-    ix = emu_indexes(p.get("kmer", 10), p.get("in_text", 4))
+    ix = emu_indexes(p.get("kmer", 10), p.get("in_text", 4), p)
     m = cb.Mapper(ix, gu.scheme_arg(p), p.get("metric", "edit"), p.get("partition", "dynamic"))
-    names, seqs = gu.read_fastq_gz(os.path.join(gu.GOLD, "g1_%s.fq.gz" % p["reads"]))
+    names, seqs = gu.read_fastq_gz(gu.reads_file(p))
     reads, off = cb.Mapper.pack(seqs)
     res = m.map_batch(reads, off, p["k"])
     exp, ctr = gu.expected(case)

@@ -175,15 +175,24 @@ def gen_reads_fast(seqs, n_reads, read_len, seed, metric="edit", max_e=4, frac_o
     as gen_reads: edits ~ U{0..max_e} for 90 %, over_e for 5 %, exact for 5 %;
     each edit substitution .70 / insertion .15 / deletion .15; strands 50/50).
     Returns a uint8 matrix n_reads x read_len (ASCII)."""
-    rng = np.random.default_rng(seed)
     lens = np.array([len(s) for s in seqs], dtype=np.int64)
     starts = np.concatenate([[0], np.cumsum(lens)])
     cat = np.concatenate(seqs) if len(seqs) > 1 else seqs[0]
+    return gen_reads_cat(cat, starts, n_reads, read_len, seed, metric, max_e, frac_over, frac_exact, over_e)
+
+
+def gen_reads_cat(cat, starts, n_reads, read_len, seed, metric="edit", max_e=4, frac_over=0.05, frac_exact=0.05,
+                  over_e=6):
+    """gen_reads_fast on the concatenated text `cat` (uint8 ASCII, e.g. a memory-mapped .txt.bin) with the
+    sequence start offsets `starts` (numSeq + 1 entries)."""
+    rng = np.random.default_rng(seed)
+    starts = np.asarray(starts, dtype=np.int64)
+    lens = np.diff(starts)
     span = read_len + 8
     ok = lens > span + 8
     prob = np.where(ok, lens, 0).astype(np.float64)
     prob /= prob.sum()
-    sid = rng.choice(len(seqs), size=n_reads, p=prob)
+    sid = rng.choice(len(lens), size=n_reads, p=prob)
     p = (rng.random(n_reads) * (lens[sid] - span)).astype(np.int64) + starts[sid]
     strand = rng.integers(0, 2, n_reads)
     cls = rng.random(n_reads)
