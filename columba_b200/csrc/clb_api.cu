@@ -173,34 +173,50 @@ template <class K> constexpr bool isWarpTask(long) { return false; }
 
 // exclusive scan of n u32 values (out[n] = total) in three launches:
 // per-tile sums, scan of the tile sums by one block, per-tile scan + offset.
+// n = min(nMax, *nDev) when nDev is given (list sizes live on the device).
 static const u32 SCAN_TILE = 2048; // 256 threads x 8 values
-__global__ void __launch_bounds__(256) clb_scan_tile_sums(const u32* __restrict__ in, u32* __restrict__ sums, u32 n) {
+__device__ __forceinline__ u32 devCount(u32 nMax, const u32* nDev) {
+    if (!nDev)
+        return nMax;
+    const u32 v = *nDev;
+    return v < nMax ? v : nMax;
+}
+__global__ void __launch_bounds__(256) clb_scan_tile_sums(const u32* __restrict__ in, u32* __restrict__ sums, u32 nMax,
+                                                          const u32* __restrict__ nDev) {
     __shared__ u32 red[8];
-    const u32 base = blockIdx.x * SCAN_TILE;
-    u32 s = 0;
-    for (u32 q = 0; q < 8; q++) {
-        u32 i = base + q * 256 + threadIdx.x;
-        if (i < n)
-            s += in[i];
-    }
-    for (u32 o = 16; o > 0; o >>= 1)
-        s += __shfl_down_sync(0xFFFFFFFFu, s, o);
-    if ((threadIdx.x & 31) == 0)
-        red[threadIdx.x >> 5] = s;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        u32 t = 0;
-        for (u32 w = 0; w < 8; w++)
-            t += red[w];
-        sums[blockIdx.x] = t;
+    const u32 n = devCount(nMax, nDev);
+    const u32 nb = (n + SCAN_TILE - 1) / SCAN_TILE;
+    for (u32 tile = blockIdx.x; tile < nb; tile += gridDim.x) {
+        const u32 base = tile * SCAN_TILE;
+        u32 s = 0;
+        for (u32 q = 0; q < 8; q++) {
+            u32 i = base + q * 256 + threadIdx.x;
+            if (i < n)
+                s += in[i];
+        }
+        for (u32 o = 16; o > 0; o >>= 1)
+            s += __shfl_down_sync(0xFFFFFFFFu, s, o);
+        if ((threadIdx.x & 31) == 0)
+            red[threadIdx.x >> 5] = s;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            u32 t = 0;
+            for (u32 w = 0; w < 8; w++)
+                t += red[w];
+            sums[tile] = t;
+        }
+        __syncthreads();
     }
 }
-// in place exclusive scan of the tile sums by one block; total -> *total
-__global__ void __launch_bounds__(1024) clb_scan_sums(u32* __restrict__ sums, u32 nb, u32* __restrict__ total) {
+// in place exclusive scan of the tile sums by one block; total -> out[n]
+__global__ void __launch_bounds__(1024) clb_scan_sums(u32* __restrict__ sums, u32 nMax, const u32* __restrict__ nDev,
+                                                      u32* __restrict__ out) {
     __shared__ u32 part[1024];
+    const u32 n = devCount(nMax, nDev);
+    const u32 nb = (n + SCAN_TILE - 1) / SCAN_TILE;
     const u32 tid = threadIdx.x, nt = blockDim.x;
     const u32 per = (nb + nt - 1) / nt;
-    const u32 b = tid * per, e = (b + per < nb) ? b + per : nb;
+    const u32 b = tmin(tid * per, nb), e = tmin(b + per, nb);
     u32 sum = 0;
     for (u32 i = b; i < e; i++)
         sum += sums[i];
@@ -219,94 +235,178 @@ __global__ void __launch_bounds__(1024) clb_scan_sums(u32* __restrict__ sums, u3
         run += v;
     }
     if (tid == nt - 1)
-        *total = part[nt - 1];
+        out[n] = part[nt - 1];
 }
 __global__ void __launch_bounds__(256) clb_scan_tiles(const u32* __restrict__ in, u32* __restrict__ out,
-                                                      const u32* __restrict__ sums, u32 n) {
+                                                      const u32* __restrict__ sums, u32 nMax,
+                                                      const u32* __restrict__ nDev) {
     __shared__ u32 wsum[8];
-    const u32 base = blockIdx.x * SCAN_TILE + threadIdx.x * 8;
-    u32 v[8], s = 0;
-    for (u32 q = 0; q < 8; q++) {
-        v[q] = (base + q < n) ? in[base + q] : 0;
-        s += v[q];
-    }
-    // exclusive scan of s over the block
-    u32 incl = s;
-    const u32 lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    for (u32 o = 1; o < 32; o <<= 1) {
-        u32 t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
-        if (lane >= o)
-            incl += t;
-    }
-    if (lane == 31)
-        wsum[warp] = incl;
-    __syncthreads();
-    u32 woff = 0;
-    for (u32 w = 0; w < warp; w++)
-        woff += wsum[w];
-    u32 run = sums[blockIdx.x] + woff + incl - s;
-    for (u32 q = 0; q < 8; q++) {
-        if (base + q < n)
-            out[base + q] = run;
-        run += v[q];
+    const u32 n = devCount(nMax, nDev);
+    const u32 nb = (n + SCAN_TILE - 1) / SCAN_TILE;
+    for (u32 tile = blockIdx.x; tile < nb; tile += gridDim.x) {
+        const u32 base = tile * SCAN_TILE + threadIdx.x * 8;
+        u32 v[8], s = 0;
+        for (u32 q = 0; q < 8; q++) {
+            v[q] = (base + q < n) ? in[base + q] : 0;
+            s += v[q];
+        }
+        // exclusive scan of s over the block
+        u32 incl = s;
+        const u32 lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+        for (u32 o = 1; o < 32; o <<= 1) {
+            u32 t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+            if (lane >= o)
+                incl += t;
+        }
+        if (lane == 31)
+            wsum[warp] = incl;
+        __syncthreads();
+        u32 woff = 0;
+        for (u32 w = 0; w < warp; w++)
+            woff += wsum[w];
+        u32 run = sums[tile] + woff + incl - s;
+        for (u32 q = 0; q < 8; q++) {
+            if (base + q < n)
+                out[base + q] = run;
+            run += v[q];
+        }
+        __syncthreads();
     }
 }
 
-// Cooperative sort of the long per-read segments of txIdx (same order as the
-// per-read kernel's own sort: TxLess is a total order).  A CTA looks at 256
-// reads at a time, collects the ones with more than TXBIG_MIN and at most
-// TXBIG_MAX occurrences and sorts each of them with a bitonic network in
-// shared memory (padded with sentinels to a power of two).
-static const u32 TXBIG_MIN = 64, TXBIG_MAX = 8192;
-__global__ void __launch_bounds__(256) clb_sort_big_segments(const Batch B, u32 R) {
-    __shared__ u32 keys[TXBIG_MAX];
-    __shared__ u32 big[256];
-    __shared__ u32 nBig;
-    TxLess less;
-    less.d = B.textOccs.data;
-    for (u32 base = blockIdx.x * 256; base < R; base += gridDim.x * 256) {
-        if (threadIdx.x == 0)
-            nBig = 0;
+// Least-significant-digit radix sort of (u64 key, u32 value) pairs, 8 bits per
+// pass, three launches per pass: per-tile digit histograms (digit-major, so
+// that a row holds one digit's counts over the tiles), one CTA per digit turns
+// its row into exclusive prefix sums and writes the digit's total, and the
+// scatter pass ranks the keys of a tile stably -- warp by warp, eight rounds
+// of 32 keys, the lanes that hold the same digit found with match.any -- and
+// writes each pair to its final place of the pass.  n lives on the device.
+static const u32 RS_TILE = 2048; // 256 threads, 8 warps x 8 rounds x 32 keys
+__global__ void __launch_bounds__(256) clb_radix_hist(const u64* __restrict__ keys, u32 nMax, const u32* __restrict__ nDev,
+                                                      u32 shift, u32* __restrict__ hist) {
+    __shared__ u32 cnt[256];
+    const u32 n = devCount(nMax, nDev);
+    const u32 nTiles = (n + RS_TILE - 1) / RS_TILE;
+    const u32 lane = threadIdx.x & 31;
+    for (u32 tile = blockIdx.x; tile < nTiles; tile += gridDim.x) {
+        cnt[threadIdx.x] = 0;
         __syncthreads();
-        const u32 r = base + threadIdx.x;
-        if (r < R) {
-            const u32 n = B.txStart[r + 1] - B.txStart[r];
-            if (n > TXBIG_MIN && n <= TXBIG_MAX)
-                big[atomicAdd(&nBig, 1u)] = r;
+        const u32 base = tile * RS_TILE;
+#pragma unroll
+        for (u32 q = 0; q < 8; q++) {
+            const u32 i = base + q * 256 + threadIdx.x;
+            const u32 d = i < n ? (u32)(keys[i] >> shift) & 255u : 0xFFFFFFFFu;
+            const unsigned m = __match_any_sync(0xFFFFFFFFu, d);
+            if (d != 0xFFFFFFFFu && (int)lane == __ffs(m) - 1)
+                atomicAdd(&cnt[d], (u32)__popc(m));
         }
         __syncthreads();
-        const u32 nb = nBig;
-        for (u32 q = 0; q < nb; q++) {
-            const u32 rr = big[q];
-            u32* idx = B.txIdx + B.txStart[rr];
-            const u32 n = B.txStart[rr + 1] - B.txStart[rr];
-            u32 N = 1;
-            while (N < n)
-                N <<= 1;
-            for (u32 i = threadIdx.x; i < N; i += 256)
-                keys[i] = i < n ? idx[i] : 0xFFFFFFFFu;
-            __syncthreads();
-            for (u32 k = 2; k <= N; k <<= 1)
-                for (u32 j = k >> 1; j > 0; j >>= 1) {
-                    for (u32 i = threadIdx.x; i < N; i += 256) {
-                        const u32 l = i ^ j;
-                        if (l > i) {
-                            const u32 a = keys[i], b = keys[l];
-                            // sentinel = +infinity
-                            const bool ba = (a == 0xFFFFFFFFu) ? false : ((b == 0xFFFFFFFFu) ? false : less(b, a));
-                            const bool gt = (a == 0xFFFFFFFFu && b != 0xFFFFFFFFu) || ba; // a > b
-                            const bool asc = (i & k) == 0;
-                            if (gt == asc) {
-                                keys[i] = b;
-                                keys[l] = a;
-                            }
-                        }
-                    }
-                    __syncthreads();
-                }
-            for (u32 i = threadIdx.x; i < n; i += 256)
-                idx[i] = keys[i];
-            __syncthreads();
+        hist[(size_t)threadIdx.x * nTiles + tile] = cnt[threadIdx.x];
+        __syncthreads();
+    }
+}
+__global__ void __launch_bounds__(1024) clb_radix_scan(u32* __restrict__ hist, u32 nMax, const u32* __restrict__ nDev,
+                                                       u32* __restrict__ digitTotal) {
+    __shared__ u32 part[1024];
+    const u32 n = devCount(nMax, nDev);
+    const u32 nTiles = (n + RS_TILE - 1) / RS_TILE;
+    u32* row = hist + (size_t)blockIdx.x * nTiles;
+    const u32 tid = threadIdx.x, nt = blockDim.x;
+    const u32 per = (nTiles + nt - 1) / nt;
+    const u32 b = tmin(tid * per, nTiles), e = tmin(b + per, nTiles);
+    u32 sum = 0;
+    for (u32 i = b; i < e; i++)
+        sum += row[i];
+    part[tid] = sum;
+    __syncthreads();
+    for (u32 off = 1; off < nt; off <<= 1) {
+        u32 v = (tid >= off) ? part[tid - off] : 0;
+        __syncthreads();
+        part[tid] += v;
+        __syncthreads();
+    }
+    u32 run = part[tid] - sum;
+    for (u32 i = b; i < e; i++) {
+        u32 v = row[i];
+        row[i] = run;
+        run += v;
+    }
+    if (tid == nt - 1)
+        digitTotal[blockIdx.x] = part[nt - 1];
+}
+__global__ void __launch_bounds__(256) clb_radix_scatter(const u64* __restrict__ kin, const u32* __restrict__ vin,
+                                                         u64* __restrict__ kout, u32* __restrict__ vout, u32 nMax,
+                                                         const u32* __restrict__ nDev, u32 shift,
+                                                         const u32* __restrict__ hist,
+                                                         const u32* __restrict__ digitTotal) {
+    __shared__ u32 wcnt[8][256];
+    __shared__ u32 dbase[256];
+    __shared__ u32 wtot[8];
+    const u32 n = devCount(nMax, nDev);
+    const u32 nTiles = (n + RS_TILE - 1) / RS_TILE;
+    const u32 lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    {
+        // exclusive scan of the 256 digit totals
+        const u32 v = digitTotal[threadIdx.x];
+        u32 incl = v;
+        for (u32 o = 1; o < 32; o <<= 1) {
+            const u32 t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+            if (lane >= o)
+                incl += t;
+        }
+        if (lane == 31)
+            wtot[warp] = incl;
+        __syncthreads();
+        u32 woff = 0;
+        for (u32 w = 0; w < warp; w++)
+            woff += wtot[w];
+        dbase[threadIdx.x] = woff + incl - v;
+        __syncthreads();
+    }
+    for (u32 tile = blockIdx.x; tile < nTiles; tile += gridDim.x) {
+#pragma unroll
+        for (u32 w = 0; w < 8; w++)
+            wcnt[w][threadIdx.x] = 0;
+        __syncthreads();
+        const u32 base = tile * RS_TILE + warp * 256;
+        u64 key[8];
+        u32 rank[8];
+#pragma unroll
+        for (u32 q = 0; q < 8; q++) {
+            const u32 i = base + q * 32 + lane;
+            key[q] = i < n ? kin[i] : 0;
+            const u32 d = i < n ? (u32)(key[q] >> shift) & 255u : 0xFFFFFFFFu;
+            const unsigned m = __match_any_sync(0xFFFFFFFFu, d);
+            u32 r = 0;
+            if (d != 0xFFFFFFFFu)
+                r = wcnt[warp][d] + (u32)__popc(m & ((1u << lane) - 1u));
+            __syncwarp();
+            if (d != 0xFFFFFFFFu && (int)lane == __ffs(m) - 1)
+                wcnt[warp][d] += (u32)__popc(m);
+            __syncwarp();
+            rank[q] = r;
+        }
+        __syncthreads();
+        {
+            // digit t: place of its first key of this tile, then per warp
+            u32 run = dbase[threadIdx.x] + hist[(size_t)threadIdx.x * nTiles + tile];
+#pragma unroll
+            for (u32 w = 0; w < 8; w++) {
+                const u32 c = wcnt[w][threadIdx.x];
+                wcnt[w][threadIdx.x] = run;
+                run += c;
+            }
+        }
+        __syncthreads();
+#pragma unroll
+        for (u32 q = 0; q < 8; q++) {
+            const u32 i = base + q * 32 + lane;
+            if (i < n) {
+                const u32 d = (u32)(key[q] >> shift) & 255u;
+                const u32 dst = wcnt[warp][d] + rank[q];
+                kout[dst] = key[q];
+                vout[dst] = vin[i];
+            }
         }
         __syncthreads();
     }
@@ -322,6 +422,8 @@ struct CudaBackend {
     u32* workCtrs = nullptr; // pool of work counters, one per dynamic launch
     u32* scanSums = nullptr; // tile sums of exclusiveScan
     u32 scanCap = 0;
+    u32* radixHist = nullptr; // per-tile digit histograms of sortPairs + 256 digit totals
+    size_t radixCap = 0;
     u32 nextCtr = 0;
     static const u32 N_CTRS = 64;
     cudaEvent_t evBegin = nullptr, evEnd = nullptr, evStage[N_STAGES + 1];
@@ -362,6 +464,8 @@ struct CudaBackend {
             cudaFree(workCtrs);
         if (scanSums)
             cudaFree(scanSums);
+        if (radixHist)
+            cudaFree(radixHist);
         if (evBegin)
             cudaEventDestroy(evBegin);
         if (evEnd)
@@ -479,15 +583,11 @@ struct CudaBackend {
         CLB_CUDA(cudaGetLastError());
         launches++;
     }
-    u32 sortBigSegments(const Batch& B, u32 R) {
-        clb_sort_big_segments<<<(u32)numSMs * 4, 256, 0, stream>>>(B, R);
-        CLB_CUDA(cudaGetLastError());
-        launches++;
-        return TXBIG_MIN; // segments above TXBIG_MAX are left to the per-read kernel's own sort
-    }
-    u32 sortBigMax() const { return TXBIG_MAX; }
-    void exclusiveScan(const u32* in, u32* out, u32 n) {
-        const u32 nb = (n + SCAN_TILE - 1) / SCAN_TILE;
+    // exclusive scan of the first n = min(nMax, *nDev) values; out[n] = total
+    void exclusiveScan(const u32* in, u32* out, u32 nMax, const u32* nDev) {
+        if (nMax == 0)
+            return;
+        const u32 nb = (nMax + SCAN_TILE - 1) / SCAN_TILE;
         if (nb > scanCap) {
             if (scanSums) {
                 CLB_CUDA(cudaStreamSynchronize(stream));
@@ -496,11 +596,44 @@ struct CudaBackend {
             scanCap = nb + nb / 2 + 64;
             CLB_CUDA(cudaMalloc(&scanSums, scanCap * sizeof(u32)));
         }
-        clb_scan_tile_sums<<<nb, 256, 0, stream>>>(in, scanSums, n);
-        clb_scan_sums<<<1, 1024, 0, stream>>>(scanSums, nb, out + n);
-        clb_scan_tiles<<<nb, 256, 0, stream>>>(in, out, scanSums, n);
+        const u32 grid = tmin<u32>(nb, (u32)numSMs * 8);
+        clb_scan_tile_sums<<<grid, 256, 0, stream>>>(in, scanSums, nMax, nDev);
+        clb_scan_sums<<<1, 1024, 0, stream>>>(scanSums, nMax, nDev, out);
+        clb_scan_tiles<<<grid, 256, 0, stream>>>(in, out, scanSums, nMax, nDev);
         CLB_CUDA(cudaGetLastError());
         launches += 3;
+    }
+    // radix sort of the first n = min(nMax, *nDev) (key, value) pairs on the low keyBits bits of the keys;
+    // the pairs ping-pong between the two buffer pairs, the result is in pair sortResult(keyBits)
+    static u32 sortPasses(u32 keyBits) { return (keyBits + 7) / 8; }
+    static u32 sortResult(u32 keyBits) { return sortPasses(keyBits) & 1u; }
+    void sortPairs(u64* k0, u32* v0, u64* k1, u32* v1, u32 nMax, const u32* nDev, u32 keyBits) {
+        if (nMax == 0)
+            return;
+        const u32 nTiles = (nMax + RS_TILE - 1) / RS_TILE;
+        const size_t need = (size_t)nTiles * 256 + 256;
+        if (need > radixCap) {
+            if (radixHist) {
+                CLB_CUDA(cudaStreamSynchronize(stream));
+                cudaFree(radixHist);
+            }
+            radixCap = need + need / 4;
+            CLB_CUDA(cudaMalloc(&radixHist, radixCap * sizeof(u32)));
+        }
+        u32* digitTotal = radixHist + (size_t)nTiles * 256;
+        const u32 grid = tmin<u32>(nTiles, (u32)numSMs * 8);
+        u64* kk[2] = {k0, k1};
+        u32* vv[2] = {v0, v1};
+        const u32 passes = sortPasses(keyBits);
+        for (u32 p = 0; p < passes; p++) {
+            const u32 src = p & 1u, dst = src ^ 1u;
+            clb_radix_hist<<<grid, 256, 0, stream>>>(kk[src], nMax, nDev, 8 * p, radixHist);
+            clb_radix_scan<<<256, 1024, 0, stream>>>(radixHist, nMax, nDev, digitTotal);
+            clb_radix_scatter<<<grid, 256, 0, stream>>>(kk[src], vv[src], kk[dst], vv[dst], nMax, nDev, 8 * p, radixHist,
+                                                        digitTotal);
+            launches += 3;
+        }
+        CLB_CUDA(cudaGetLastError());
     }
     void mark(int stage) {
         if (stage >= 0 && stage < N_STAGES) {

@@ -113,6 +113,12 @@ struct OutOcc {
     u8 trimmed;     // FOUND_WITH_TRIMMING
 };
 
+// alignment of an occurrence after clipping at a sequence boundary (stage 6)
+struct TrimRec {
+    u32 b, e, seqID;
+    u8 dist, ncig, pad[2];
+};
+
 template <typename T> struct DevList {
     T* data;
     u32* count; // device counter
@@ -224,20 +230,21 @@ struct Batch {
     DevList<FMOccRec> fmOccs;
     DevList<TextOccRec> textOccs;
     u16* textCig;          // textOccs.cap x cigW
-    // per-read grouping
-    u32* fmCount;   // R+1
-    u32* fmStart;   // R+1 (exclusive scan)
-    u32* fmFill;    // R
-    u32* fmIdx;     // fmOccs.cap : indices grouped by read
-    u32* fmUnique;  // R : unique FM occurrences per read (after sort+unique)
-    u32* txCount;   // R+1
-    u32* txStart;   // R+1
-    u32* txFill;    // R
-    u32* txIdx;     // textOccs.cap
-    u32* txTmp;     // textOccs.cap : merge-sort scratch
-    u32 txPresorted, txPresortedMax; // segments with (txPresorted, txPresortedMax] entries were sorted by the backend's cooperative sort
-    u32* outCount;  // R+1 : surviving occurrences per read
-    u32* outStart;  // R+1
+    // grouping by read (stages 4-6): keys (group << 32 | begin) and list indices, sorted by the backend's
+    // radix sort (ping-pong buffers; sortRes = the pair that holds the sorted result).  The other pair is
+    // scratch afterwards: its values hold the widths / keep flags, its keys the prefix sums.
+    u64* sortKey[2];
+    u32* sortVal[2];
+    u32 sortRes;
+    u32* fmSlots;   // [0] first slot of the expanded index occurrences in textOccs, [1] their number
+    u16* fmCig;     // fmOccs.cap x cigW : shared CIGAR of the occurrences with more than CIGAR_THRESHOLD rows
+    u8* fmNcig;     // fmOccs.cap
+    DevList<u32> trimJobs;      // sorted slots of kept occurrences that cross a sequence end
+    TrimRec* trimRecs;          // per job: the clipped alignment
+    u16* trimCig;               // per job x cigW
+    u32* trimOf;                // per sorted slot: its job
+    u32* outCount;  // G+1 : surviving occurrences per group
+    u32* outStart;  // G+1 : first output slot of the group (outStart[G] = number of outputs)
     DevList<OutOcc> out;
     u16* outCig;    // out.cap x cigW
     DevList<u32> cigJobs;  // indices into out[] whose CIGAR is still to be computed (index occurrences)

@@ -194,70 +194,131 @@ CLB_HD u32 cigarForOcc(const IndexView& ix, const Batch& B, u32 t, u32 b, u32 e,
     return n;
 }
 
-// stage 4 task: dedup the FM occurrences of read r and expand them to text
-// occurrences.
-CLB_HD void fmPerReadTask(const IndexView& ix, const Batch& B, u32 r, FilterScratch& fs, LocalCtr& lc) {
-    const u32 s0 = B.fmStart[r], s1 = B.fmStart[r + 1];
-    if (s1 == s0)
+// ---- stage 4: index occurrences -> text occurrences, as global passes ------
+// (the reference does this per read: Occurrences::eraseDoublesFM
+// src/indexhelpers.h:2135-2143 then getTextPositionsFromSARange per unique
+// occurrence, src/indexinterface.cpp:1373-1491).  Here every index occurrence of
+// the batch gets the key (group, SA begin), the keys are sorted by the
+// backend's radix sort, runs of equal keys are put in FMLess order and made
+// unique by their first lane, a prefix sum over the range widths of the
+// survivors gives every (occurrence, row) pair its slot in the text-occurrence
+// list, and one thread per slot does the locate.
+CLB_HD u64 groupKey(u32 g, u32 b) { return ((u64)g << 32) | b; }
+CLB_HD u32 keyGroup(u64 k) { return (u32)(k >> 32); }
+CLB_HD u32 listSize(const u32* count, u32 cap) { return tmin(*count, cap); }
+// consecutive sorted keys of the same group whose begins are at most maxDiff apart
+CLB_HD bool keysLinked(u64 prev, u64 cur, u32 maxDiff) {
+    return keyGroup(prev) == keyGroup(cur) && (u32)cur - (u32)prev <= maxDiff;
+}
+
+CLB_HD void fmKeyTask(const Batch& B, u32 i) {
+    const FMOccRec& f = B.fmOccs.data[i];
+    B.sortKey[0][i] = groupKey(groupOf(B, f.t), f.sa.b);
+    B.sortVal[0][i] = i;
+}
+// run head: order the run, mark the unique occurrences with their widths
+CLB_HD void fmRunTask(const Batch& B, u32 i, LocalCtr& lc) {
+    const u32 n = listSize(B.fmOccs.count, B.fmOccs.cap);
+    const u64* keys = B.sortKey[B.sortRes];
+    u32* vals = B.sortVal[B.sortRes];
+    u32* width = B.sortVal[1 - B.sortRes];
+    if (i > 0 && keys[i] == keys[i - 1])
         return;
-    u32* idx = B.fmIdx + s0;
-    const u32 n = s1 - s0;
+    u32 e = i + 1;
+    while (e < n && keys[e] == keys[i])
+        e++;
     const FMOccRec* d = B.fmOccs.data;
     FMLess less;
     less.d = d;
-    heapSortIdx(idx, n, less);
-    // unique (adjacent)
-    u32 m = 0;
-    for (u32 i = 0; i < n; i++) {
-        if (m > 0) {
-            const FMOccRec &a = d[idx[m - 1]], &b = d[idx[i]];
-            if (a.sa.b == b.sa.b && a.sa.e == b.sa.e && a.dist == b.dist && a.depth == b.depth &&
-                a.shift == b.shift && (a.t & 1) == (b.t & 1))
+    heapSortIdx(vals + i, e - i, less);
+    u32 last = i;
+    u64 total = 0;
+    for (u32 j = i; j < e; j++) {
+        if (j > i) {
+            const FMOccRec &a = d[vals[last]], &b = d[vals[j]];
+            if (a.sa.e == b.sa.e && a.dist == b.dist && a.depth == b.depth && a.shift == b.shift &&
+                (a.t & 1) == (b.t & 1)) {
+                width[j] = 0;
                 continue;
-        }
-        idx[m++] = idx[i];
-    }
-    const u32 hamSize = d[idx[0]].depth;
-    for (u32 j = 0; j < m; j++) {
-        const FMOccRec f = d[idx[j]];
-        const u32 w = f.sa.width();
-        lc.c[TOTAL_REPORTED_POSITIONS] += w;
-        u32 at = B.textOccs.reserve(w, B.err, ERR_TEXTOCC_OVERFLOW);
-        if (at == 0xFFFFFFFFu)
-            return;
-        const bool edit = B.metric == METRIC_EDIT;
-        const bool calc = edit && !B.noCigarFlag && w > 10; // CIGAR_THRESHOLD
-        u32 ncig = 0;
-        for (u32 i = 0; i < w; i++) {
-            u32 pos = findSA(ix, f.sa.b + i, lc.s[ST_LF_STEPS]);
-            TextOccRec o;
-            o.t = f.t;
-            o.b = edit ? pos + f.shift : pos;
-            o.e = o.b + (edit ? f.depth : hamSize);
-            o.order = j;
-            o.order2 = i;
-            o.dist = (u8)f.dist;
-            o.cls = 1;
-            o.pad = 0;
-            o.ncig = 0;
-            u16* dst = B.textCig + (size_t)(at + i) * B.cigW;
-            if (!edit) {
-                if (!B.noCigarFlag) {
-                    o.ncig = 1;
-                    dst[0] = (u16)((hamSize << 2) | CIG_M);
-                }
-            } else if (calc) {
-                if (i == 0) {
-                    ncig = cigarForOcc(ix, B, f.t, o.b, o.e, f.dist, fs, fs.ops, lc);
-                }
-                o.ncig = (u8)ncig;
-                for (u32 q = 0; q < ncig; q++)
-                    dst[q] = fs.ops[q];
             }
-            B.textOccs.data[at + i] = o;
         }
-        lc.s[ST_TEXT_OCCS] += w;
+        last = j;
+        const u32 w = d[vals[j]].sa.width();
+        width[j] = w;
+        total += w;
     }
+    lc.c[TOTAL_REPORTED_POSITIONS] += total;
+    lc.s[ST_TEXT_OCCS] += total;
+}
+// slots of the expansion in the text-occurrence list (one thread)
+CLB_HD void fmReserveTask(const Batch& B) {
+    const u32 n = listSize(B.fmOccs.count, B.fmOccs.cap);
+    const u32* wOff = (const u32*)B.sortKey[1 - B.sortRes];
+    const u32 total = n ? wOff[n] : 0u;
+    const u32 base = *B.textOccs.count;
+    B.fmSlots[0] = base;
+    B.fmSlots[1] = total;
+    if (base > B.textOccs.cap || total > B.textOccs.cap - base) {
+        atomOr(B.err, ERR_TEXTOCC_OVERFLOW);
+        B.fmSlots[1] = 0;
+    }
+    const u64 sum = (u64)base + total;
+    *B.textOccs.count = sum > 0xFFFFFFFFull ? 0xFFFFFFFFu : (u32)sum;
+}
+// CIGAR of an occurrence with more than CIGAR_THRESHOLD rows: computed once for its first
+// row and shared by all of them (getTextPositionsFromSARange, src/indexinterface.cpp:1416-1431)
+CLB_HD void fmCigarTask(const IndexView& ix, const Batch& B, u32 j, FilterScratch& fs, LocalCtr& lc) {
+    const u32* vals = B.sortVal[B.sortRes];
+    const u32* width = B.sortVal[1 - B.sortRes];
+    if (B.metric != METRIC_EDIT || B.noCigarFlag || width[j] <= 10)
+        return;
+    const FMOccRec f = B.fmOccs.data[vals[j]];
+    u64 lf = 0;
+    const u32 b = findSA(ix, f.sa.b, lf) + f.shift;
+    B.fmNcig[j] = (u8)cigarForOcc(ix, B, f.t, b, b + f.depth, f.dist, fs, B.fmCig + (size_t)j * B.cigW, lc);
+}
+// one (occurrence, row) pair: locate
+CLB_HD void fmExpandTask(const IndexView& ix, const Batch& B, u32 s, LocalCtr& lc) {
+    const u32 n = listSize(B.fmOccs.count, B.fmOccs.cap);
+    const u32* vals = B.sortVal[B.sortRes];
+    const u32* wOff = (const u32*)B.sortKey[1 - B.sortRes];
+    u32 lo = 0, hi = n; // last j with wOff[j] <= s
+    while (hi - lo > 1) {
+        const u32 mid = (lo + hi) >> 1;
+        if (wOff[mid] <= s)
+            lo = mid;
+        else
+            hi = mid;
+    }
+    const u32 j = lo, i = s - wOff[j], w = wOff[j + 1] - wOff[j];
+    const FMOccRec f = B.fmOccs.data[vals[j]];
+    const bool edit = B.metric == METRIC_EDIT;
+    const u32 pos = findSA(ix, f.sa.b + i, lc.s[ST_LF_STEPS]);
+    const u32 at = B.fmSlots[0] + s;
+    TextOccRec o;
+    o.t = f.t;
+    o.b = edit ? pos + f.shift : pos;
+    o.e = o.b + f.depth;
+    o.order = wOff[j]; // increases with the occurrence's place in its read's sorted list
+    o.order2 = i;
+    o.dist = (u8)f.dist;
+    o.cls = 1;
+    o.pad = 0;
+    o.ncig = 0;
+    u16* dst = B.textCig + (size_t)at * B.cigW;
+    if (!edit) {
+        if (!B.noCigarFlag) {
+            o.ncig = 1;
+            dst[0] = (u16)((f.depth << 2) | CIG_M);
+        }
+    } else if (!B.noCigarFlag && w > 10) { // CIGAR_THRESHOLD
+        const u32 ncig = B.fmNcig[j];
+        const u16* src = B.fmCig + (size_t)j * B.cigW;
+        o.ncig = (u8)ncig;
+        for (u32 q = 0; q < ncig; q++)
+            dst[q] = src[q];
+    }
+    B.textOccs.data[at] = o;
 }
 
 struct TrimSink {
@@ -282,136 +343,255 @@ struct TrimSink {
     }
 };
 
-// stage 6 task: filter the text occurrences of read r and write the output
-// `act`: the lanes of the warp that run this function side by side (they meet
-// again before the output slots are reserved, so that one atomic serves them all)
-CLB_HD void txPerReadTask(const IndexView& ix, const Batch& B, u32 r, FilterScratch& fs, LocalCtr& lc, unsigned act) {
-    const u32 s0 = B.txStart[r], s1 = B.txStart[r + 1];
-    B.outStart[r] = 0;
-    B.outCount[r] = 0;
-    u32* idx = B.txIdx + s0;
-    const u32 n = s1 - s0;
-    TextOccRec* d = B.textOccs.data;
-    TxLess less;
-    less.d = d;
-    if (n > 1 && (n <= B.txPresorted || n > B.txPresortedMax)) // the others: see Backend::sortBigSegments
-        heapSortIdx(idx, n, less);
-    u32 m = 0;
-    for (u32 i = 0; i < n; i++) {
-        if (m > 0 && !B.noFilter) {
-            const TextOccRec &a = d[idx[m - 1]], &b = d[idx[i]];
-            if (a.b == b.b && a.e == b.e && a.dist == b.dist)
-                continue;
-        }
-        idx[m++] = idx[i];
-    }
-    const bool edit = B.metric == METRIC_EDIT;
-    u32 nOut = m;
-    if (edit && !B.noFilter) { // redundancy filter, indexinterface.cpp:1451-1485
-        const u32 maxDiff = 2 * B.k;
-        u32 prevBegin = 0xFFFFFFFFu, prevDepth = 0xFFFFFFFFu, prevED = B.k + 1;
-        nOut = 0;
-        for (u32 i = 0; i < m; i++) {
-            const TextOccRec& o = d[idx[i]];
-            u32 diff = o.b > prevBegin ? o.b - prevBegin : prevBegin - o.b;
-            if (diff == 0)
-                continue;
-            u32 width = o.e <= o.b ? 0 : o.e - o.b;
-            if (diff <= maxDiff) {
-                if (o.dist > prevED || (o.dist == prevED && width >= prevDepth))
-                    continue;
-                nOut--;
-            }
-            prevBegin = o.b;
-            prevED = o.dist;
-            prevDepth = width;
-            idx[nOut++] = idx[i];
-        }
-    }
-    warpSync(act);
-    u32 at = B.out.reserve(nOut, B.err, ERR_OUT_OVERFLOW);
-    if (at == 0xFFFFFFFFu || nOut == 0)
+// ---- stages 5-6: sort, unique, redundancy filter, sequence assignment --------
+// (the reference: Occurrences::eraseDoublesAndSortText src/indexhelpers.h:2149-2157,
+// the filter loop of getUniqueTextOccurrences src/indexinterface.cpp:1451-1485,
+// findSeqName :799-897 in the assignment loop of generateOutputSingleEnd
+// src/searchstrategy.cpp:1824-1856; all of it per read.)  Global passes here:
+// key (group, begin) per text occurrence, radix sort, runs of equal keys put in
+// TxLess order by their first lane.  The filter is a sequential scan whose
+// state is the last kept occurrence; an occurrence that begins more than 2k
+// after its predecessor in sorted order is kept whatever the state is, so the
+// sorted list splits into independent CHAINS at those gaps and at group
+// boundaries, and one thread walks one chain.  Survivors get their output slot
+// from a prefix sum over the keep flags, so every read's occurrences are
+// contiguous and in text order without gaps.
+CLB_HD void txKeyTask(const Batch& B, u32 i) {
+    const TextOccRec& o = B.textOccs.data[i];
+    B.sortKey[0][i] = groupKey(groupOf(B, o.t), o.b);
+    B.sortVal[0][i] = i;
+}
+CLB_HD void txRunTask(const Batch& B, u32 i) {
+    const u32 n = listSize(B.textOccs.count, B.textOccs.cap);
+    const u64* keys = B.sortKey[B.sortRes];
+    u32* vals = B.sortVal[B.sortRes];
+    if (i + 1 >= n || keys[i + 1] != keys[i] || (i > 0 && keys[i] == keys[i - 1]))
         return;
-    u32 w = 0;
-    for (u32 i = 0; i < nOut; i++) {
-        TextOccRec o = d[idx[i]];
-        u16* cig = B.textCig + (size_t)idx[i] * B.cigW;
-        // generateCIGARS for index occurrences (indexinterface.h:939-949): the
-        // alignment itself is left to a dense follow-up kernel (cigarJobTask)
-        const bool pending = edit && !B.noCigarFlag && o.ncig == 0;
-        // findSeqName, indexinterface.cpp:799-897
-        u32 lo = 0, hi = ix.numSeq + 1; // upper_bound over seqStart[0..numSeq]
-        while (lo < hi) {
-            u32 mid = (lo + hi) >> 1;
-            if (ix.seqStart[mid] <= o.b)
-                lo = mid + 1;
-            else
-                hi = mid;
-        }
-        u32 index = lo - 1;
-        OutOcc out;
-        out.read = B.grpShift ? r : (r >> 1);
-        out.strand = (u8)(o.t & 1);
-        u32 ncig = o.ncig;
-        const u16* src = cig;
-        if (o.e <= ix.seqStart[index + 1]) {
-            if (pending)
-                B.cigJobs.push(at + w, B.err, ERR_OUT_OVERFLOW);
-            out.trimmed = 0;
-            out.indexBegin = o.b;
-            out.pos = o.b - ix.seqStart[index];
-            out.end = o.e - ix.seqStart[index];
-            out.dist = o.dist;
-        } else {
-            if (!edit)
-                continue;
-            if (pending)
-                lc.c[CIGARS_IN_INDEX]++; // computed by the reference, then superseded by the trimmed alignment
-            u32 nb, ne;
-            const u32 largest = B.trimMax; // ALL mode: k; BEST mode: the cut-off (indexinterface.cpp:799-897)
-            if ((ix.seqStart[index + 1] - o.b) <= largest) {
-                index++;
-                nb = ix.seqStart[index];
-                ne = tmin(o.e, ix.seqStart[index + 1]);
-            } else if ((o.e - ix.seqStart[index + 1]) <= largest) {
-                nb = o.b;
-                ne = ix.seqStart[index + 1];
-            } else
-                continue;
-            // inTextVerificationOneString, fmindex.cpp:312-342
-            TrimSink sink;
-            sink.any = false;
-            sink.bestOps = fs.ops + B.cigW;
-            bool considered = true, ok;
-            lc.c[IN_TEXT_STARTED]++;
-            if (use64(1, largest))
-                ok = verifyWindow<u64>(ix, B, o.t, (Row<u64>*)fs.rows, nb, ne, 1, largest, 0, fs.ops, B.cigW, lc,
-                                       considered, sink);
-            else
-                ok = verifyWindow<u128>(ix, B, o.t, (Row<u128>*)fs.rows, nb, ne, 1, largest, 0, fs.ops, B.cigW, lc,
-                                        considered, sink);
-            if (!ok && considered)
-                lc.c[ABORTED_IN_TEXT_VERIF]++;
-            if (!sink.any)
-                continue;
-            out.trimmed = 1;
-            out.indexBegin = sink.best.b;
-            out.pos = sink.best.b - ix.seqStart[index];
-            out.end = sink.best.e - ix.seqStart[index];
-            out.dist = (u8)sink.best.dist;
-            ncig = B.noCigarFlag ? 0 : sink.best.ncig;
-            src = sink.bestOps;
-        }
-        out.seqID = index;
-        out.ncig = (u8)ncig;
-        B.out.data[at + w] = out;
-        u16* dst = B.outCig + (size_t)(at + w) * B.cigW;
-        for (u32 q = 0; q < ncig; q++)
-            dst[q] = src[q];
-        w++;
+    u32 e = i + 2;
+    while (e < n && keys[e] == keys[i])
+        e++;
+    TxLess less;
+    less.d = B.textOccs.data;
+    heapSortIdx(vals + i, e - i, less);
+}
+// findSeqName for a kept occurrence at sorted slot `slot`: 1 = inside one sequence; 0 = dropped,
+// or it crosses a sequence end and is queued for txTrimTask, which may set the flag again
+CLB_HD u32 txAssign(const IndexView& ix, const Batch& B, const TextOccRec& o, u32 slot) {
+    if (o.dist < B.minD) // SearchStrategy::mapRead, src/searchstrategy.h:510-515: removed after the filter
+        return 0u;
+    u32 lo = 0, hi = ix.numSeq + 1; // upper_bound over seqStart[0..numSeq]
+    while (lo < hi) {
+        const u32 mid = (lo + hi) >> 1;
+        if (ix.seqStart[mid] <= o.b)
+            lo = mid + 1;
+        else
+            hi = mid;
     }
-    B.outStart[r] = at;
-    B.outCount[r] = w;
+    if (o.e <= ix.seqStart[lo])
+        return 1u;
+    if (B.metric != METRIC_EDIT)
+        return 0u;
+    B.trimJobs.push(slot, B.err, ERR_OUT_OVERFLOW);
+    return 0u;
+}
+CLB_HD void txChainTask(const IndexView& ix, const Batch& B, u32 i) {
+    const u32 n = listSize(B.textOccs.count, B.textOccs.cap);
+    const u64* keys = B.sortKey[B.sortRes];
+    const u32* vals = B.sortVal[B.sortRes];
+    u32* flag = B.sortVal[1 - B.sortRes];
+    const TextOccRec* d = B.textOccs.data;
+    const bool filter = B.metric == METRIC_EDIT && !B.noFilter;
+    const u32 maxDiff = filter ? 2 * B.k : 0u;
+    if (i > 0 && keysLinked(keys[i - 1], keys[i], maxDiff))
+        return; // same group and within reach of the predecessor: not the head of a chain
+    u32 prevBegin = 0xFFFFFFFFu, prevDepth = 0xFFFFFFFFu, prevED = B.k + 1;
+    u32 pending = 0xFFFFFFFFu, lastU = 0xFFFFFFFFu;
+    for (u32 j = i; j < n; j++) {
+        if (j > i && !keysLinked(keys[j - 1], keys[j], maxDiff))
+            break;
+        const TextOccRec& o = d[vals[j]];
+        if (!B.noFilter && lastU != 0xFFFFFFFFu) { // unique
+            const TextOccRec& a = d[vals[lastU]];
+            if (a.b == o.b && a.e == o.e && a.dist == o.dist) {
+                flag[j] = 0;
+                continue;
+            }
+        }
+        lastU = j;
+        if (!filter) {
+            flag[j] = txAssign(ix, B, o, j);
+            continue;
+        }
+        const u32 diff = o.b > prevBegin ? o.b - prevBegin : prevBegin - o.b;
+        const u32 width = o.e <= o.b ? 0u : o.e - o.b;
+        if (diff == 0) {
+            flag[j] = 0;
+            continue;
+        }
+        if (diff <= maxDiff) {
+            if (o.dist > prevED || (o.dist == prevED && width >= prevDepth)) {
+                flag[j] = 0;
+                continue;
+            }
+            flag[pending] = 0; // the better occurrence replaces the last kept one
+        } else if (pending != 0xFFFFFFFFu) {
+            flag[pending] = txAssign(ix, B, d[vals[pending]], pending);
+        }
+        prevBegin = o.b;
+        prevED = o.dist;
+        prevDepth = width;
+        pending = j;
+    }
+    if (pending != 0xFFFFFFFFu)
+        flag[pending] = txAssign(ix, B, d[vals[pending]], pending);
+}
+// an occurrence that crosses a sequence end: clip and re-verify
+// (findSeqName src/indexinterface.cpp:838-897, inTextVerificationOneString src/fmindex/fmindex.cpp:312-342)
+CLB_HD void txTrimTask(const IndexView& ix, const Batch& B, u32 job, FilterScratch& fs, LocalCtr& lc) {
+    const u32 slot = B.trimJobs.data[job];
+    const u32* vals = B.sortVal[B.sortRes];
+    u32* flag = B.sortVal[1 - B.sortRes];
+    const TextOccRec o = B.textOccs.data[vals[slot]];
+    flag[slot] = 0;
+    u32 lo = 0, hi = ix.numSeq + 1;
+    while (lo < hi) {
+        const u32 mid = (lo + hi) >> 1;
+        if (ix.seqStart[mid] <= o.b)
+            lo = mid + 1;
+        else
+            hi = mid;
+    }
+    u32 index = lo - 1;
+    if (B.metric == METRIC_EDIT && !B.noCigarFlag && o.ncig == 0)
+        lc.c[CIGARS_IN_INDEX]++; // computed by the reference, then superseded by the clipped alignment
+    u32 nb, ne;
+    const u32 largest = B.trimMax; // ALL mode: k; BEST mode: the cut-off
+    if ((ix.seqStart[index + 1] - o.b) <= largest) {
+        index++;
+        nb = ix.seqStart[index];
+        ne = tmin(o.e, ix.seqStart[index + 1]);
+    } else if ((o.e - ix.seqStart[index + 1]) <= largest) {
+        nb = o.b;
+        ne = ix.seqStart[index + 1];
+    } else
+        return;
+    TrimSink sink;
+    sink.any = false;
+    sink.bestOps = B.trimCig + (size_t)job * B.cigW;
+    bool considered = true, ok;
+    lc.c[IN_TEXT_STARTED]++;
+    if (use64(1, largest))
+        ok = verifyWindow<u64>(ix, B, o.t, (Row<u64>*)fs.rows, nb, ne, 1, largest, 0, fs.ops, B.cigW, lc, considered,
+                               sink);
+    else
+        ok = verifyWindow<u128>(ix, B, o.t, (Row<u128>*)fs.rows, nb, ne, 1, largest, 0, fs.ops, B.cigW, lc, considered,
+                                sink);
+    if (!ok && considered)
+        lc.c[ABORTED_IN_TEXT_VERIF]++;
+    if (!sink.any)
+        return;
+    TrimRec tr;
+    tr.b = sink.best.b;
+    tr.e = sink.best.e;
+    tr.seqID = index;
+    tr.dist = (u8)sink.best.dist;
+    tr.ncig = (u8)(B.noCigarFlag ? 0u : sink.best.ncig);
+    tr.pad[0] = o.dist; // distance before clipping
+    tr.pad[1] = 0;
+    B.trimRecs[job] = tr;
+    B.trimOf[slot] = job;
+    flag[slot] = 1;
+}
+// number of survivors (one thread)
+CLB_HD void txReserveTask(const Batch& B) {
+    const u32 n = listSize(B.textOccs.count, B.textOccs.cap);
+    const u32* offs = (const u32*)B.sortKey[1 - B.sortRes];
+    const u32 total = n ? offs[n] : 0u;
+    *B.out.count = total;
+    if (total > B.out.cap)
+        atomOr(B.err, ERR_OUT_OVERFLOW);
+}
+// survivor at sorted slot i -> output record; first slot of a group -> the group's start
+CLB_HD void txEmitTask(const IndexView& ix, const Batch& B, u32 i) {
+    const u32 n = listSize(B.textOccs.count, B.textOccs.cap);
+    const u64* keys = B.sortKey[B.sortRes];
+    const u32* vals = B.sortVal[B.sortRes];
+    const u32* flag = B.sortVal[1 - B.sortRes];
+    const u32* offs = (const u32*)B.sortKey[1 - B.sortRes];
+    const u32 g = keyGroup(keys[i]);
+    {
+        const u32 first = i ? keyGroup(keys[i - 1]) + 1 : 0u;
+        for (u32 q = first; q <= g; q++)
+            B.outStart[q] = offs[i];
+        if (i + 1 == n)
+            for (u32 q = g + 1; q <= B.G; q++)
+                B.outStart[q] = offs[n];
+    }
+    if (!flag[i])
+        return;
+    const u32 at = offs[i];
+    if (at >= B.out.cap)
+        return;
+    const u32 ti = vals[i];
+    const TextOccRec o = B.textOccs.data[ti];
+    OutOcc out;
+    out.read = B.grpShift ? g : (g >> 1);
+    out.strand = (u8)(o.t & 1);
+    const u16* src = B.textCig + (size_t)ti * B.cigW;
+    u32 ncig = o.ncig;
+    u32 lo = 0, hi = ix.numSeq + 1;
+    while (lo < hi) {
+        const u32 mid = (lo + hi) >> 1;
+        if (ix.seqStart[mid] <= o.b)
+            lo = mid + 1;
+        else
+            hi = mid;
+    }
+    const u32 index = lo - 1;
+    if (o.e > ix.seqStart[index + 1]) { // kept although it crosses a sequence end: clipped by txTrimTask
+        const u32 job = B.trimOf[i];
+        const TrimRec tr = B.trimRecs[job];
+        out.trimmed = (u8)(1u + tr.pad[0]);
+        out.indexBegin = tr.b;
+        out.seqID = tr.seqID;
+        out.pos = tr.b - ix.seqStart[tr.seqID];
+        out.end = tr.e - ix.seqStart[tr.seqID];
+        out.dist = tr.dist;
+        ncig = tr.ncig;
+        src = B.trimCig + (size_t)job * B.cigW;
+    } else {
+        out.trimmed = 0;
+        out.indexBegin = o.b;
+        out.seqID = index;
+        out.pos = o.b - ix.seqStart[index];
+        out.end = o.e - ix.seqStart[index];
+        out.dist = o.dist;
+        // generateCIGARS for index occurrences (indexinterface.h:939-949): the alignment itself is left to
+        // a dense follow-up kernel (cigarJobTask)
+        if (B.metric == METRIC_EDIT && !B.noCigarFlag && o.ncig == 0)
+            B.cigJobs.push(at, B.err, ERR_OUT_OVERFLOW);
+    }
+    out.ncig = (u8)ncig;
+    B.out.data[at] = out;
+    u16* dst = B.outCig + (size_t)at * B.cigW;
+    for (u32 q = 0; q < ncig; q++)
+        dst[q] = src[q];
+}
+// hit count and the per-read counters of one group
+CLB_HD void txGroupTask(const Batch& B, u32 g, LocalCtr& lc) {
+    const u32 n = B.outStart[g + 1] - B.outStart[g];
+    B.outCount[g] = n;
+    if (B.grpShift == 0) { // per-strand groups (BEST mode strata): MAPPED_READS is the host loop's business
+        if (!(g & 1u))
+            lc.c[NUMBER_OF_READS]++;
+        lc.c[TOTAL_UNIQUE_MATCHES] += n;
+        return;
+    }
+    if (n) {
+        lc.c[MAPPED_READS]++;
+        lc.c[TOTAL_UNIQUE_MATCHES] += n;
+    }
+    lc.c[NUMBER_OF_READS]++;
 }
 
 // Exact stratum of read r, both strands: IndexInterface::exactMatchesOutput

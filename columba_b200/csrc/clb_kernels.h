@@ -255,43 +255,7 @@ struct DedupKernel {
     CLB_HD void end(State&) const {}
 };
 
-// grouping by read: count / scatter
-struct FmCountKernel {
-    Batch B;
-    struct State {};
-    CLB_HD void begin(State&, u32) const {}
-    CLB_HD void run(State&, u32 i) const { atomAdd<u32>(B.fmCount + groupOf(B, B.fmOccs.data[i].t), 1u); }
-    CLB_HD void end(State&) const {}
-};
-struct FmScatterKernel {
-    Batch B;
-    struct State {};
-    CLB_HD void begin(State&, u32) const {}
-    CLB_HD void run(State&, u32 i) const {
-        u32 r = groupOf(B, B.fmOccs.data[i].t);
-        B.fmIdx[B.fmStart[r] + atomAdd<u32>(B.fmFill + r, 1u)] = i;
-    }
-    CLB_HD void end(State&) const {}
-};
-struct TxCountKernel {
-    Batch B;
-    struct State {};
-    CLB_HD void begin(State&, u32) const {}
-    CLB_HD void run(State&, u32 i) const { atomAdd<u32>(B.txCount + groupOf(B, B.textOccs.data[i].t), 1u); }
-    CLB_HD void end(State&) const {}
-};
-struct TxScatterKernel {
-    Batch B;
-    struct State {};
-    CLB_HD void begin(State&, u32) const {}
-    CLB_HD void run(State&, u32 i) const {
-        u32 r = groupOf(B, B.textOccs.data[i].t);
-        B.txIdx[B.txStart[r] + atomAdd<u32>(B.txFill + r, 1u)] = i;
-    }
-    CLB_HD void end(State&) const {}
-};
-
-// stages 4 and 6
+// stages 4-6 as global passes (clb_filter.h)
 struct FilterState {
     LocalCtr lc;
     FilterScratch fs;
@@ -302,43 +266,50 @@ CLB_HD void carveFilter(FilterState& s, u8* p, u32 cigW, u32 rowsCap) {
     s.fs.rows = p + (((size_t)cigW * 2 * sizeof(u16) + 63) & ~(size_t)63);
     s.fs.rowsCap = rowsCap;
 }
-struct FmPerReadKernel {
-    IndexView ix;
-    Batch B;
-    u8* slabs;
-    size_t slabBytes;
-    u32 rowsCap;
-    typedef FilterState State;
-    CLB_HD void begin(State& s, u32 worker) const { carveFilter(s, slabs + (size_t)worker * slabBytes, B.cigW, rowsCap); }
-    CLB_HD void run(State& s, u32 r) const { fmPerReadTask(ix, B, r, s.fs, s.lc); }
-    CLB_HD void end(State& s) const { s.lc.flush(B.counters, B.stats); }
-};
-struct TxPerReadKernel {
-    IndexView ix;
-    Batch B;
-    u8* slabs;
-    size_t slabBytes;
-    u32 rowsCap;
-    typedef FilterState State;
-    CLB_HD void begin(State& s, u32 worker) const { carveFilter(s, slabs + (size_t)worker * slabBytes, B.cigW, rowsCap); }
-    CLB_HD void run(State& s, u32 r) const { run(s, r, 1u); }
-    CLB_HD void run(State& s, u32 r, unsigned act) const {
-        txPerReadTask(ix, B, r, s.fs, s.lc, act);
-        u32 n = B.outCount[r];
-        if (B.grpShift == 0) { // per-strand groups (BEST mode strata): MAPPED_READS is the host loop's business
-            if (!(r & 1u))
-                s.lc.c[NUMBER_OF_READS]++;
-            s.lc.c[TOTAL_UNIQUE_MATCHES] += n;
-            return;
-        }
-        if (n) {
-            s.lc.c[MAPPED_READS]++;
-            s.lc.c[TOTAL_UNIQUE_MATCHES] += n;
-        }
-        s.lc.c[NUMBER_OF_READS]++;
-    }
-    CLB_HD void end(State& s) const { s.lc.flush(B.counters, B.stats); }
-};
+#define CLB_PLAIN_KERNEL(NAME, CALL)                       \
+    struct NAME {                                          \
+        IndexView ix;                                      \
+        Batch B;                                           \
+        struct State {};                                   \
+        CLB_HD void begin(State&, u32) const {}            \
+        CLB_HD void run(State&, u32 i) const { CALL; }     \
+        CLB_HD void end(State&) const {}                   \
+    };
+#define CLB_COUNTING_KERNEL(NAME, CALL)                                        \
+    struct NAME {                                                              \
+        IndexView ix;                                                          \
+        Batch B;                                                               \
+        typedef WorkerCtr State;                                               \
+        CLB_HD void begin(State& s, u32) const { s.lc.clear(); }               \
+        CLB_HD void run(State& s, u32 i) const { CALL; }                       \
+        CLB_HD void end(State& s) const { s.lc.flush(B.counters, B.stats); }   \
+    };
+#define CLB_SCRATCH_KERNEL(NAME, CALL)                                                                        \
+    struct NAME {                                                                                             \
+        IndexView ix;                                                                                         \
+        Batch B;                                                                                              \
+        u8* slabs;                                                                                            \
+        size_t slabBytes;                                                                                     \
+        u32 rowsCap;                                                                                          \
+        typedef FilterState State;                                                                            \
+        CLB_HD void begin(State& s, u32 worker) const {                                                       \
+            carveFilter(s, slabs + (size_t)worker * slabBytes, B.cigW, rowsCap);                              \
+        }                                                                                                     \
+        CLB_HD void run(State& s, u32 i) const { CALL; }                                                      \
+        CLB_HD void end(State& s) const { s.lc.flush(B.counters, B.stats); }                                  \
+    };
+CLB_PLAIN_KERNEL(FmKeyKernel, fmKeyTask(B, i))
+CLB_COUNTING_KERNEL(FmRunKernel, fmRunTask(B, i, s.lc))
+CLB_PLAIN_KERNEL(FmReserveKernel, fmReserveTask(B))
+CLB_SCRATCH_KERNEL(FmCigarKernel, fmCigarTask(ix, B, i, s.fs, s.lc))
+CLB_COUNTING_KERNEL(FmExpandKernel, fmExpandTask(ix, B, i, s.lc))
+CLB_PLAIN_KERNEL(TxKeyKernel, txKeyTask(B, i))
+CLB_PLAIN_KERNEL(TxRunKernel, txRunTask(B, i))
+CLB_PLAIN_KERNEL(TxChainKernel, txChainTask(ix, B, i))
+CLB_SCRATCH_KERNEL(TxTrimKernel, txTrimTask(ix, B, i, s.fs, s.lc))
+CLB_PLAIN_KERNEL(TxReserveKernel, txReserveTask(B))
+CLB_PLAIN_KERNEL(TxEmitKernel, txEmitTask(ix, B, i))
+CLB_COUNTING_KERNEL(TxGroupKernel, txGroupTask(B, i, s.lc))
 
 struct CigarJobKernel {
     IndexView ix;

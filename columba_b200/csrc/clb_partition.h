@@ -589,7 +589,7 @@ CLB_HD void partFinish(const IndexView& ix, const DevStrategy& st, const Batch& 
             Cand c;
             c.t = t;
             c.maxED = (u8)B.k;
-            c.minED = (u8)B.minD;
+            c.minED = 0; // mapRead maps with minimal distance 0 and drops what is below minD after the filter
             c.pad = 0;
             c.add = 0;
             if (B.metric == METRIC_EDIT) {

@@ -6,14 +6,16 @@
 //   void* alloc(size_t), void free(void*), void zero(void*, size_t),
 //   void* hostAlloc(size_t), void hostFree(void*)  (result arrays on the host),
 //   void d2hAsync(dst, src, n) (completed by sync()),
-//   u32 sortBigSegments(B, R): sorts txIdx segments longer than the returned bound (0xFFFFFFFF: none),
+//   void sortPairs(u64* k0, u32* v0, u64* k1, u32* v1, u32 nMax, const u32* nDev, u32 keyBits): sorts the first
+//   min(nMax, *nDev) (key, value) pairs by the low keyBits bits of the keys; static u32 sortResult(keyBits) tells
+//   which of the two buffer pairs holds the result,
 //   void copyBegin(), void copySlice(dst, src, n, slice), void copyWait(slice)  (host-to-device copies that
 //   overlap the kernels: slice s is usable by work launched after copyWait(s)),
 //   void h2d(void* dst, const void* src, size_t), void d2h(void* dst, const void* src, size_t),
 //   void sync(), u32 workers(int kind) (number of workers for scratch slabs),
 //   u32 fallbackWorkers() (workers that need slabs instead of shared memory; 0 on the GPU),
 //   template<class K> void launch(const K&, u32 nMax, const u32* nDev, int kind),
-//   void exclusiveScan(const u32* in, u32* out, u32 n)   (out[n] = total),
+//   void exclusiveScan(const u32* in, u32* out, u32 nMax, const u32* nDev)   (n = min(nMax, *nDev); out[n] = total),
 //   void mark(int stage) (timing hook)
 #pragma once
 #include "clb_kernels.h"
@@ -105,7 +107,7 @@ template <typename BE> struct MapResult {
 template <typename BE> struct Pipeline {
     BE& be;
     IndexView ix;
-    DevBuf<BE> bReads, bOff, bCodes, bPlanes, bParts, bTasks, bCands, bCandAux, bExtra, bFm, bTx, bTxCig, bOut, bOutCig, bCigJobs, bPerRead, bIdx,
+    DevBuf<BE> bReads, bOff, bCodes, bPlanes, bParts, bTasks, bCands, bCandAux, bExtra, bFm, bTx, bTxCig, bOut, bOutCig, bCigJobs, bPerRead, bSort, bFmCig, bTrim,
         bMisc, bSlabPart, bSlabSearch, bSlabVerify, bSlabVerifyWide, bSlabFilter, bStrategy;
     // list capacities (per read multipliers, grown after an overflow)
     double candPerRead = 24, fmPerRead = 4, txPerRead = 24, outPerRead = 8;
@@ -116,7 +118,7 @@ template <typename BE> struct Pipeline {
     Pipeline(BE& b) : be(b) {}
     ~Pipeline() {
         DevBuf<BE>* all[] = {&bReads, &bOff, &bCodes, &bPlanes, &bParts, &bTasks, &bCands, &bCandAux, &bExtra, &bFm, &bTx, &bTxCig, &bCigJobs, &bOut,
-                             &bOutCig, &bPerRead, &bIdx, &bMisc, &bSlabPart, &bSlabSearch, &bSlabVerify, &bSlabVerifyWide, &bSlabFilter,
+                             &bOutCig, &bPerRead, &bSort, &bFmCig, &bTrim, &bMisc, &bSlabPart, &bSlabSearch, &bSlabVerify, &bSlabVerifyWide, &bSlabFilter,
                              &bStrategy};
         for (auto* d : all)
             d->release(be);
@@ -127,7 +129,8 @@ template <typename BE> struct Pipeline {
         u64 counters[N_COUNTERS];
         u64 stats[N_STATS];
         u32 err;
-        u32 nTasks, nCands, nFm, nTx, nOut, nExtra, nCigJobs, nUniq, nHeavy;
+        u32 nTasks, nCands, nFm, nTx, nOut, nExtra, nCigJobs, nUniq, nHeavy, nTrim;
+        u32 fmSlots[2];
         u32 nT, nR; // 2R and R as device-side task counts
     };
 
@@ -239,18 +242,34 @@ template <typename BE> struct Pipeline {
         B.counters = M->counters;
         B.stats = M->stats;
         B.err = &M->err;
-        // per-group arrays: 9 x (G+1)
+        // per-group arrays: 2 x (G+1)
         const size_t pr = (size_t)(G + 1);
-        bPerRead.ensure(be, pr * 9 * 4);
-        be.zero(bPerRead.p, pr * 9 * 4);
-        u32* q = (u32*)bPerRead.p;
-        B.fmCount = q; B.fmStart = q + pr; B.fmFill = q + 2 * pr; B.fmUnique = q + 3 * pr;
-        B.txCount = q + 4 * pr; B.txStart = q + 5 * pr; B.txFill = q + 6 * pr;
-        B.outCount = q + 7 * pr; B.outStart = q + 8 * pr;
-        bIdx.ensure(be, ((size_t)capFm + 2 * (size_t)capTx) * 4);
-        B.fmIdx = (u32*)bIdx.p;
-        B.txIdx = B.fmIdx + capFm;
-        B.txTmp = B.txIdx + capTx;
+        bPerRead.ensure(be, pr * 2 * 4);
+        be.zero(bPerRead.p, pr * 2 * 4);
+        B.outCount = (u32*)bPerRead.p;
+        B.outStart = B.outCount + pr;
+        // sort buffers of stages 4-6: two (u64 key, u32 value) arrays of capSort + 2 entries each
+        const size_t capSort = (size_t)tmax(capFm, capTx) + 2;
+        u32 groupBits = 1;
+        while (groupBits < 32 && ((u64)1 << groupBits) < (u64)G)
+            groupBits++;
+        const u32 keyBits = 32 + groupBits;
+        bSort.ensure(be, capSort * 2 * (sizeof(u64) + sizeof(u32)));
+        B.sortKey[0] = (u64*)bSort.p;
+        B.sortKey[1] = B.sortKey[0] + capSort;
+        B.sortVal[0] = (u32*)(B.sortKey[1] + capSort);
+        B.sortVal[1] = B.sortVal[0] + capSort;
+        B.sortRes = BE::sortResult(keyBits);
+        B.trimOf = (u32*)B.sortKey[1 - B.sortRes] + capSort; // second half of the scratch key array
+        bFmCig.ensure(be, (size_t)capFm * (B.cigW * 2 + 1));
+        B.fmCig = (u16*)bFmCig.p;
+        B.fmNcig = (u8*)(B.fmCig + (size_t)capFm * B.cigW);
+        B.fmSlots = M->fmSlots;
+        const u32 capTrim = capOut;
+        bTrim.ensure(be, (size_t)capTrim * (sizeof(u32) + sizeof(TrimRec) + B.cigW * 2));
+        B.trimRecs = (TrimRec*)bTrim.p;
+        B.trimJobs.data = (u32*)(B.trimRecs + capTrim); B.trimJobs.count = &M->nTrim; B.trimJobs.cap = capTrim;
+        B.trimCig = (u16*)(B.trimJobs.data + capTrim);
         const DevStrategy* dst = (const DevStrategy*)bStrategy.p;
 
         // ---- stage 0/1
@@ -343,33 +362,53 @@ template <typename BE> struct Pipeline {
             be.mark(STG_VERIFY);
         }
         } // k > 0
-        // ---- stages 4-6
+        // ---- stages 4-6: global passes over the occurrence lists (clb_filter.h)
         {
             size_t sb = (((size_t)B.cigW * 2 * 2 + 63) & ~(size_t)63) + (size_t)vRows * sizeof(Row<u128>);
             sb = (sb + 63) & ~(size_t)63;
             const u32 nw = be.workers(WK_FILTER);
             bSlabFilter.ensure(be, sb * nw);
-            FmCountKernel c1{B};
+            u64 *ks = B.sortKey[B.sortRes], *kx = B.sortKey[1 - B.sortRes];
+            u32 *vs = B.sortVal[B.sortRes], *vx = B.sortVal[1 - B.sortRes];
+            (void)ks;
+            (void)vs;
+            // index occurrences -> text occurrences
+            FmKeyKernel c1{ix, B};
             be.launch(c1, capFm, &M->nFm, WK_LIGHT);
-            be.exclusiveScan(B.fmCount, B.fmStart, G);
-            FmScatterKernel c2{B};
+            be.sortPairs(B.sortKey[0], B.sortVal[0], B.sortKey[1], B.sortVal[1], capFm, &M->nFm, keyBits);
+            FmRunKernel c2{ix, B};
             be.launch(c2, capFm, &M->nFm, WK_LIGHT);
-            FmPerReadKernel c3{ix, B, (u8*)bSlabFilter.p, sb, vRows};
-            be.launch(c3, G, nullptr, WK_FILTER);
+            be.exclusiveScan(vx, (u32*)kx, capFm, &M->nFm);
+            FmReserveKernel c3{ix, B};
+            be.launch(c3, 1, nullptr, WK_LIGHT);
+            if (opt.metric == METRIC_EDIT && !opt.noCigar) {
+                FmCigarKernel c4{ix, B, (u8*)bSlabFilter.p, sb, vRows};
+                be.launch(c4, capFm, &M->nFm, WK_FILTER);
+            }
+            FmExpandKernel c5{ix, B};
+            be.launch(c5, capTx, &M->fmSlots[1], WK_LIGHT);
             be.mark(STG_FM);
-            TxCountKernel d1{B};
+            // text occurrences -> output
+            TxKeyKernel d1{ix, B};
             be.launch(d1, capTx, &M->nTx, WK_LIGHT);
-            be.exclusiveScan(B.txCount, B.txStart, G);
-            TxScatterKernel d2{B};
+            be.sortPairs(B.sortKey[0], B.sortVal[0], B.sortKey[1], B.sortVal[1], capTx, &M->nTx, keyBits);
+            TxRunKernel d2{ix, B};
             be.launch(d2, capTx, &M->nTx, WK_LIGHT);
-            // reads inside repeats have thousands of occurrences: their segments are sorted
-            // by whole CTAs first (the per-read kernel sorts the small ones itself)
-            B.txPresorted = be.sortBigSegments(B, G);
-            B.txPresortedMax = be.sortBigMax();
-            TxPerReadKernel d3{ix, B, (u8*)bSlabFilter.p, sb, vRows};
-            be.launch(d3, G, nullptr, WK_FILTER);
-            CigarJobKernel d4{ix, B, (u8*)bSlabFilter.p, sb, vRows};
-            be.launch(d4, capOut, &M->nCigJobs, WK_FILTER);
+            TxChainKernel d3{ix, B};
+            be.launch(d3, capTx, &M->nTx, WK_LIGHT);
+            if (opt.metric == METRIC_EDIT) {
+                TxTrimKernel d4{ix, B, (u8*)bSlabFilter.p, sb, vRows};
+                be.launch(d4, capTrim, &M->nTrim, WK_FILTER);
+            }
+            be.exclusiveScan(vx, (u32*)kx, capTx, &M->nTx);
+            TxReserveKernel d5{ix, B};
+            be.launch(d5, 1, nullptr, WK_LIGHT);
+            TxEmitKernel d6{ix, B};
+            be.launch(d6, capTx, &M->nTx, WK_LIGHT);
+            TxGroupKernel d7{ix, B};
+            be.launch(d7, G, nullptr, WK_LIGHT);
+            CigarJobKernel d8{ix, B, (u8*)bSlabFilter.p, sb, vRows};
+            be.launch(d8, capOut, &M->nCigJobs, WK_FILTER);
             be.mark(STG_TEXT);
         }
         // ---- results

@@ -1,22 +1,23 @@
-"""Host-side mode drivers on top of the ALL-mode device pass.
+"""Host-side mode drivers on top of the device pass (Python binding of the logic
+that include/columba_b200.hpp implements for C++ callers).
 
 In the reference BEST mode and paired-end pairing are host loops around the same
 per-read mapping call; here they are
 loops around `Mapper.map_batch(max_dist, min_dist)`:
 
-  * map_best      -- SearchStrategy::findBestAlignments, src/searchstrategy.cpp:623-712
-                     (strata 0; 1, 3, 5, 9, 13 ... or best + x), cut-off from the
-                     minimal identity (getMaxED, src/searchstrategy.h:1797-1806),
-                     batched: every stratum is one device pass over the reads
-                     that have no alignment yet.
+  * map_best      -- SearchStrategy::matchApproxBestPlusX / findBestAlignments,
+                     src/searchstrategy.cpp:623-744: exact stratum, then the strata
+                     1, 3, 5, 9, 13 (or best + x), cut-off from the minimal identity
+                     (getMaxED, src/searchstrategy.h:1797-1806).  Batched: every
+                     stratum is one device pass over the reads that still need it.
+                     As in the reference the two strands of a read are mapped and
+                     filtered separately (clb_ctx_set_filter_per_strand), occurrences
+                     are kept per strand and distance, clipped alignments move to the
+                     level of their new distance (checkAlignments, :537-568) and the
+                     result is combineOccVectors (:570-621).
   * pair_occurrences -- SearchStrategy::pairOccurrences, src/searchstrategy.cpp:1281-1343:
                      window join of two position-sorted occurrence lists on
                      [min_frag, max_frag].
-
-Known difference to the reference, documented in DESIGN.md section 7: the
-reference maps the two strands of a read in separate calls in BEST mode (so its
-redundancy filter sees one strand at a time), the device pass filters both
-strands together as the reference's ALL mode does.
 """
 import numpy as np
 
@@ -51,81 +52,188 @@ class Occ(tuple):
     __slots__ = ()
 
 
-def _occs_of(res, r):
-    s, c = int(res.read_start[r]), int(res.read_count[r])
+def _group_occs(res, g):
+    """Occurrences of group g of a batch result as (Occ, clipped, distance before clipping)."""
+    s, c = int(res.read_start[g]), int(res.read_count[g])
     out = []
     for i in range(s, s + c):
         o = res.occ[i]
-        out.append(Occ((int(o["strand"]), int(o["seq_id"]), int(o["pos"]), int(o["end"]), int(o["index_begin"]),
-                        int(o["dist"]), cigar_string(res.cigar[i, :int(o["n_cigar"])]) if o["n_cigar"] else "*")))
+        occ = Occ((int(o["strand"]), int(o["seq_id"]), int(o["pos"]), int(o["end"]), int(o["index_begin"]),
+                   int(o["dist"]), cigar_string(res.cigar[i, :int(o["n_cigar"])]) if o["n_cigar"] else "*"))
+        tr = int(o["trimmed"])
+        out.append((occ, tr != 0, tr - 1 if tr else int(o["dist"])))
     return out
 
 
-def map_best(mapper, seqs, min_identity=95, x=0):
-    """BEST mode for a list of reads.  Returns (per-read list of Occ with
-    distance <= best + x, per-read best distance or None)."""
+def _occs_of(res, r):
+    return [t[0] for t in _group_occs(res, r)]
+
+
+class _BestState:
+    """findBestAlignments' per-read state: occurrences per strand and distance, which distances have
+    been mapped, and the stratum loop's variables."""
+
+    def __init__(self, cutoff, x):
+        self.cutoff, self.x = cutoff, x
+        self.lv = [[[] for _ in range(cutoff + 1)] for _ in (0, 1)]   # [strand][distance] -> [(Occ, clipped)]
+        self.done_upto = -1       # distances 0..done_upto have been mapped (both strands move in step)
+        self.best = cutoff + 1
+        self.best_found = False
+        self.finished = False
+        self.max_ed = cutoff
+        self.k = max(x, 1)
+        self.prev_k = 0
+
+    def add(self, strand, items):
+        for occ, clipped, level in items:
+            if level <= self.cutoff:
+                self.lv[strand][level].append((occ, clipped))
+
+    def check(self, level):
+        """checkAlignments (src/searchstrategy.cpp:537-568) for both strands"""
+        for strand in (0, 1):
+            keep, moved = [], []
+            for occ, clipped in self.lv[strand][level]:
+                if clipped:
+                    if occ[5] > level:
+                        moved.append(occ)
+                else:
+                    keep.append((occ, False))
+                    if level < self.best:
+                        self.best = level
+            self.lv[strand][level] = keep
+            for occ in moved:
+                if occ[5] <= self.cutoff:
+                    self.lv[strand][occ[5]].append((occ, False))
+
+    def any_upto(self, k):
+        return any(self.lv[s][d] for s in (0, 1) for d in range(min(k, self.cutoff) + 1))
+
+    def after_exact(self):
+        """x == 0: the exact stratum has been mapped (src/searchstrategy.cpp:637-662)"""
+        self.done_upto = 0
+        if self.lv[0][0] or self.lv[1][0]:
+            self.check(0)
+            if self.best == 0:
+                self.best_found = True
+        self.max_ed = self.x if self.best == 0 else self.cutoff
+        if self.k > self.max_ed:
+            self.finished = True
+
+    def needs_mapping(self):
+        return not self.finished and self.k > self.done_upto
+
+    def step(self, mapped):
+        """one iteration of the stratum loop (src/searchstrategy.cpp:677-708); `mapped`: distance k was
+        mapped in this iteration (else its occurrences were already there)"""
+        k = self.k
+        if mapped:
+            self.done_upto = k
+            update = self.any_upto(k)
+        else:
+            update = bool(self.lv[0][k] or self.lv[1][k])
+        if update:
+            level = self.prev_k + 1
+            while level <= min(k, self.best + self.x):
+                self.check(level)
+                level += 1
+        if self.best_found:
+            self.finished = True
+            return
+        if update and self.best < self.cutoff + 1:
+            self.best_found = True
+            if self.x == 0:
+                self.finished = True
+                return
+            self.prev_k, self.k = k, min(self.best + self.x, self.max_ed)
+        else:
+            if k == self.max_ed:
+                self.finished = True
+                return
+            self.prev_k, self.k = k, min(k + self.x + (2 if k < 5 else 4), self.max_ed)
+
+    def result(self):
+        """combineOccVectors (src/searchstrategy.cpp:570-621) -> (occurrences, number of best hits)"""
+        if not self.best_found:
+            return [], 0
+        n_hits = len(self.lv[0][self.best]) + len(self.lv[1][self.best])
+        out = []
+        for d in range(self.best, min(self.best + self.x, self.cutoff) + 1):
+            for strand in (0, 1):
+                last = None
+                for occ in sorted((o for o, _ in self.lv[strand][d]), key=lambda o: (o[1], o[2])):  # stable
+                    if last is not None and (occ[1], occ[2]) == last:
+                        continue
+                    last = (occ[1], occ[2])
+                    out.append(occ)
+        return out, n_hits
+
+
+def map_best(mapper, seqs, min_identity=95, x=0, with_hits=False):
+    """BEST mode for a list of reads.  Returns (per-read list of Occ in the reference's output order --
+    the first one is the primary alignment --, per-read best distance or None[, per-read nHits])."""
     n = len(seqs)
-    found = [None] * n
-    occs = [[] for _ in range(n)]
-    # reads of one length share the cut-off and therefore the strata
-    by_cut = {}
     supported = 0  # getMaxSupportedDistanceForBestMapping: largest k with all of 1..k supported
     while supported < MAX_K and mapper.supports(supported + 1):
         supported += 1
-    for i, s in enumerate(seqs):
-        by_cut.setdefault(max_ed(min_identity, len(s), supported), []).append(i)
-    for cutoff, ids in sorted(by_cut.items()):
-        pending = list(ids)
-        prev = -1
-        sched = strata(cutoff, x)
-        # The exact stratum (exactMatchesOutput, src/indexinterface.cpp:947-1014) has no
-        # search scheme of its own: it is mapped together with stratum 1 (min_dist 0)
-        # and only its distance-0 occurrences are kept when there are any.
-        if sched and sched[0] == 0:
-            sched = sched[1:] if len(sched) > 1 else [1]
-        mapper.set_trim_max(cutoff)  # checkAlignments clips with the cut-off, src/searchstrategy.cpp:537-568
-        for k in sched:
-            if not pending:
+    st = [_BestState(max_ed(min_identity, len(s), supported), x) for s in seqs]
+    mapper.set_filter_per_strand(True)
+    try:
+        def device_pass(ids, k, min_d, cutoff):
+            mapper.set_trim_max(cutoff)  # checkAlignments clips with the cut-off
+            reads, off = Mapper.pack([seqs[i] for i in ids])
+            res = mapper.map_batch(reads, off, k, min_d, allow_short=True)
+            for j, i in enumerate(ids):
+                for strand in (0, 1):
+                    st[i].add(strand, _group_occs(res, 2 * j + strand))
+        if x == 0:
+            by_cut = {}
+            for i in range(n):
+                by_cut.setdefault(st[i].cutoff, []).append(i)
+            for cutoff, ids in sorted(by_cut.items()):
+                device_pass(ids, 0, 0, cutoff)
+            for s in st:
+                s.after_exact()
+        else:
+            for s in st:
+                if s.k > s.max_ed:
+                    s.finished = True
+        while True:
+            groups = {}
+            for i, s in enumerate(st):
+                if s.needs_mapping():
+                    groups.setdefault((s.cutoff, s.k, min(s.done_upto + 1, s.k)), []).append(i)
+            for (cutoff, k, min_d), ids in sorted(groups.items()):
+                device_pass(ids, k, min_d, cutoff)
+            progressed = False
+            for i, s in enumerate(st):
+                if s.finished:
+                    continue
+                s.step(mapped=s.k > s.done_upto)
+                progressed = True
+            if not progressed:
                 break
-            reads, off = Mapper.pack([seqs[i] for i in pending])
-            res = mapper.map_batch(reads, off, k, prev + 1, allow_short=True)
-            still = []
-            for j, i in enumerate(pending):
-                o = [t for t in _occs_of(res, j) if t[5] <= cutoff]
-                if o:
-                    found[i] = min(t[5] for t in o)
-                    occs[i] = o
-                else:
-                    still.append(i)
-            # reads found at this stratum with x > 0: one more pass up to best + x
-            if x > 0:
-                more = {}
-                for j, i in enumerate(pending):
-                    if found[i] is not None and occs[i] and min(found[i] + x, cutoff) > k:
-                        more.setdefault(min(found[i] + x, cutoff), []).append(i)
-                for k2, ids2 in sorted(more.items()):
-                    reads2, off2 = Mapper.pack([seqs[i] for i in ids2])
-                    res2 = mapper.map_batch(reads2, off2, k2, k + 1, allow_short=True)
-                    for j, i in enumerate(ids2):
-                        occs[i] += _occs_of(res2, j)
-            pending = still
-            prev = k
-    mapper.set_trim_max(0)
-    for i in range(n):
-        if found[i] is not None:
-            occs[i] = sorted(t for t in occs[i] if t[5] <= found[i] + x)
-    return occs, found
+    finally:
+        mapper.set_trim_max(0)
+        mapper.set_filter_per_strand(False)
+    occs, found, hits = [], [], []
+    for s in st:
+        o, h = s.result()
+        occs.append(o)
+        found.append(s.best if s.best_found else None)
+        hits.append(h)
+    return (occs, found, hits) if with_hits else (occs, found)
 
 
-def best_tuples(occs, found, read_names, seq_names):
-    """The record the reference writes per read in BEST mode (one primary
-    alignment): smallest distance, then text order."""
+def best_records(occs, found, read_names, seq_names):
+    """Every record the reference writes in BEST mode, as (read, flag & (16 | 256), sequence, pos, NM, CIGAR):
+    the first occurrence of a read is its primary alignment, the others are secondary (flag 256)."""
     out = []
     for i, o in enumerate(occs):
         if found[i] is None:
             continue
-        prim = min(o, key=lambda t: (t[5], t[4], t[3] - t[2]))
-        out.append((read_names[i], 16 if prim[0] else 0, seq_names[prim[1]], prim[2] + 1, prim[5], prim[6]))
+        for j, t in enumerate(o):
+            out.append((read_names[i], (16 if t[0] else 0) | (256 if j else 0), seq_names[t[1]], t[2] + 1, t[5], t[6]))
     return sorted(out)
 
 

@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define CLB_ABI_VERSION 2
+#define CLB_ABI_VERSION 3
 
 enum {
     CLB_OK = 0,
@@ -69,7 +69,8 @@ typedef struct clb_occ {
     uint8_t strand;       /* 0 forward, 1 reverse complement */
     uint8_t dist;         /* edit / Hamming distance (NM) */
     uint8_t n_cigar;      /* number of CIGAR runs in cigar[i * cigar_stride ...] */
-    uint8_t trimmed;      /* 1: FOUND_WITH_TRIMMING at a sequence boundary */
+    uint8_t trimmed;      /* 0, or 1 + the distance before clipping: FOUND_WITH_TRIMMING at a sequence
+                             boundary (dist, pos, end, cigar describe the clipped alignment) */
 } clb_occ;
 
 /* Result of one batch; arrays are owned by the context and stay valid until
@@ -80,7 +81,7 @@ typedef struct clb_result {
     uint32_t n_reads;
     uint32_t n_groups;            /* entries of read_start / read_count: n_reads, or 2 * n_reads with group
                                      2 * read + strand after clb_ctx_set_filter_per_strand(ctx, 1) */
-    uint32_t n_occ;               /* entries in occ[] (some may be unused gaps) */
+    uint32_t n_occ;               /* entries in occ[]: read by read, no gaps */
     const clb_occ* occ;
     const uint16_t* cigar;        /* n_occ x cigar_stride, run = (len << 2) | op, op 0=M 1=I 2=D */
     uint32_t cigar_stride;
@@ -144,7 +145,9 @@ int clb_ctx_num_parts(const clb_ctx*, int k); /* calculateNumParts */
 /* ---- the hot path (replaces SearchStrategy::matchApproxAllMap for a whole
  * chunk, src/searchstrategy.cpp:495-535).  reads: concatenated ASCII reads,
  * offsets: n_reads+1 offsets into it.  HOST pointers; copies are part of the
- * call.  max_dist = -e, min_dist = minimal distance to report (0 in ALL mode).
+ * call.  max_dist = -e; min_dist = minimal distance to report (0 in ALL mode): as in
+ * SearchStrategy::mapRead (src/searchstrategy.h:490-517) the read is mapped and filtered over the whole
+ * range 0..max_dist and occurrences below min_dist are removed afterwards.
  * max_dist = 0 is the exact stratum (IndexInterface::exactMatchesOutput,
  * src/indexinterface.cpp:947-1014): every exact occurrence of either strand,
  * no redundancy filter, no search scheme needed. */

@@ -6,7 +6,10 @@
 #include <cstdlib>
 #include <cstring>
 #include <stdexcept>
+#include <algorithm>
 #include <string>
+#include <utility>
+#include <vector>
 
 #include "../../columba_b200/csrc/clb_pipeline.h"
 
@@ -25,8 +28,6 @@ struct HostEmuBackend {
     void h2d(void* d, const void* s, size_t n) { std::memcpy(d, s, n); }
     void d2h(void* d, const void* s, size_t n) { std::memcpy(d, s, n); }
     void sync() {}
-    u32 sortBigSegments(const Batch&, u32) { return 0xFFFFFFFFu; }
-    u32 sortBigMax() const { return 0xFFFFFFFFu; }
     void d2hAsync(void* d, const void* s, size_t n) { std::memcpy(d, s, n); }
     void copyBegin() {}
     void copySlice(void* d, const void* s, size_t n, u32) { std::memcpy(d, s, n); }
@@ -51,7 +52,21 @@ struct HostEmuBackend {
         k.end(st);
         launches++;
     }
-    void exclusiveScan(const u32* in, u32* out, u32 n) {
+    static u32 sortResult(u32) { return 0; }
+    void sortPairs(u64* k0, u32* v0, u64*, u32*, u32 nMax, const u32* nDev, u32) {
+        const u32 n = nDev ? (*nDev < nMax ? *nDev : nMax) : nMax;
+        std::vector<std::pair<u64, u32>> a(n);
+        for (u32 i = 0; i < n; i++)
+            a[i] = std::make_pair(k0[i], v0[i]);
+        std::stable_sort(a.begin(), a.end(),
+                         [](const std::pair<u64, u32>& x, const std::pair<u64, u32>& y) { return x.first < y.first; });
+        for (u32 i = 0; i < n; i++) {
+            k0[i] = a[i].first;
+            v0[i] = a[i].second;
+        }
+    }
+    void exclusiveScan(const u32* in, u32* out, u32 nMax, const u32* nDev) {
+        const u32 n = nDev ? (*nDev < nMax ? *nDev : nMax) : nMax;
         u32 run = 0;
         for (u32 i = 0; i < n; i++) {
             u32 v = in[i];

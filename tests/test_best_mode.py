@@ -29,32 +29,41 @@ def test_strata_schedule_follows_reference():
     assert host.strata(4) == [0, 1, 3, 4]
     assert host.strata(0) == [0]
     assert host.strata(7, x=1) == [1, 4, 7]
+    # the per-read state machine walks the same schedule while nothing is found
+    s = host._BestState(13, 0)
+    s.after_exact()
+    seen = []
+    while not s.finished:
+        seen.append(s.k)
+        s.step(mapped=True)
+    assert [0] + seen == host.strata(13)
     assert host.max_ed(95, 150) == 7 and host.max_ed(97, 150) == 4 and host.max_ed(100, 150) == 0
 
 
-def run_case(case, ix):
+def run_case(case, lib, device):
+    """Every record of `columba -a best` (all co-optimal alignments, which of them is primary, strands,
+    positions, distances, CIGARs) for every read."""
     p = CASES[case]
+    base = gu.index_of(p, lib)
+    ix = cb.Index(base, 4, 10, 4, device=device, lib_path=lib)
     m = cb.Mapper(ix)
-    names, seqs = gu.read_fastq_gz(os.path.join(gu.GOLD, "g1_edit.fq.gz"))
+    names, seqs = gu.read_fastq_gz(os.path.join(gu.GOLD, (p["reads"] if "reads" in p else "g1_edit") + ".fq.gz"))
     occs, found = host.map_best(m, seqs, p["identity"], p["x"])
-    got = host.best_tuples(occs, found, names, ix.seq_names)
+    got = host.best_records(occs, found, names, ix.seq_names)
     m.close()
+    ix.close()
     assert got == expected_best(case)
 
 
 @pytest.mark.parametrize("case", sorted(CASES))
 def test_best_mode_kernel_logic(case, golden_index, hostemu_lib):
-    ix = cb.Index(golden_index, 4, 10, 4, lib_path=hostemu_lib)
-    run_case(case, ix)
-    ix.close()
+    run_case(case, hostemu_lib, 0)
 
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("case", sorted(CASES))
 def test_best_mode_gpu(case, golden_index, cuda_lib):
-    ix = cb.Index(golden_index, 4, 10, 4, device=0, lib_path=cuda_lib)
-    run_case(case, ix)
-    ix.close()
+    run_case(case, cuda_lib, 0)
 
 
 def test_pair_occurrences_window_join():

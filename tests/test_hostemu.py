@@ -123,7 +123,7 @@ def test_cuda_library_exports_the_whole_abi(cuda_lib):
     lib = cb.load_library(cuda_lib)
     for name in declared:
         assert hasattr(lib, name), name
-    assert lib.clb_abi_version() == 2
+    assert lib.clb_abi_version() == 3
 
 
 def test_product_has_no_cpu_fallback(cuda_lib, golden_index):

@@ -2,7 +2,7 @@
 """SAM -> canonical occurrence tuples (read, strand flag, seq, pos, dist, CIGAR), sorted."""
 import sys
 
-def sam_tuples(path):
+def sam_tuples(path, flag_mask=16):
     out = []
     for line in open(path):
         if line.startswith("@"):
@@ -13,7 +13,7 @@ def sam_tuples(path):
             continue
         nm = [x for x in f[11:] if x.startswith("NM:i:")]
         dist = int(nm[0][5:]) if nm else -1
-        out.append((f[0], flag & 16, f[2], int(f[3]), dist, f[5]))
+        out.append((f[0], flag & flag_mask, f[2], int(f[3]), dist, f[5]))
     out.sort()
     return out
 
