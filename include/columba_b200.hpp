@@ -8,7 +8,8 @@
 //   clb::SearchStrategy   <- SearchStrategy, src/searchstrategy.h:1724-2081, as built by
 //                            Parameters::createStrategy, src/parameters/alignparameters.cpp:1312-1387
 //     matchApproxBatch    <- matchApprox (:2021) / matchApproxAllMap src/searchstrategy.cpp:495-535 per chunk
-//     matchBestBatch      <- findBestAlignments src/searchstrategy.cpp:623-712 (strata loop, batched)
+//     matchBestBatch      <- matchApproxBestPlusX / findBestAlignments / checkAlignments / combineOccVectors,
+//                            src/searchstrategy.cpp:537-744 (per-read state machine over batched device passes)
 //     supportsDistanceScore, calculateNumParts, getMaxED (:1797-1806)
 //   clb::TextOcc          <- the fields of TextOcc the SAM writer uses, src/indexhelpers.h:289-930
 //   clb::Counters         <- Counters, src/indexhelpers.h:1848-1883 (same enum order)
@@ -48,7 +49,8 @@ struct TextOcc {
     uint32_t indexBegin = 0; // begin in the concatenated text
     uint32_t distance = 0;
     Strand strand = FORWARD_STRAND;
-    bool trimmed = false;    // FOUND_WITH_TRIMMING
+    bool trimmed = false;    // FOUND_WITH_TRIMMING: clipped at a sequence boundary
+    uint32_t distanceBeforeTrimming = 0; // the distance the occurrence was found with (== distance unless trimmed)
     std::string cigar;       // "*" when CIGARs are switched off
 };
 
@@ -102,10 +104,11 @@ class SearchStrategy {
         return std::min(std::min<uint32_t>(13u, supported), (seqSize * (100 - minIdentity)) / 100);
     }
 
-    // ALL mode for a chunk of reads: result[i] = occurrences of reads[i] in text order
-    void matchApproxBatch(const std::vector<std::string>& reads, uint32_t maxED, Counters& counters,
-                          std::vector<std::vector<TextOcc>>& result, uint32_t minED = 0) {
-        result.assign(reads.size(), {});
+    // One device pass over a chunk of reads: groups[g] = occurrences of group g in text order, g = read (ALL mode)
+    // or 2 * read + strand after setFilterPerStrand(true)
+    void mapChunk(const std::vector<std::string>& reads, uint32_t maxED, uint32_t minED, Counters& counters,
+                  std::vector<std::vector<TextOcc>>& groups) {
+        groups.clear();
         if (reads.empty())
             return;
         std::string cat;
@@ -119,8 +122,9 @@ class SearchStrategy {
                                (int)minED, &r);
         if (rc && !(rc == CLB_E_UNSUPPORTED && r.n_reads == reads.size())) // reads too short for the scheme are skipped
             check(rc);
-        for (uint32_t i = 0; i < r.n_reads; i++)
-            for (uint32_t j = r.read_start[i]; j < r.read_start[i] + r.read_count[i]; j++) {
+        groups.assign(r.n_groups, {});
+        for (uint32_t g = 0; g < r.n_groups; g++)
+            for (uint32_t j = r.read_start[g]; j < r.read_start[g] + r.read_count[g]; j++) {
                 const clb_occ& o = r.occ[j];
                 TextOcc t;
                 t.seqID = o.seq_id;
@@ -130,6 +134,7 @@ class SearchStrategy {
                 t.distance = o.dist;
                 t.strand = o.strand ? REVERSE_C_STRAND : FORWARD_STRAND;
                 t.trimmed = o.trimmed != 0;
+                t.distanceBeforeTrimming = o.trimmed ? (uint32_t)o.trimmed - 1u : (uint32_t)o.dist;
                 for (uint32_t c = 0; c < o.n_cigar; c++) {
                     const uint16_t run = r.cigar[(size_t)j * r.cigar_stride + c];
                     t.cigar += std::to_string(run >> 2);
@@ -137,80 +142,208 @@ class SearchStrategy {
                 }
                 if (!o.n_cigar)
                     t.cigar = "*";
-                result[i].push_back(std::move(t));
+                groups[g].push_back(std::move(t));
             }
         counters.add(r.counters);
     }
 
-    // BEST mode (strata 0; 1, 3, 5, 9, 13 or best + x) for a chunk of reads of one
-    // length class: result[i] = occurrences with distance <= best + x
+    // ALL mode for a chunk of reads: result[i] = occurrences of reads[i] in text order
+    void matchApproxBatch(const std::vector<std::string>& reads, uint32_t maxED, Counters& counters,
+                          std::vector<std::vector<TextOcc>>& result, uint32_t minED = 0) {
+        mapChunk(reads, maxED, minED, counters, result);
+        result.resize(reads.size());
+    }
+
+    // BEST mode (-a best, -x strata after the best one) for a chunk of reads.  result[i] = the occurrences the
+    // reference reports for reads[i], in its order: the first one is the primary alignment.  nHits (optional) =
+    // number of alignments in the best stratum (the reference's MAPQ input).
     void matchBestBatch(const std::vector<std::string>& reads, uint32_t minIdentity, uint32_t x, Counters& counters,
-                        std::vector<std::vector<TextOcc>>& result) {
-        result.assign(reads.size(), {});
-        std::vector<uint32_t> cut(reads.size());
-        uint32_t maxCut = 0;
-        for (size_t i = 0; i < reads.size(); i++) {
-            cut[i] = getMaxED(minIdentity, (uint32_t)reads[i].size());
-            maxCut = std::max(maxCut, cut[i]);
-        }
-        for (uint32_t cutoff = 0; cutoff <= maxCut; cutoff++) {
-            std::vector<size_t> pending;
-            for (size_t i = 0; i < reads.size(); i++)
-                if (cut[i] == cutoff)
-                    pending.push_back(i);
-            if (pending.empty())
-                continue;
-            check(clb_ctx_set_trim_max(ctx, (int)cutoff));
-            // the exact stratum is mapped together with stratum 1
-            std::vector<uint32_t> sched;
-            for (uint32_t k = std::max(x, 1u); k <= std::max(cutoff, 1u);) {
-                sched.push_back(k);
-                if (k >= cutoff)
-                    break;
-                k = std::min(k + x + (k < 5 ? 2u : 4u), cutoff);
-            }
-            int prev = -1;
-            for (uint32_t k : sched) {
-                if (pending.empty())
-                    break;
-                std::vector<std::string> sub;
-                for (size_t i : pending)
-                    sub.push_back(reads[i]);
-                std::vector<std::vector<TextOcc>> occ;
-                matchApproxBatch(sub, k, counters, occ, (uint32_t)(prev + 1));
-                std::vector<size_t> still;
-                for (size_t j = 0; j < pending.size(); j++) {
-                    auto& o = occ[j];
-                    o.erase(std::remove_if(o.begin(), o.end(), [&](const TextOcc& t) { return t.distance > cutoff; }),
-                            o.end());
-                    if (o.empty()) {
-                        still.push_back(pending[j]);
-                        continue;
-                    }
-                    uint32_t best = o[0].distance;
-                    for (const auto& t : o)
-                        best = std::min(best, t.distance);
-                    const uint32_t lim = std::min(best + x, cutoff);
-                    if (x > 0 && lim > k) { // the strata up to best + x
-                        std::vector<std::vector<TextOcc>> more;
-                        matchApproxBatch({reads[pending[j]]}, lim, counters, more, k + 1);
-                        for (auto& t : more[0])
-                            o.push_back(std::move(t));
-                    }
-                    o.erase(std::remove_if(o.begin(), o.end(), [&](const TextOcc& t) { return t.distance > lim; }),
-                            o.end());
-                    result[pending[j]] = std::move(o);
+                        std::vector<std::vector<TextOcc>>& result, std::vector<uint32_t>* nHits = nullptr) {
+        const size_t n = reads.size();
+        result.assign(n, {});
+        if (nHits)
+            nHits->assign(n, 0);
+        std::vector<BestState> st;
+        st.reserve(n);
+        for (size_t i = 0; i < n; i++)
+            st.emplace_back(getMaxED(minIdentity, (uint32_t)reads[i].size()), x);
+        check(clb_ctx_set_filter_per_strand(ctx, 1));
+        try {
+            // one pass per (cut-off, k, minimal distance) over the reads that need it
+            struct Key {
+                uint32_t cutoff, k, minD;
+                bool operator<(const Key& o) const {
+                    return cutoff != o.cutoff ? cutoff < o.cutoff : (k != o.k ? k < o.k : minD < o.minD);
                 }
-                pending.swap(still);
-                prev = (int)k;
+                bool operator==(const Key& o) const { return cutoff == o.cutoff && k == o.k && minD == o.minD; }
+            };
+            auto devicePass = [&](std::vector<std::pair<Key, size_t>>& want) {
+                std::sort(want.begin(), want.end());
+                for (size_t a = 0; a < want.size();) {
+                    size_t b = a;
+                    std::vector<std::string> sub;
+                    while (b < want.size() && want[b].first == want[a].first)
+                        sub.push_back(reads[want[b++].second]);
+                    check(clb_ctx_set_trim_max(ctx, (int)want[a].first.cutoff)); // checkAlignments clips with the cut-off
+                    std::vector<std::vector<TextOcc>> groups;
+                    mapChunk(sub, want[a].first.k, want[a].first.minD, counters, groups);
+                    for (size_t j = a; j < b; j++)
+                        for (int strand = 0; strand < 2; strand++)
+                            st[want[j].second].add(strand, groups[2 * (j - a) + strand]);
+                    a = b;
+                }
+            };
+            std::vector<std::pair<Key, size_t>> want;
+            if (x == 0) {
+                for (size_t i = 0; i < n; i++)
+                    want.push_back({Key{st[i].cutoff, 0, 0}, i});
+                devicePass(want);
+                for (auto& s : st)
+                    s.afterExact();
+            } else {
+                for (auto& s : st)
+                    if (s.k > s.maxED)
+                        s.finished = true;
             }
+            for (;;) {
+                want.clear();
+                for (size_t i = 0; i < n; i++)
+                    if (!st[i].finished && (int)st[i].k > st[i].doneUpto)
+                        want.push_back({Key{st[i].cutoff, st[i].k, std::min((uint32_t)(st[i].doneUpto + 1), st[i].k)}, i});
+                devicePass(want);
+                bool progressed = false;
+                for (auto& s : st)
+                    if (!s.finished) {
+                        s.step((int)s.k > s.doneUpto);
+                        progressed = true;
+                    }
+                if (!progressed)
+                    break;
+            }
+        } catch (...) {
+            clb_ctx_set_trim_max(ctx, 0);
+            clb_ctx_set_filter_per_strand(ctx, 0);
+            throw;
         }
         check(clb_ctx_set_trim_max(ctx, 0));
+        check(clb_ctx_set_filter_per_strand(ctx, 0));
+        for (size_t i = 0; i < n; i++) {
+            const uint32_t h = st[i].result(result[i]);
+            if (nHits)
+                (*nHits)[i] = h;
+        }
     }
 
     clb_ctx* handle() const { return ctx; }
 
   private:
+    // findBestAlignments' state of one read (src/searchstrategy.cpp:623-712): occurrences per strand and distance,
+    // the distances mapped so far, and the variables of the stratum loop
+    struct BestState {
+        uint32_t cutoff, x, best, maxED, k, prevK = 0;
+        int doneUpto = -1;
+        bool bestFound = false, finished = false;
+        std::vector<std::vector<TextOcc>> lv[2];
+        BestState(uint32_t cutoff_, uint32_t x_) : cutoff(cutoff_), x(x_), best(cutoff_ + 1), maxED(cutoff_), k(std::max(x_, 1u)) {
+            lv[0].resize(cutoff + 1);
+            lv[1].resize(cutoff + 1);
+        }
+        void add(int strand, std::vector<TextOcc>& occs) {
+            for (auto& t : occs)
+                if (t.distanceBeforeTrimming <= cutoff)
+                    lv[strand][t.distanceBeforeTrimming].push_back(std::move(t));
+        }
+        // checkAlignments, src/searchstrategy.cpp:537-568
+        void checkLevel(uint32_t level) {
+            for (int strand = 0; strand < 2; strand++) {
+                std::vector<TextOcc> keep, moved;
+                for (auto& t : lv[strand][level]) {
+                    if (t.trimmed) {
+                        if (t.distance > level)
+                            moved.push_back(std::move(t));
+                    } else {
+                        keep.push_back(std::move(t));
+                        best = std::min(best, level);
+                    }
+                }
+                lv[strand][level].swap(keep);
+                for (auto& t : moved)
+                    if (t.distance <= cutoff) {
+                        t.trimmed = false; // removeTrimmingLabel
+                        t.distanceBeforeTrimming = t.distance;
+                        lv[strand][t.distance].push_back(std::move(t));
+                    }
+            }
+        }
+        bool anyUpto(uint32_t d) const {
+            for (int strand = 0; strand < 2; strand++)
+                for (uint32_t i = 0; i <= std::min(d, cutoff); i++)
+                    if (!lv[strand][i].empty())
+                        return true;
+            return false;
+        }
+        void afterExact() { // :637-668
+            doneUpto = 0;
+            if (!lv[0][0].empty() || !lv[1][0].empty()) {
+                checkLevel(0);
+                if (best == 0)
+                    bestFound = true;
+            }
+            maxED = best == 0 ? x : cutoff;
+            if (k > maxED)
+                finished = true;
+        }
+        void step(bool mapped) { // one iteration of the loop at :677-708
+            bool update;
+            if (mapped) {
+                doneUpto = (int)k;
+                update = anyUpto(k);
+            } else {
+                update = !lv[0][k].empty() || !lv[1][k].empty();
+            }
+            if (update)
+                for (uint32_t level = prevK + 1; level <= std::min(k, best + x); level++)
+                    checkLevel(level);
+            if (bestFound) {
+                finished = true;
+                return;
+            }
+            if (update && best < cutoff + 1) {
+                bestFound = true;
+                if (x == 0) {
+                    finished = true;
+                    return;
+                }
+                prevK = k;
+                k = std::min(best + x, maxED);
+            } else {
+                if (k == maxED) {
+                    finished = true;
+                    return;
+                }
+                prevK = k;
+                k = std::min(k + x + (k < 5 ? 2u : 4u), maxED);
+            }
+        }
+        // combineOccVectors, src/searchstrategy.cpp:570-621; returns nHits
+        uint32_t result(std::vector<TextOcc>& out) {
+            out.clear();
+            if (!bestFound)
+                return 0;
+            const uint32_t nHits = (uint32_t)(lv[0][best].size() + lv[1][best].size());
+            for (uint32_t d = best; d <= std::min(best + x, cutoff); d++)
+                for (int strand = 0; strand < 2; strand++) {
+                    auto& v = lv[strand][d];
+                    std::stable_sort(v.begin(), v.end(), [](const TextOcc& a, const TextOcc& b) {
+                        return a.seqID < b.seqID || (a.seqID == b.seqID && a.begin < b.begin);
+                    });
+                    for (size_t i = 0; i < v.size(); i++)
+                        if (i == 0 || v[i].seqID != v[i - 1].seqID || v[i].begin != v[i - 1].begin)
+                            out.push_back(v[i]);
+                }
+            return nHits;
+        }
+    };
     void check(int rc) const {
         if (rc)
             throw std::runtime_error(clb_last_error(ctx));

@@ -2,7 +2,7 @@
 // file in ALL or BEST mode and prints canonical tuples.  Linked against the
 // CUDA library on the GPU box and against the host emulation of the kernels
 // (same C ABI) in the CPU tests.
-//   host_cpp_test <index base> <fastq> <schemes dir> all <k> | best <min identity>
+//   host_cpp_test <index base> <fastq> <schemes dir> all <k> | best <min identity> [x]
 #include <fstream>
 #include <iostream>
 
@@ -33,22 +33,14 @@ int main(int argc, char** argv) {
         if (mode == "all")
             strategy.matchApproxBatch(reads, v, counters, occ);
         else
-            strategy.matchBestBatch(reads, v, 0, counters, occ);
+            strategy.matchBestBatch(reads, v, argc > 6 ? (uint32_t)std::stoul(argv[6]) : 0u, counters, occ);
         const auto& sn = index.getSeqNames();
-        for (size_t i = 0; i < reads.size(); i++) {
-            if (mode == "best" && !occ[i].empty()) { // the primary alignment: distance, then text order
-                auto best = std::min_element(occ[i].begin(), occ[i].end(), [](const clb::TextOcc& a, const clb::TextOcc& b) {
-                    if (a.distance != b.distance) return a.distance < b.distance;
-                    if (a.indexBegin != b.indexBegin) return a.indexBegin < b.indexBegin;
-                    return (a.end - a.begin) < (b.end - b.begin);
-                });
-                std::vector<clb::TextOcc> one(1, *best);
-                occ[i].swap(one);
+        for (size_t i = 0; i < reads.size(); i++)
+            for (size_t j = 0; j < occ[i].size(); j++) { // BEST mode: the first record is the primary alignment
+                const auto& t = occ[i][j];
+                std::cout << names[i] << '\t' << ((t.strand == clb::REVERSE_C_STRAND ? 16 : 0) | (mode == "best" && j ? 256 : 0))
+                          << '\t' << sn[t.seqID] << '\t' << t.begin + 1 << '\t' << t.distance << '\t' << t.cigar << '\n';
             }
-            for (const auto& t : occ[i])
-                std::cout << names[i] << '\t' << (t.strand == clb::REVERSE_C_STRAND ? 16 : 0) << '\t' << sn[t.seqID] << '\t'
-                          << t.begin + 1 << '\t' << t.distance << '\t' << t.cigar << '\n';
-        }
         std::cerr << "reads " << counters.get(CLB_CTR_NUMBER_OF_READS) << " mapped " << counters.get(CLB_CTR_MAPPED_READS)
                   << "\n";
     } catch (std::exception& e) {

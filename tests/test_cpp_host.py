@@ -13,17 +13,17 @@ from test_best_mode import expected_best
 SRC = os.path.join(gu.ROOT, "tests", "cpp", "host_cpp_test.cpp")
 
 
-def build_and_run(lib, base, mode, value):
+def build_and_run(lib, base, mode, value, reads="g1_edit", x=0):
     exe = os.path.join(gu.WORK, "host_cpp_test_" + os.path.basename(lib).replace(".", "_"))
     libdir, libname = os.path.dirname(lib), os.path.basename(lib)[3:-3]
     if not os.path.exists(exe) or os.path.getmtime(exe) < max(os.path.getmtime(SRC), os.path.getmtime(lib)):
         subprocess.check_call(["g++", "-std=c++14", "-O1", "-I", os.path.join(gu.ROOT, "include"), SRC, "-L", libdir,
                                "-l" + libname, "-Wl,-rpath," + libdir, "-o", exe])
-    fq = os.path.join(gu.WORK, "g1_edit.fq")
+    fq = os.path.join(gu.WORK, reads + ".fq")
     if not os.path.exists(fq):
-        with gzip.open(os.path.join(gu.GOLD, "g1_edit.fq.gz"), "rb") as i, open(fq, "wb") as o:
+        with gzip.open(os.path.join(gu.GOLD, reads + ".fq.gz"), "rb") as i, open(fq, "wb") as o:
             o.write(i.read())
-    p = subprocess.run([exe, base, fq, cb.SCHEMES_DIR, mode, str(value)], capture_output=True, text=True)
+    p = subprocess.run([exe, base, fq, cb.SCHEMES_DIR, mode, str(value), str(x)], capture_output=True, text=True)
     assert p.returncode == 0, p.stderr[-500:]
     rows = []
     for line in p.stdout.splitlines():
@@ -32,15 +32,23 @@ def build_and_run(lib, base, mode, value):
     return sorted(rows)
 
 
+def all_and_best(lib, golden_index):
+    assert build_and_run(lib, golden_index, "all", 4) == gu.expected("edit_k4_columba")[0]
+    assert build_and_run(lib, golden_index, "best", 95) == expected_best("best_I95")
+    assert build_and_run(lib, golden_index, "best", 95, x=2) == expected_best("best_I95_x2")
+    # repeat-rich reference: many co-optimal alignments, exact stratum, strata after the best one
+    g2 = gu.index_of({"fasta": "g2"}, lib)
+    assert build_and_run(lib, g2, "best", 95, reads="g3") == expected_best("g3_best_I95")
+    assert build_and_run(lib, g2, "best", 97, reads="g2", x=1) == expected_best("g2_best_I97_x1")
+
+
 def test_cpp_host_all_and_best_kernel_logic(golden_index, hostemu_lib):
-    assert build_and_run(hostemu_lib, golden_index, "all", 4) == gu.expected("edit_k4_columba")[0]
-    assert build_and_run(hostemu_lib, golden_index, "best", 95) == expected_best("best_I95")
+    all_and_best(hostemu_lib, golden_index)
 
 
 @pytest.mark.gpu
 def test_cpp_host_all_and_best_gpu(golden_index, cuda_lib):
-    assert build_and_run(cuda_lib, golden_index, "all", 4) == gu.expected("edit_k4_columba")[0]
-    assert build_and_run(cuda_lib, golden_index, "best", 95) == expected_best("best_I95")
+    all_and_best(cuda_lib, golden_index)
 
 
 def test_cpp_host_reports_missing_device_or_index(cuda_lib, tmp_path):
