@@ -15,15 +15,16 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 DEFAULT_LIB = os.path.join(HERE, "libcolumba_b200.so")
 SCHEMES_DIR = os.path.join(HERE, "schemes")
 
-N_COUNTERS, N_STATS, N_STAGES = 17, 9, 6
+N_COUNTERS, N_STATS, N_STAGES = 17, 11, 6  # CLB_N_COUNTERS, CLB_N_STATS, CLB_N_STAGES of include/columba_b200.h
 COUNTER_NAMES = ["NODE_COUNTER", "TOTAL_REPORTED_POSITIONS", "CIGARS_IN_INDEX", "IN_TEXT_STARTED",
                  "ABORTED_IN_TEXT_VERIF", "CIGARS_IN_TEXT_VERIFICATION", "IMMEDIATE_SWITCH", "SEARCH_STARTED",
                  "DROPPED_UNIQUE_MATCHES", "NUMBER_OF_READS", "TOTAL_UNIQUE_MATCHES", "MAPPED_READS",
                  "TOTAL_UNIQUE_PAIRS", "MAPPED_PAIRS", "DISCORDANTLY_MAPPED_PAIRS", "MAPPED_HALF_PAIRS",
                  "UNPAIRED_BUT_MAPPED_PAIRS"]
 STAT_NAMES = ["RANK_LOOKUPS", "LF_STEPS", "VERIFY_ROWS", "SEARCH_ROWS", "SEARCH_TASKS", "CANDIDATES", "FM_OCCS",
-              "TEXT_OCCS", "SEARCH_LOOKUPS"]
+              "TEXT_OCCS", "SEARCH_LOOKUPS", "UNIQUE_CANDIDATES", "HEAVY_TASKS"]
 STAGE_NAMES = ["prep", "partition", "search", "verify", "fm_expand", "text_filter"]
+assert len(STAT_NAMES) == N_STATS and len(STAGE_NAMES) == N_STAGES
 METRIC = {"hamming": 0, "edit": 1}
 PARTITION = {"uniform": 0, "static": 1, "dynamic": 2}
 
@@ -44,7 +45,7 @@ class ClbError(RuntimeError):
         self.code = code
 
 
-EXPORTS = ["clb_abi_version", "clb_device_count", "clb_index_load", "clb_index_free", "clb_index_text_length",
+EXPORTS = ["clb_abi_version", "clb_sizeof_result", "clb_device_count", "clb_index_load", "clb_index_free", "clb_index_text_length",
            "clb_index_num_seqs", "clb_index_seq_name", "clb_index_seq_start", "clb_index_device_bytes",
            "clb_ctx_create", "clb_ctx_free", "clb_last_error", "clb_ctx_set_strategy", "clb_ctx_set_options",
            "clb_ctx_set_stream", "clb_ctx_set_trim_max", "clb_ctx_set_filter_per_strand", "clb_ctx_supports_distance", "clb_ctx_num_parts", "clb_map_batch", "clb_map_batch_device", "clb_occ4",
@@ -96,6 +97,9 @@ def load_library(path=None):
     lib.clb_build_index.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_char_p, C.c_size_t]
     if hasattr(lib, "clb_gather_ceiling"):  # CUDA library only (the CPU unit-test harness has no such kernel)
         lib.clb_gather_ceiling.argtypes = [vp, C.c_uint64, C.POINTER(C.c_float), C.POINTER(C.c_uint64)]
+    lib.clb_sizeof_result.restype = C.c_size_t
+    if lib.clb_sizeof_result() != C.sizeof(ClbResult):
+        raise ClbError(-6, "clb_result layout of %s differs from this binding's" % path)
     _libs[path] = lib
     return lib
 

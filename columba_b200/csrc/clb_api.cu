@@ -170,6 +170,35 @@ __global__ void __launch_bounds__(128) clb_kernel_warp(const K k, u32 nMax, cons
 }
 template <class K> constexpr auto isWarpTask(int) -> decltype(K::kWarpTask) { return K::kWarpTask; }
 template <class K> constexpr bool isWarpTask(long) { return false; }
+template <class K> constexpr auto groupOfK(int) -> decltype(K::kGroup) { return K::kGroup; }
+template <class K> constexpr int groupOfK(long) { return 32; }
+
+// Group-task functors with K::kGroup > 32: a task is run by all threads of a CTA of K::kGroup threads
+// together (the functor's collectives use __syncthreads); CTAs claim tasks one at a time.
+static const int HEAVY_GROUP = 512;
+template <class K>
+__global__ void __launch_bounds__(HEAVY_GROUP) clb_kernel_cta(const K k, u32 nMax, const u32* __restrict__ nDev, u32* workCtr) {
+    __shared__ u32 claimed;
+    u32 n = nMax;
+    if (nDev) {
+        u32 v = *nDev;
+        n = v < nMax ? v : nMax;
+    }
+    typename K::State st;
+    k.begin(st, blockIdx.x);
+    for (;;) {
+        if (threadIdx.x == 0)
+            claimed = atomicAdd(workCtr, 1u);
+        __syncthreads();
+        const u32 i = claimed;
+        __syncthreads();
+        if (i >= n)
+            break;
+        k.runWarp(st, i);
+        __syncthreads();
+    }
+    k.end(st);
+}
 
 // exclusive scan of n u32 values (out[n] = total) in three launches:
 // per-tile sums, scan of the tile sums by one block, per-tile scan + offset.
@@ -536,20 +565,29 @@ struct CudaBackend {
     u32 blocksFor(int kind) const {
         switch (kind) {
         case WK_SEARCH: return (u32)numSMs * 4;   // x128 threads: 16 warps per SM, one task per warp
-        case WK_SEARCH_HEAVY: return (u32)numSMs; // 4 warps per SM with large scratch
+        case WK_SEARCH_HEAVY: return (u32)numSMs; // one CTA of HEAVY_GROUP threads per SM, with large scratch
         case WK_VERIFY: return (u32)numSMs * 8;
         case WK_FILTER: return (u32)numSMs * 4;
         default: return (u32)numSMs * 16;
         }
     }
-    u32 workers(int kind) { return blocksFor(kind) * 128; }
+    static const int kHeavyGroup = HEAVY_GROUP; // lanes per heavy search task
+    u32 workers(int kind) { return blocksFor(kind) * (kind == WK_SEARCH_HEAVY ? (u32)HEAVY_GROUP : 128u); }
     u32 laneStride() const { return 32; }
     u32 fallbackWorkers() const { return 0; }
     template <class K> void launch(const K& k, u32 nMax, const u32* nDev, int kind) {
         if (nMax == 0)
             return;
         void (*fn)(const K, u32, const u32*, u32*);
-        if constexpr (isWarpTask<K>(0))
+        if constexpr (isWarpTask<K>(0) && groupOfK<K>(0) > 32) {
+            static_assert(groupOfK<K>(0) == HEAVY_GROUP, "CTA size of the group-task launcher");
+            if (nextCtr >= N_CTRS)
+                throw BackendError("work counter pool exhausted");
+            clb_kernel_cta<K><<<blocksFor(kind), HEAVY_GROUP, 0, stream>>>(k, nMax, nDev, workCtrs + nextCtr++);
+            CLB_CUDA(cudaGetLastError());
+            launches++;
+            return;
+        } else if constexpr (isWarpTask<K>(0))
             fn = clb_kernel_warp<K>;
         else if constexpr (isStepped<K>(0))
             fn = clb_kernel_stepped<K>;

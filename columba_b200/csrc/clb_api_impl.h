@@ -41,6 +41,7 @@ static thread_local std::string g_clbLoadError;
 extern "C" {
 
 int clb_abi_version(void) { return CLB_ABI_VERSION; }
+size_t clb_sizeof_result(void) { return sizeof(clb_result); }
 int clb_device_count(void) { return CLB_BE::deviceCount(); }
 
 int clb_index_load(const char* base, int sa_sparse, int kmer, int in_text_switch, int no_cigar, int device,

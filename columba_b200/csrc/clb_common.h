@@ -165,6 +165,8 @@ enum Stat {
     ST_FM_OCCS,       // index occurrences reported by the searches
     ST_TEXT_OCCS,     // text occurrences before the per-read filter
     ST_SEARCH_LOOKUPS, // the part of ST_RANK_LOOKUPS done by the search kernel (rest: partitioning)
+    ST_UNIQUE_CANDS,   // candidates left after collapsing equal verification windows (the ones that are verified)
+    ST_HEAVY_TASKS,    // search tasks re-run by a whole CTA with large scratch
     N_STATS
 };
 

@@ -190,8 +190,9 @@ template <typename W> struct FrontierCaps {
     static constexpr u32 LS = 2 * CL;
 };
 
-// The search of one task by one warp.  `scr` is the warp's scratch.
-template <typename W> struct Frontier {
+// The search of one task by one group of GS lanes: a warp (GS = 32), or a whole CTA of GS threads for the
+// tasks whose trees are too large for a warp to finish in time.  `scr` is the group's scratch.
+template <typename W, int GS> struct Frontier {
     typedef FNode<W> Node;
     static constexpr u32 CL = FrontierCaps<W>::CL, LS = FrontierCaps<W>::LS;
 
@@ -212,7 +213,7 @@ template <typename W> struct Frontier {
                     u8* scr_, u32 cap_)
         : ix(ix_), B(B_), s(s_), pi(pi_), t(t_), searchIdx(si), scr(scr_), cap(cap_), top(0), err(0),
           edit(B_.metric == METRIC_EDIT), nGroups(0) {
-        CLB_LANES(l) {
+        CLB_LANES_G(l, GS) {
             ctr[l].nodes = 0;
             ctr[l].lookups = 0;
             ctr[l].rows = 0;
@@ -353,10 +354,10 @@ template <typename W> struct Frontier {
         lvl[1] = b1;
         while (b1 > b0 && !err) {
             u32 outBase = b1; // children are appended to the node array
-            for (u32 base = b0; base < b1 && !err; base += GRP) {
+            for (u32 base = b0; base < b1 && !err; base += GS) {
                 LV<u32> nKids;
                 LV<Node> kid[4];
-                CLB_LANES(l) {
+                CLB_LANES_G(l, GS) {
                     nKids[l] = 0;
                     const u32 i = base + (u32)l;
                     if (i >= b1)
@@ -473,14 +474,14 @@ template <typename W> struct Frontier {
                     nKids[l] = nk;
                 }
                 LV<u32> off;
-                const u32 total = grpExScan(nKids, off);
+                const u32 total = grpExScanG<GS>(nKids, off);
                 if (total) {
                     const u32 need = alloc((size_t)total * sizeof(Node));
                     (void)need;
                     if (err)
                         break;
                     // the node array of the group is the last allocation: it grows in place
-                    CLB_LANES(l) {
+                    CLB_LANES_G(l, GS) {
 #pragma unroll
                         for (u32 q = 0; q < 4; q++)
                             if (q < nKids[l])
@@ -488,7 +489,7 @@ template <typename W> struct Frontier {
                     }
                     outBase += total;
                 }
-                grpSync();
+                grpSyncG<GS>();
             }
             if (err)
                 break;
@@ -512,8 +513,8 @@ template <typename W> struct Frontier {
         const u32* lvl = lvlOf(G);
         for (u32 L = G.nLevels; L-- > 1;) {
             const u32 b0 = lvl[L], b1 = lvl[L + 1];
-            for (u32 base = b0; base < b1; base += GRP) {
-                CLB_LANES(l) {
+            for (u32 base = b0; base < b1; base += GS) {
+                CLB_LANES_G(l, GS) {
                     const u32 i = base + (u32)l;
                     if (i < b1) {
                         const u32 c = nodes[i].cnt;
@@ -522,19 +523,19 @@ template <typename W> struct Frontier {
                     }
                 }
             }
-            grpSync();
+            grpSyncG<GS>();
         }
         // roots in instance order
         u32 run = 0;
         FPI* pis = pisOf(G);
-        for (u32 base = 0; base < G.nPI; base += GRP) {
+        for (u32 base = 0; base < G.nPI; base += GS) {
             LV<u32> c, off;
-            CLB_LANES(l) {
+            CLB_LANES_G(l, GS) {
                 const u32 i = base + (u32)l;
                 c[l] = i < G.nPI ? nodes[i].cnt : 0u;
             }
-            const u32 tot = grpExScan(c, off);
-            CLB_LANES(l) {
+            const u32 tot = grpExScanG<GS>(c, off);
+            CLB_LANES_G(l, GS) {
                 const u32 i = base + (u32)l;
                 if (i < G.nPI) {
                     nodes[i].base = run + off[l];
@@ -544,15 +545,15 @@ template <typename W> struct Frontier {
             run += tot;
         }
         G.nActs = run;
-        grpSync();
+        grpSyncG<GS>();
         G.actOff = alloc((size_t)(run ? run : 1) * sizeof(FAct));
         if (err)
             return;
         FAct* acts = actsOf(G);
         for (u32 L = 1; L < G.nLevels; L++) {
             const u32 b0 = lvl[L], b1 = lvl[L + 1];
-            for (u32 base = b0; base < b1; base += GRP) {
-                CLB_LANES(l) {
+            for (u32 base = b0; base < b1; base += GS) {
+                CLB_LANES_G(l, GS) {
                     const u32 i = base + (u32)l;
                     if (i < b1) {
                         const u32 p = nodes[i].parent;
@@ -563,10 +564,10 @@ template <typename W> struct Frontier {
                     }
                 }
             }
-            grpSync();
+            grpSyncG<GS>();
         }
-        for (u32 base = 0; base < G.nNodes; base += GRP) {
-            CLB_LANES(l) {
+        for (u32 base = 0; base < G.nNodes; base += GS) {
+            CLB_LANES_G(l, GS) {
                 const u32 i = base + (u32)l;
                 if (i < G.nNodes) {
                     const Node& n = nodes[i];
@@ -582,7 +583,7 @@ template <typename W> struct Frontier {
                 }
             }
         }
-        grpSync();
+        grpSyncG<GS>();
     }
 
     // the cluster of final-column values above a leaf: entry j belongs to row
@@ -744,8 +745,8 @@ template <typename W> struct Frontier {
         const bool edge = edit && s.isEdge(idx);
         // pass 1: clear the marks of every node some leaf may report once
         if (edge) {
-            for (u32 base = 0; base < nA; base += GRP) {
-                CLB_LANES(l) {
+            for (u32 base = 0; base < nA; base += GS) {
+                CLB_LANES_G(l, GS) {
                     const u32 a = base + (u32)l;
                     if (a >= nA)
                         continue;
@@ -760,9 +761,9 @@ template <typename W> struct Frontier {
                         nodes[C.node[ctz64(m)]].cnt = F_NONE;
                 }
             }
-            grpSync();
-            for (u32 base = 0; base < nA; base += GRP) {
-                CLB_LANES(l) {
+            grpSyncG<GS>();
+            for (u32 base = 0; base < nA; base += GS) {
+                CLB_LANES_G(l, GS) {
                     const u32 a = base + (u32)l;
                     if (a >= nA)
                         continue;
@@ -777,14 +778,14 @@ template <typename W> struct Frontier {
                         atomMinU32(&nodes[C.node[ctz64(m)]].cnt, a);
                 }
             }
-            grpSync();
+            grpSyncG<GS>();
         }
         // pass 2: emissions and hand-overs of every leaf; sizes of the lists handed over
         u32 nSpawn = 0;
         size_t listBytes = 0;
-        for (u32 base = 0; base < nA; base += GRP) {
+        for (u32 base = 0; base < nA; base += GS) {
             LV<u32> sp, lb;
-            CLB_LANES(l) {
+            CLB_LANES_G(l, GS) {
                 sp[l] = 0;
                 lb[l] = 0;
                 const u32 a = base + (u32)l;
@@ -845,9 +846,9 @@ template <typename W> struct Frontier {
                 }
             }
             LV<u32> so, lo;
-            const u32 ts = grpExScan(sp, so);
-            const u32 tl = grpExScan(lb, lo);
-            CLB_LANES(l) {
+            const u32 ts = grpExScanG<GS>(sp, so);
+            const u32 tl = grpExScanG<GS>(lb, lo);
+            CLB_LANES_G(l, GS) {
                 const u32 a = base + (u32)l;
                 if (a < nA && sp[l]) {
                     acts[a].spawn = nSpawn + so[l];
@@ -856,7 +857,7 @@ template <typename W> struct Frontier {
             }
             nSpawn += ts;
             listBytes += tl;
-            grpSync();
+            grpSyncG<GS>();
         }
         if (!nSpawn)
             return 0;
@@ -872,8 +873,8 @@ template <typename W> struct Frontier {
         FPI* npis = pisOf(N);
         const bool dswN = nIdx < s.P && s.dsw[nIdx] != 0;
         // pass 3: fill the instances
-        for (u32 base = 0; base < nA; base += GRP) {
-            CLB_LANES(l) {
+        for (u32 base = 0; base < nA; base += GS) {
+            CLB_LANES_G(l, GS) {
                 const u32 a = base + (u32)l;
                 if (a >= nA || acts[a].spawn == F_NONE)
                     continue;
@@ -958,20 +959,20 @@ template <typename W> struct Frontier {
                 acts[a].off = 0;
             }
         }
-        grpSync();
+        grpSyncG<GS>();
         return nSpawn;
     }
 
     // roots of a group (after its instances are filled)
     CLB_HD void initGroup(FGroup& G, const PartSeq& ps) {
-        for (u32 base = 0; base < G.nPI; base += GRP) {
-            CLB_LANES(l) {
+        for (u32 base = 0; base < G.nPI; base += GS) {
+            CLB_LANES_G(l, GS) {
                 const u32 p = base + (u32)l;
                 if (p < G.nPI)
                     initInstance(G, p, ps);
             }
         }
-        grpSync();
+        grpSyncG<GS>();
     }
 
     // emission indices over all groups, then the emissions themselves
@@ -983,8 +984,8 @@ template <typename W> struct Frontier {
             Node* nodes = nodesOf(G);
             FPI* pis = pisOf(G);
             FPI* npis = (q + 1 < nGroups) ? pisOf(grp[q + 1]) : (FPI*)0;
-            for (u32 base = 0; base < G.nActs; base += GRP) {
-                CLB_LANES(l) {
+            for (u32 base = 0; base < G.nActs; base += GS) {
+                CLB_LANES_G(l, GS) {
                     const u32 a = base + (u32)l;
                     if (a < G.nActs) {
                         const u32 w = acts[a].spawn != F_NONE ? npis[acts[a].spawn].total : acts[a].nEv;
@@ -993,7 +994,7 @@ template <typename W> struct Frontier {
                     }
                 }
             }
-            grpSync();
+            grpSyncG<GS>();
         }
         // offsets, first group first
         for (u32 q = 0; q < nGroups; q++) {
@@ -1003,33 +1004,33 @@ template <typename W> struct Frontier {
             FPI* pis = pisOf(G);
             FPI* npis = (q + 1 < nGroups) ? pisOf(grp[q + 1]) : (FPI*)0;
             u32 run = 0;
-            for (u32 base = 0; base < G.nActs; base += GRP) {
+            for (u32 base = 0; base < G.nActs; base += GS) {
                 LV<u32> w, off;
-                CLB_LANES(l) {
+                CLB_LANES_G(l, GS) {
                     const u32 a = base + (u32)l;
                     w[l] = 0;
                     if (a < G.nActs)
                         w[l] = acts[a].spawn != F_NONE ? npis[acts[a].spawn].total : acts[a].nEv;
                 }
-                const u32 tot = grpExScan(w, off);
-                CLB_LANES(l) {
+                const u32 tot = grpExScanG<GS>(w, off);
+                CLB_LANES_G(l, GS) {
                     const u32 a = base + (u32)l;
                     if (a < G.nActs)
                         acts[a].off = run + off[l];
                 }
                 run += tot;
             }
-            grpSync();
-            for (u32 base = 0; base < G.nPI; base += GRP) {
-                CLB_LANES(l) {
+            grpSyncG<GS>();
+            for (u32 base = 0; base < G.nPI; base += GS) {
+                CLB_LANES_G(l, GS) {
                     const u32 p = base + (u32)l;
                     if (p < G.nPI)
                         pis[p].sBegin = pis[p].actBegin < G.nActs ? acts[pis[p].actBegin].off : 0u;
                 }
             }
-            grpSync();
-            for (u32 base = 0; base < G.nActs; base += GRP) {
-                CLB_LANES(l) {
+            grpSyncG<GS>();
+            for (u32 base = 0; base < G.nActs; base += GS) {
+                CLB_LANES_G(l, GS) {
                     const u32 a = base + (u32)l;
                     if (a < G.nActs) {
                         const FPI& P = pis[nodes[acts[a].node].pi];
@@ -1040,7 +1041,7 @@ template <typename W> struct Frontier {
                     }
                 }
             }
-            grpSync();
+            grpSyncG<GS>();
         }
         // emissions
         for (u32 q = 0; q < nGroups; q++) {
@@ -1049,9 +1050,9 @@ template <typename W> struct Frontier {
             Node* nodes = nodesOf(G);
             FPI* pis = pisOf(G);
             const bool isEnd = (G.idx + 1 == s.P);
-            for (u32 base = 0; base < G.nActs; base += GRP) {
+            for (u32 base = 0; base < G.nActs; base += GS) {
                 LV<u32> nc, nf;
-                CLB_LANES(l) {
+                CLB_LANES_G(l, GS) {
                     const u32 a = base + (u32)l;
                     nc[l] = 0;
                     nf[l] = 0;
@@ -1063,11 +1064,11 @@ template <typename W> struct Frontier {
                     }
                 }
                 LV<u32> co, fo;
-                const u32 tc = grpExScan(nc, co), tf = grpExScan(nf, fo);
+                const u32 tc = grpExScanG<GS>(nc, co), tf = grpExScanG<GS>(nf, fo);
                 if (!tc && !tf)
                     continue;
                 LV<u32> cb, fb;
-                CLB_LANES(l) {
+                CLB_LANES_G(l, GS) {
                     cb[l] = 0;
                     fb[l] = 0;
                     if (l == 0) {
@@ -1077,8 +1078,8 @@ template <typename W> struct Frontier {
                             fb[l] = B.fmOccs.reserve(tf, B.err, ERR_FMOCC_OVERFLOW);
                     }
                 }
-                const u32 candAt = grpBcast(cb, 0), fmAt = grpBcast(fb, 0);
-                CLB_LANES(l) {
+                const u32 candAt = grpBcastG<GS>(cb, 0), fmAt = grpBcastG<GS>(fb, 0);
+                CLB_LANES_G(l, GS) {
                     const u32 a = base + (u32)l;
                     if (a >= G.nActs || !acts[a].nEv)
                         continue;
@@ -1157,7 +1158,7 @@ template <typename W> struct Frontier {
         if (err)
             return false;
         Start* st = (Start*)(scr + startOff);
-        CLB_LANES(l) {
+        CLB_LANES_G(l, GS) {
             if (l != 0)
                 continue;
             LocalCtr lc;
@@ -1199,9 +1200,9 @@ template <typename W> struct Frontier {
             S.nodes = lc.c[NODE_COUNTER];
             *st = S;
         }
-        grpSync();
+        grpSyncG<GS>();
         const Start S = *st;
-        CLB_LANES(l) {
+        CLB_LANES_G(l, GS) {
             if (l == 0) {
                 ctr[l].lookups += S.lookups;
                 ctr[l].nodes += S.nodes;
@@ -1210,7 +1211,7 @@ template <typename W> struct Frontier {
         if (S.go == 0)
             return true;
         if (S.go == 2) { // verifyExactPartialMatchInText, src/fmindex/fmindex.cpp:245-265
-            CLB_LANES(l) {
+            CLB_LANES_G(l, GS) {
                 if (l != 0)
                     continue;
                 immediate[l]++;
@@ -1233,7 +1234,7 @@ template <typename W> struct Frontier {
             }
             return true;
         }
-        CLB_LANES(l) {
+        CLB_LANES_G(l, GS) {
             if (l == 0 && edit)
                 searchStarted[l]++;
         }
@@ -1254,11 +1255,11 @@ template <typename W> struct Frontier {
             P.actBegin = P.total = P.base = P.sBegin = 0;
             P.clSize = 0;
             P.g.n = P.g.m = P.g.Wv = P.g.Wh = P.g.maxED = 0;
-            CLB_LANES(l) {
+            CLB_LANES_G(l, GS) {
                 if (l == 0)
                     pisOf(G)[0] = P;
             }
-            grpSync();
+            grpSyncG<GS>();
             nGroups = 1;
         }
         for (;;) {

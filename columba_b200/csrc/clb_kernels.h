@@ -81,11 +81,15 @@ struct EmitKernel {
     CLB_HD void run(State& s, u32 t, unsigned act) const { partFinish(a.ix, *a.st, a.B, t, s.ps, s.lc, act); }
 };
 
-// stage 2: one warp per (read, strand, search) task (clb_frontier.h).  A task
-// whose frontier outgrows the warp's scratch is queued in B.heavy and run again
-// by a second launch of this kernel (heavy = 1) with large scratch.
-template <typename W> struct FrontierKernel {
+// stage 2: one group of GS lanes per (read, strand, search) task (clb_frontier.h).
+// First launch: one warp per task (GS = 32).  A task whose frontier outgrows the
+// warp's scratch is queued in B.heavy and run again by a second launch (heavy = 1)
+// with large scratch and, on the GPU, a whole CTA of GS threads per task: such a
+// task has levels of thousands of nodes, and the launch lasts as long as its
+// longest task.
+template <typename W, int GS> struct FrontierKernel {
     static const bool kWarpTask = true;
+    static const int kGroup = GS;
     IndexView ix;
     const DevStrategy* st;
     Batch B;
@@ -99,28 +103,28 @@ template <typename W> struct FrontierKernel {
         u8* scr;
     };
     CLB_HD void begin(State& s, u32 warp) const {
-        CLB_LANES(l) {
+        CLB_LANES_G(l, GS) {
             s.ctr[l].nodes = s.ctr[l].lookups = s.ctr[l].rows = s.ctr[l].fmOccs = 0;
             s.started[l] = 0;
             s.immediate[l] = 0;
         }
         s.tasks = 0;
-        s.scr = slabs + (size_t)warp * slabBytes;
+        s.scr = slabs + (size_t)warp * slabBytes; // warp = index of the group (warp or CTA)
     }
     CLB_HD void runWarp(State& s, u32 i) const {
         const u32 ti = heavy ? B.heavy.data[i] : i;
         const SearchTask task = B.tasks.data[ti];
         const PartInfo pi = B.parts.load(task.t, st->P);
         const DevSearch& se = st->sc[pi.scheme].s[task.search];
-        Frontier<W> F(ix, B, se, pi, task.t, task.search, s.scr, (u32)slabBytes);
+        Frontier<W, GS> F(ix, B, se, pi, task.t, task.search, s.scr, (u32)slabBytes);
         LV<u64> started, immediate;
-        CLB_LANES(l) {
+        CLB_LANES_G(l, GS) {
             started[l] = 0;
             immediate[l] = 0;
         }
         const bool ok = F.run(started, immediate);
         if (!ok) {
-            CLB_LANES(l) {
+            CLB_LANES_G(l, GS) {
                 if (l == 0) {
                     if (F.err == ERR_STACK_OVERFLOW && !heavy)
                         B.heavy.push(ti, B.err, ERR_TASK_OVERFLOW);
@@ -131,7 +135,7 @@ template <typename W> struct FrontierKernel {
             return;
         }
         s.tasks++;
-        CLB_LANES(l) {
+        CLB_LANES_G(l, GS) {
             s.ctr[l].nodes += F.ctr[l].nodes;
             s.ctr[l].lookups += F.ctr[l].lookups;
             s.ctr[l].rows += F.ctr[l].rows;
@@ -141,7 +145,7 @@ template <typename W> struct FrontierKernel {
         }
     }
     CLB_HD void end(State& s) const {
-        CLB_LANES(l) {
+        CLB_LANES_G(l, GS) {
             if (s.ctr[l].nodes)
                 atomAdd64(B.counters + NODE_COUNTER, s.ctr[l].nodes);
             if (s.ctr[l].lookups) {

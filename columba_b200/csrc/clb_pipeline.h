@@ -316,22 +316,21 @@ template <typename BE> struct Pipeline {
             // outgrew the first launch's
             const bool wide = opt.k > BPC<u64>::MAX_ED;
             const u32 nWarps = be.workers(WK_SEARCH) / be.laneStride();
-            const u32 nHeavyWarps = be.workers(WK_SEARCH_HEAVY) / be.laneStride();
             const size_t minSlab = ((size_t)(maxLen + 128) * 4 * (P + 2) + 65536 + 255) & ~(size_t)255;
             const size_t sb = tmax<size_t>(searchSlabBytes, minSlab), hb = tmax<size_t>(heavySlabBytes, sb);
-            bSlabSearch.ensure(be, tmax<size_t>(sb * nWarps, hb * nHeavyWarps));
+            // heavy tasks: one group of BE::kHeavyGroup lanes (a CTA on the GPU) per task
+            const u32 nHeavyGroups = tmax<u32>(1u, be.workers(WK_SEARCH_HEAVY) / ((u32)BE::kHeavyGroup / 32u * be.laneStride()));
+            bSlabSearch.ensure(be, tmax<size_t>(sb * nWarps, hb * nHeavyGroups));
             if (wide) {
-                FrontierKernel<u128> k2{ix, dst, B, (u8*)bSlabSearch.p, sb, 0};
+                FrontierKernel<u128, 32> k2{ix, dst, B, (u8*)bSlabSearch.p, sb, 0};
                 be.launch(k2, capTasks, &M->nTasks, WK_SEARCH);
-                k2.slabBytes = hb;
-                k2.heavy = 1;
-                be.launch(k2, capTasks, &M->nHeavy, WK_SEARCH_HEAVY);
+                FrontierKernel<u128, BE::kHeavyGroup> k2h{ix, dst, B, (u8*)bSlabSearch.p, hb, 1};
+                be.launch(k2h, capTasks, &M->nHeavy, WK_SEARCH_HEAVY);
             } else {
-                FrontierKernel<u64> k2{ix, dst, B, (u8*)bSlabSearch.p, sb, 0};
+                FrontierKernel<u64, 32> k2{ix, dst, B, (u8*)bSlabSearch.p, sb, 0};
                 be.launch(k2, capTasks, &M->nTasks, WK_SEARCH);
-                k2.slabBytes = hb;
-                k2.heavy = 1;
-                be.launch(k2, capTasks, &M->nHeavy, WK_SEARCH_HEAVY);
+                FrontierKernel<u64, BE::kHeavyGroup> k2h{ix, dst, B, (u8*)bSlabSearch.p, hb, 1};
+                be.launch(k2h, capTasks, &M->nHeavy, WK_SEARCH_HEAVY);
             }
             be.mark(STG_SEARCH);
         }
@@ -430,6 +429,8 @@ template <typename BE> struct Pipeline {
             res->err = err;
             memcpy(res->counters, hm.counters, sizeof(hm.counters));
             memcpy(res->stats, hm.stats, sizeof(hm.stats));
+            res->stats[ST_UNIQUE_CANDS] = opt.metric == METRIC_EDIT ? tmin(hm.nUniq, capCands) : tmin(hm.nCands, capCands);
+            res->stats[ST_HEAVY_TASKS] = hm.nHeavy;
             res->cigW = B.cigW;
             if (fetch && !(err & ~(u32)ERR_SHORT_READ)) {
                 u32 n = hm.nOut;

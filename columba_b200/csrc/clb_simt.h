@@ -57,6 +57,54 @@ __device__ __forceinline__ u32 grpMax(const LV<u32>& x) {
 }
 __device__ __forceinline__ u32 grpBcast(const LV<u32>& x, int src) { return __shfl_sync(0xFFFFFFFFu, x.v, src); }
 __device__ __forceinline__ u32 atomMinU32(u32* p, u32 v) { return atomicMin(p, v); }
+// The same collectives for a group of GS lanes: GS == 32 is a warp, a larger GS is
+// the whole CTA (blockDim.x == GS), whose collectives go through shared memory and
+// __syncthreads.  A routine written with these runs unchanged with either group.
+template <int GS> __device__ __forceinline__ int grpLaneG() { return GS == 32 ? (int)(threadIdx.x & 31u) : (int)threadIdx.x; }
+#define CLB_LANES_G(l, GS) for (int l = grpLaneG<GS>(), l##_go = 1; l##_go; l##_go = 0)
+template <int GS> __device__ __forceinline__ void grpSyncG() {
+    if (GS == 32)
+        __syncwarp();
+    else
+        __syncthreads();
+}
+template <int GS> __device__ __forceinline__ u32 grpExScanG(const LV<u32>& x, LV<u32>& out) {
+    if (GS == 32)
+        return grpExScan(x, out);
+    __shared__ u32 wsum[GS / 32 + 1];
+    const u32 lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    u32 incl = x.v;
+#pragma unroll
+    for (u32 o = 1; o < 32; o <<= 1) {
+        const u32 t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+        if (lane >= o)
+            incl += t;
+    }
+    if (lane == 31)
+        wsum[warp] = incl;
+    __syncthreads();
+    u32 before = 0, total = 0;
+#pragma unroll
+    for (u32 w = 0; w < GS / 32; w++) {
+        const u32 v = wsum[w];
+        before += w < warp ? v : 0u;
+        total += v;
+    }
+    __syncthreads();
+    out.v = before + incl - x.v;
+    return total;
+}
+template <int GS> __device__ __forceinline__ u32 grpBcastG(const LV<u32>& x, int src) {
+    if (GS == 32)
+        return grpBcast(x, src);
+    __shared__ u32 slot;
+    if ((int)threadIdx.x == src)
+        slot = x.v;
+    __syncthreads();
+    const u32 v = slot;
+    __syncthreads();
+    return v;
+}
 #else
 template <typename T> struct LV {
     T v[GRP];
@@ -93,6 +141,11 @@ inline u32 grpMax(const LV<u32>& x) {
     return s;
 }
 inline u32 grpBcast(const LV<u32>& x, int src) { return x.v[src]; }
+// the CPU harness always emulates a group of 32 lanes
+#define CLB_LANES_G(l, GS) for (int l = 0; l < GRP; l++)
+template <int GS> inline void grpSyncG() { static_assert(GS == GRP, "the host emulation runs groups of 32 lanes"); }
+template <int GS> inline u32 grpExScanG(const LV<u32>& x, LV<u32>& out) { return grpExScan(x, out); }
+template <int GS> inline u32 grpBcastG(const LV<u32>& x, int src) { return grpBcast(x, src); }
 inline u32 atomMinU32(u32* p, u32 v) {
     const u32 o = *p;
     if (v < o)

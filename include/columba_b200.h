@@ -51,7 +51,8 @@ enum {
 /* device statistics next to the reference's counters */
 enum {
     CLB_STAT_RANK_LOOKUPS, CLB_STAT_LF_STEPS, CLB_STAT_VERIFY_ROWS, CLB_STAT_SEARCH_ROWS, CLB_STAT_SEARCH_TASKS,
-    CLB_STAT_CANDIDATES, CLB_STAT_FM_OCCS, CLB_STAT_TEXT_OCCS, CLB_STAT_SEARCH_LOOKUPS, CLB_N_STATS
+    CLB_STAT_CANDIDATES, CLB_STAT_FM_OCCS, CLB_STAT_TEXT_OCCS, CLB_STAT_SEARCH_LOOKUPS, CLB_STAT_UNIQUE_CANDIDATES,
+    CLB_STAT_HEAVY_TASKS, CLB_N_STATS
 };
 enum { CLB_N_STAGES = 6 }; /* prep, partition, search, verify, fm-expand, text-filter */
 
@@ -178,6 +179,7 @@ int clb_gather_ceiling(clb_ctx*, uint64_t n_lookups, float* ms, uint64_t* done);
 int clb_build_index(const char* fasta, const char* base, int sa_sparse, char* err, size_t err_len);
 
 int clb_abi_version(void);
+size_t clb_sizeof_result(void); /* sizeof(clb_result): lets a foreign-language binding check its struct layout */
 int clb_device_count(void);
 
 #ifdef __cplusplus
