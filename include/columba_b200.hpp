@@ -94,6 +94,11 @@ class SearchStrategy {
     SearchStrategy(const SearchStrategy&) = delete;
     SearchStrategy& operator=(const SearchStrategy&) = delete;
 
+    // BEST and paired-end mode map and filter the two strands of a read separately (the results then come in
+    // groups 2 * read + strand) and clip alignments at sequence ends up to the cut-off instead of the distance
+    void setFilterPerStrand(bool perStrand) { check(clb_ctx_set_filter_per_strand(ctx, perStrand ? 1 : 0)); }
+    void setTrimMax(uint32_t largestStratum) { check(clb_ctx_set_trim_max(ctx, (int)largestStratum)); }
+
     bool supportsDistanceScore(int maxScore) const { return maxScore == 0 || clb_ctx_supports_distance(ctx, maxScore); }
     int calculateNumParts(int maxED) const { return clb_ctx_num_parts(ctx, maxED); }
     // src/searchstrategy.h:1797-1806
