@@ -175,9 +175,9 @@ template <class K> constexpr int groupOfK(long) { return 32; }
 
 // Group-task functors with K::kGroup > 32: a task is run by all threads of a CTA of K::kGroup threads
 // together (the functor's collectives use __syncthreads); CTAs claim tasks one at a time.
-static const int HEAVY_GROUP = 512;
+static const int HEAVY_GROUP = 256, HEAVY_CTAS_PER_SM = 2;
 template <class K>
-__global__ void __launch_bounds__(HEAVY_GROUP) clb_kernel_cta(const K k, u32 nMax, const u32* __restrict__ nDev, u32* workCtr) {
+__global__ void __launch_bounds__(HEAVY_GROUP, HEAVY_CTAS_PER_SM) clb_kernel_cta(const K k, u32 nMax, const u32* __restrict__ nDev, u32* workCtr) {
     __shared__ u32 claimed;
     u32 n = nMax;
     if (nDev) {
@@ -565,7 +565,7 @@ struct CudaBackend {
     u32 blocksFor(int kind) const {
         switch (kind) {
         case WK_SEARCH: return (u32)numSMs * 4;   // x128 threads: 16 warps per SM, one task per warp
-        case WK_SEARCH_HEAVY: return (u32)numSMs; // one CTA of HEAVY_GROUP threads per SM, with large scratch
+        case WK_SEARCH_HEAVY: return (u32)numSMs * HEAVY_CTAS_PER_SM; // CTAs of HEAVY_GROUP threads, with large scratch
         case WK_VERIFY: return (u32)numSMs * 8;
         case WK_FILTER: return (u32)numSMs * 4;
         default: return (u32)numSMs * 16;

@@ -227,6 +227,8 @@ struct Batch {
     u32* candStart;        // cands.cap : start of the verification window in the text (edit distance)
     u32* candMult;         // cands.cap : number of candidates a unique candidate stands for
     DevList<u32> uniq;     // candidates with distinct (sequence, window): the ones that are verified
+    DevList<u32> surv;     // unique candidates that the screening pass could not settle (full verification)
+    u32 verifyRowsCap;     // rows the verification scratch is sized for
     DevList<FMOccRec> fmOccs;
     DevList<TextOccRec> textOccs;
     u16* textCig;          // textOccs.cap x cigW

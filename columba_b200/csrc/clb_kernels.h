@@ -230,13 +230,35 @@ struct VerifyKernel {
             return;
         }
         if (B.metric == METRIC_EDIT) {
-            verifyEditTask(ix, B, B.uniq.data[i], s.vs, s.lc, 0);
+            verifyEditTask(ix, B, B.surv.data[i], s.vs, s.lc, 0);
         } else {
             s.lc.s[ST_CANDIDATES]++;
             verifyHammingTask(ix, B, i, s.lc);
         }
     }
     CLB_HD void end(State& s) const { s.lc.flush(B.counters, B.stats); }
+};
+
+// stage 3c': screening pass (clb_verify.h), stepped with lane refill
+struct ScreenKernel {
+    IndexView ix;
+    Batch B;
+    static const bool kStepped = true;
+    struct State {
+        LocalCtr lc;
+        ScreenState s;
+    };
+    CLB_HD void begin(State& st, u32) const { st.lc.clear(); }
+    CLB_HD void run(State& st, u32 i) const {
+        start(st, i);
+        while (!step(st)) {
+        }
+        finish(st);
+    }
+    CLB_HD void start(State& st, u32 i) const { screenStart(ix, B, B.uniq.data[i], st.s); }
+    CLB_HD bool step(State& st) const { return screenStep(ix, st.s); }
+    CLB_HD void finish(State& st) const { screenFinish(B, st.s, st.lc); }
+    CLB_HD void end(State& st) const { st.lc.flush(B.counters, B.stats); }
 };
 
 // stage 3a / 3b (edit distance)

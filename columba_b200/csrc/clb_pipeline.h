@@ -111,7 +111,7 @@ template <typename BE> struct Pipeline {
         bMisc, bSlabPart, bSlabSearch, bSlabVerify, bSlabVerifyWide, bSlabFilter, bStrategy;
     // list capacities (per read multipliers, grown after an overflow)
     double candPerRead = 24, fmPerRead = 4, txPerRead = 24, outPerRead = 8;
-    size_t searchSlabBytes = (size_t)256 << 10, heavySlabBytes = (size_t)32 << 20; // scratch per warp of the search
+    size_t searchSlabBytes = (size_t)1 << 20, heavySlabBytes = (size_t)32 << 20; // scratch per warp of the search
     u32 minCap = 1 << 16;
     std::string lastError;
 
@@ -129,7 +129,7 @@ template <typename BE> struct Pipeline {
         u64 counters[N_COUNTERS];
         u64 stats[N_STATS];
         u32 err;
-        u32 nTasks, nCands, nFm, nTx, nOut, nExtra, nCigJobs, nUniq, nHeavy, nTrim;
+        u32 nTasks, nCands, nFm, nTx, nOut, nExtra, nCigJobs, nUniq, nHeavy, nTrim, nSurv;
         u32 fmSlots[2];
         u32 nT, nR; // 2R and R as device-side task counts
     };
@@ -209,7 +209,7 @@ template <typename BE> struct Pipeline {
                   capOut = capOf(outPerRead);
         bTasks.ensure(be, (size_t)capTasks * (sizeof(SearchTask) + sizeof(u32)));
         bCands.ensure(be, (size_t)capCands * sizeof(Cand));
-        bCandAux.ensure(be, (size_t)capCands * 3 * sizeof(u32));
+        bCandAux.ensure(be, (size_t)capCands * 4 * sizeof(u32));
         const u32 capExtra = capCands / 4 + 1024;
         bExtra.ensure(be, (size_t)capExtra * sizeof(u32));
         bFm.ensure(be, (size_t)capFm * sizeof(FMOccRec));
@@ -232,6 +232,7 @@ template <typename BE> struct Pipeline {
         B.candStart = (u32*)bCandAux.p;
         B.candMult = B.candStart + capCands;
         B.uniq.data = B.candMult + capCands; B.uniq.count = &M->nUniq; B.uniq.cap = capCands;
+        B.surv.data = B.uniq.data + capCands; B.surv.count = &M->nSurv; B.surv.cap = capCands;
         B.extra.data = (u32*)bExtra.p; B.extra.count = &M->nExtra; B.extra.cap = capExtra;
         B.fmOccs.data = (FMOccRec*)bFm.p; B.fmOccs.count = &M->nFm; B.fmOccs.cap = capFm;
         B.textOccs.data = (TextOccRec*)bTx.p; B.textOccs.count = &M->nTx; B.textOccs.cap = capTx;
@@ -283,6 +284,7 @@ template <typename BE> struct Pipeline {
             be.mark(STG_PREP);
         }
         const u32 vRows = maxLen + 3 * kk + 8;
+        B.verifyRowsCap = vRows;
         if (opt.k == 0) {
             // exact stratum: backward exact match + text compare, one task per read
             ExactKernel e0{ix, B};
@@ -349,7 +351,9 @@ template <typename BE> struct Pipeline {
                 be.launch(l1, capCands, &M->nCands, WK_LIGHT);
                 DedupKernel l2{B, wide ? 0u : 1u};
                 be.launch(l2, capCands, &M->nCands, WK_LIGHT);
-                be.launch(k3, capCands, &M->nUniq, WK_VERIFY);
+                ScreenKernel l3{ix, B};
+                be.launch(l3, capCands, &M->nUniq, WK_LIGHT);
+                be.launch(k3, capCands, &M->nSurv, WK_VERIFY);
             } else {
                 be.launch(k3, capCands, &M->nCands, WK_VERIFY);
             }

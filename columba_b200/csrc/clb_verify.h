@@ -116,6 +116,8 @@ struct BandStore {
     u32 cpStride;
     u32 cpCap;
 };
+// checkpoints the full verification has room for (VerifyKernel::cpCapOf of the batch's rows capacity)
+CLB_HD u32 VerifyKernelCpCap(const Batch& B) { return B.verifyRowsCap / BPC<u64>::BLOCK + 2; }
 struct VerifyScratch {
     void* rows;   // Row<u128>[rowsCap], thread private (wide path only; may be null)
     BandStore bs; // fast path
@@ -468,6 +470,178 @@ CLB_HD void verifyEditTask(const IndexView& ix, const Batch& B, u32 ci, VerifySc
         lc.c[ABORTED_IN_TEXT_VERIF] += mult;
     lc.c[TOTAL_REPORTED_POSITIONS] += (u64)(sink.sub - first) * mult;
     lc.s[ST_TEXT_OCCS] += sink.sub - first;
+}
+
+// Screening pass of the edit-distance verification.  Nine candidates out of ten are
+// aborted after a fraction of their rows (the right-most active column leaves the
+// band), at a different row in every lane, so a warp that verifies 32 candidates side
+// by side idles most of its lanes.  The screening pass runs only the forward
+// recurrence -- no band storage, no checkpoints, no traceback -- as a stepped task
+// (start / step / finish): a lane whose candidate is decided takes the next one while
+// the others keep stepping (clb_kernel_stepped).  A candidate without a cluster centre
+// is settled here (counters as the full verification would count them); one with a
+// centre goes to the `surv` list, which the full verification (forward pass with band
+// storage + traceback) works off as a dense list of equally long tasks.
+struct ScreenState {
+    u64 HP, HN, RAC, M0, M1, M2, M3, tcur, tnxt;
+    const u64* planes;
+    u32 ci, start, size, i, score, mult;
+    u32 Wv, firstRow, col, sofc, nw, len;
+    u8 maxED, minED, run, considered, ok, done;
+    u8 eds[3 * BPC<u64>::MAX_ED + 4];
+};
+CLB_HD u32 screenEdAtCol(const ScreenState& s, u32 i) {
+    typedef BPC<u64> K;
+    const u32 bit = (i % K::BLOCK) + K::DIAG_R0, col = s.col;
+    const u32 b = (i > col) ? bit - (i - col) + 1 : bit + 1;
+    const u32 e = (i > col) ? bit + 1 : bit + (col - i) + 1;
+    const u64 mask = ((1ull << (e - b)) - 1ull) << b;
+    const int neg = popc64(s.HN & mask), pos = popc64(s.HP & mask);
+    return s.score + ((i > col) ? (u32)(neg - pos) : (u32)(pos - neg));
+}
+CLB_HD void screenStart(const IndexView& ix, const Batch& B, u32 ci, ScreenState& s) {
+    typedef BPC<u64> K;
+    const Cand c = B.cands.data[ci];
+    s.ci = ci;
+    s.start = B.candStart[ci];
+    s.mult = B.candMult[ci];
+    s.maxED = c.maxED;
+    s.minED = c.minED;
+    const u32 nZeros = c.fixedStart ? 1u : 2 * (u32)c.maxED + 1;
+    const u32 len = seqLen(B, c.t);
+    s.done = 0;
+    s.ok = 1;
+    s.run = 1;
+    s.considered = 1;
+    if (!use64(nZeros, c.maxED)) { // 128-bit matrices: straight to the full verification
+        s.done = 2;
+        return;
+    }
+    const u32 nRows = nZeros - 1 + c.maxED + len + 1;
+    const u32 end = tmin(ix.textLength - 1, s.start + nRows - 1);
+    const PartSeq ps = fullSeq(B, c.t);
+    s.planes = ps.planes;
+    s.nw = ps.nw;
+    s.len = ps.len;
+    const u32 n = len + 1;
+    s.Wv = nZeros - 1 + c.maxED;
+    const u32 Wh = c.maxED, m = s.Wv + n;
+    s.sofc = Wh + s.Wv + 1;
+    s.size = end <= s.start ? 0u : end - s.start;
+    s.firstRow = (m - 1) - s.sofc;
+    s.col = n - 1;
+    s.i = 1;
+    s.score = 0;
+    if (!(s.size >= m - s.sofc)) {
+        s.considered = 0;
+        s.run = 0;
+        s.done = 1;
+        return;
+    }
+    if (s.size / K::BLOCK + 1 > VerifyKernelCpCap(B)) { // the full verification would raise ERR_ROWS_OVERFLOW: let it
+        s.done = 2;
+        return;
+    }
+    s.HP = (~0ull) << K::LEFT;
+    s.HN = ~s.HP;
+    {
+        const u32 nn = tmin<u32>(nZeros, K::LEFT + 1);
+        for (u32 i = 1; i < nn; ++i)
+            s.HN ^= 1ull << (K::LEFT - i);
+    }
+    s.RAC = 1ull << (K::DIAG_R0 + Wh);
+    if (s.firstRow == 0)
+        s.eds[0] = (u8)screenEdAtCol(s, 0);
+    s.M0 = matchVec<u64>(ps, 0, 0);
+    s.M1 = matchVec<u64>(ps, 0, 1);
+    s.M2 = matchVec<u64>(ps, 0, 2);
+    s.M3 = matchVec<u64>(ps, 0, 3);
+    s.tcur = textWindow64(ix, s.start) << 2;
+    s.tnxt = textWindow64(ix, s.start + K::BLOCK - 1);
+    if (s.size == 0)
+        s.done = 1;
+}
+// up to SCREEN_ROWS rows; true when the candidate is decided
+enum { SCREEN_ROWS = 8 };
+CLB_HD bool screenStep(const IndexView& ix, ScreenState& s) {
+    typedef BPC<u64> K;
+    if (s.done)
+        return true;
+    PartSeq ps;
+    ps.planes = s.planes;
+    ps.nw = s.nw;
+    ps.base = 0;
+    ps.len = s.len;
+    u32 i = s.i;
+    const u32 last = tmin(s.size, i + SCREEN_ROWS - 1);
+    for (; i <= last; ++i) {
+        const u32 l = i % K::BLOCK;
+        s.RAC <<= 1;
+        if (l == 0) {
+            s.tcur = s.tnxt;
+            s.tnxt = textWindow64(ix, s.start + i + K::BLOCK - 1);
+            s.HP >>= K::BLOCK;
+            s.HN >>= K::BLOCK;
+            s.RAC >>= K::BLOCK;
+            const u32 b = i / K::BLOCK;
+            s.M0 = matchVec<u64>(ps, b, 0);
+            s.M1 = matchVec<u64>(ps, b, 1);
+            s.M2 = matchVec<u64>(ps, b, 2);
+            s.M3 = matchVec<u64>(ps, b, 3);
+        }
+        const u32 Y = (u32)(s.tcur >> (2 * l)) & 3u;
+        const u64 M = pickM(s.M0, s.M1, s.M2, s.M3, Y);
+        const u64 D0 = bandRow(s.HP, s.HN, M);
+        const u32 diagBit = l + K::DIAG_R0;
+        s.score += (D0 >> diagBit) & 1ull ? 0u : 1u;
+        if (!(D0 & s.RAC)) {
+            u32 val = 1u;
+            while (val > 0) {
+                if (s.HP & s.RAC)
+                    val--;
+                if (s.HN & s.RAC)
+                    val++;
+                if (s.RAC == (1ull << (diagBit - s.Wv))) {
+                    s.ok = 0;
+                    break;
+                }
+                s.RAC >>= 1;
+            }
+        }
+        if (!s.ok)
+            break;
+        if (i >= s.firstRow)
+            s.eds[i - s.firstRow] = (u8)screenEdAtCol(s, i);
+    }
+    s.i = i;
+    if (!s.ok || i > s.size)
+        s.done = 1;
+    return s.done != 0;
+}
+CLB_HD void screenFinish(const Batch& B, ScreenState& s, LocalCtr& lc) {
+    bool survivor = s.done == 2;
+    u32 rows = 0;
+    if (!survivor && s.run) {
+        rows = (s.i <= s.size) ? s.i : s.size;
+        const u32 lastRow = s.i - 1;
+        if (!(lastRow <= s.size - s.sofc)) // unsigned compare, as in the reference
+            for (u32 r = lastRow; r > s.firstRow && !survivor; r--) {
+                const u32 ED = s.eds[r - s.firstRow];
+                if (ED > s.maxED || ED < s.minED)
+                    continue;
+                const bool above = ED <= s.eds[r - 1 - s.firstRow];
+                const bool below = (r == lastRow) || ED <= s.eds[r + 1 - s.firstRow];
+                survivor = above && below;
+            }
+    }
+    if (survivor) {
+        B.surv.push(s.ci, B.err, ERR_CAND_OVERFLOW);
+        return;
+    }
+    lc.c[IN_TEXT_STARTED] += s.mult;
+    if (s.considered)
+        lc.c[ABORTED_IN_TEXT_VERIF] += s.mult;
+    lc.s[ST_VERIFY_ROWS] += rows;
 }
 
 // stage 3 task (Hamming distance), fmindex.cpp:358-407
