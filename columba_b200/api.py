@@ -35,6 +35,7 @@ OCC_DTYPE = np.dtype([("read", "<u4"), ("seq_id", "<u4"), ("pos", "<u4"), ("end"
 class ClbResult(C.Structure):
     _fields_ = [("n_reads", C.c_uint32), ("n_groups", C.c_uint32), ("n_occ", C.c_uint32), ("occ", C.c_void_p), ("cigar", C.c_void_p),
                 ("cigar_stride", C.c_uint32), ("read_start", C.c_void_p), ("read_count", C.c_void_p),
+                ("read_status", C.c_void_p), ("n_short_reads", C.c_uint32),
                 ("counters", C.c_uint64 * N_COUNTERS), ("stats", C.c_uint64 * N_STATS),
                 ("stage_ms", C.c_float * N_STAGES), ("total_ms", C.c_float), ("gpu_launches", C.c_uint32)]
 
@@ -144,6 +145,8 @@ class BatchResult:
                 .reshape(n, r.cigar_stride).copy() if n else np.zeros((0, r.cigar_stride), np.uint16)
             self.read_start = np.frombuffer((C.c_uint32 * r.n_groups).from_address(r.read_start), dtype=np.uint32).copy()
             self.read_count = np.frombuffer((C.c_uint32 * r.n_groups).from_address(r.read_count), dtype=np.uint32).copy()
+            self.read_status = np.frombuffer((C.c_uint8 * r.n_reads).from_address(r.read_status), dtype=np.uint8).copy()
+            self.n_short_reads = r.n_short_reads
         else:
             self.occ = None
 
@@ -234,15 +237,14 @@ class Mapper:
         off[1:] = np.cumsum([len(b) for b in bs])
         return np.frombuffer(b"".join(bs), dtype=np.uint8).copy(), off
 
-    def map_batch(self, reads, offsets, max_dist, min_dist=0, allow_short=False):
+    def map_batch(self, reads, offsets, max_dist, min_dist=0, allow_short=True):
         """reads: uint8 array of concatenated reads, offsets: uint32[n+1] (host)."""
         reads = np.ascontiguousarray(reads, np.uint8)
         offsets = np.ascontiguousarray(offsets, np.uint32)
         r = ClbResult()
         rc = self.lib.clb_map_batch(self.h, _ptr(reads), _ptr(offsets), len(offsets) - 1, max_dist, min_dist,
                                     C.byref(r))
-        if rc and not (allow_short and rc == -4 and r.n_reads):
-            self._check(rc)
+        self._check(rc)
         return BatchResult(r)
 
     def map_batch_device(self, d_reads_ptr, d_offsets_ptr, n_reads, max_read_len, max_dist, min_dist=0, fetch=False):

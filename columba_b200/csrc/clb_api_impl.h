@@ -196,14 +196,14 @@ static int clbFinish(clb_ctx* c, clb::u32 err, uint32_t n_reads, clb_result* out
             out->cigar = c->res.cig.data();
             out->read_start = c->res.outStart.data();
             out->read_count = c->res.outCount.data();
+            out->read_status = c->res.readStatus.data();
+            out->n_short_reads = c->res.nShort;
         }
         c->be->fillTimings(out->stage_ms, &out->total_ms, &out->gpu_launches);
     }
-    if (err & ERR_SHORT_READ) {
+    if (err & ERR_SHORT_READ) // not an error of the batch: read_status tells which reads were skipped
         c->err = "The pattern size is too short for the current number of parts (the naive fallback of "
                  "src/searchstrategy.cpp:442-459 is not implemented on the device); such reads got no hits";
-        return CLB_E_UNSUPPORTED;
-    }
     return CLB_OK;
 }
 static int clbPrepare(clb_ctx* c, int max_dist, int min_dist) {
@@ -283,7 +283,18 @@ int clb_map_batch_device(clb_ctx* c, const uint8_t* d_reads, const uint32_t* d_o
         int rc = clbPrepare(c, max_dist, min_dist);
         if (rc)
             return rc;
+        if (max_read_len > 16000) {
+            c->err = "reads longer than 16000 are not supported";
+            return CLB_E_UNSUPPORTED;
+        }
         c->be->beginBatch();
+        // every per-read buffer is sized from max_read_len: check it against the offsets before anything is written
+        const clb::u32 longest = c->pipe->maxReadLen(d_offsets, n_reads);
+        if (longest > max_read_len) {
+            c->be->endBatch();
+            c->err = "a read of " + std::to_string(longest) + " characters exceeds max_read_len = " + std::to_string(max_read_len);
+            return CLB_E_INVALID;
+        }
         clb::u32 err = c->pipe->run(c->flat[max_dist], d_reads, d_offsets, n_reads, max_read_len, 0, true, c->opt,
                                     &c->res, fetch != 0);
         c->be->endBatch();

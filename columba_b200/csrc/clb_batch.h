@@ -245,6 +245,7 @@ struct Batch {
     TrimRec* trimRecs;          // per job: the clipped alignment
     u16* trimCig;               // per job x cigW
     u32* trimOf;                // per sorted slot: its job
+    u8* readStatus; // R : 1 = too short to be partitioned (no search was run for it)
     u32* outCount;  // G+1 : surviving occurrences per group
     u32* outStart;  // G+1 : first output slot of the group (outStart[G] = number of outputs)
     DevList<OutOcc> out;

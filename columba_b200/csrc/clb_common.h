@@ -70,6 +70,14 @@ CLB_HD void atomOr(u32* p, u32 v) {
     *p |= v;
 #endif
 }
+CLB_HD void atomMaxU32(u32* p, u32 v) {
+#if defined(__CUDA_ARCH__)
+    atomicMax(p, v);
+#else
+    if (v > *p)
+        *p = v;
+#endif
+}
 
 // warp-level votes over the lanes in `mask` (the lanes that run a task side
 // by side); the host emulation runs one task at a time

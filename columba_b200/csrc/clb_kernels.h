@@ -13,6 +13,21 @@ struct WorkerCtr {
     LocalCtr lc;
 };
 
+// longest read of a batch whose offsets live on the device (the host sizes every per-read buffer from it)
+struct MaxLenKernel {
+    const u32* off;
+    u32* out;
+    struct State {
+        u32 m;
+    };
+    CLB_HD void begin(State& s, u32) const { s.m = 0; }
+    CLB_HD void run(State& s, u32 i) const { s.m = tmax(s.m, off[i + 1] - off[i]); }
+    CLB_HD void end(State& s) const {
+        if (s.m)
+            atomMaxU32(out, s.m);
+    }
+};
+
 // stage 0
 struct PrepKernel {
     Batch B;

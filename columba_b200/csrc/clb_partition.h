@@ -471,6 +471,7 @@ CLB_HD void partStart(const IndexView& ix, const DevStrategy& st, const Batch& B
     h.pad = 0;
     if (P >= pSize || P == 1) { // searchstrategy.cpp:141-156: no partitioning possible
         atomOr(B.err, ERR_SHORT_READ);
+        B.readStatus[t >> 1] = 1; // both strands write the same value
         B.parts.hdr[t] = h;
         return;
     }

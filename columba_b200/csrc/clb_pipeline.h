@@ -92,6 +92,8 @@ template <typename BE> struct MapResult {
     HostBuf<BE, OutOcc> occ;
     HostBuf<BE, u16> cig; // occ.size() x cigW
     HostBuf<BE, u32> outStart, outCount; // per read
+    HostBuf<BE, u8> readStatus;          // per read
+    u32 nShort = 0;
     u32 cigW = 0;
     u64 counters[N_COUNTERS];
     u64 stats[N_STATS];
@@ -101,6 +103,7 @@ template <typename BE> struct MapResult {
         cig.release(be);
         outStart.release(be);
         outCount.release(be);
+        readStatus.release(be);
     }
 };
 
@@ -133,6 +136,18 @@ template <typename BE> struct Pipeline {
         u32 fmSlots[2];
         u32 nT, nR; // 2R and R as device-side task counts
     };
+
+    // longest read of a batch whose offsets are on the device
+    u32 maxReadLen(const u32* dOff, u32 R) {
+        bMisc.ensure(be, sizeof(Misc));
+        be.zero(bMisc.p, sizeof(Misc));
+        Misc* M = (Misc*)bMisc.p;
+        MaxLenKernel k{dOff, &M->nT};
+        be.launch(k, R, nullptr, WK_LIGHT);
+        u32 v = 0;
+        be.d2h(&v, &M->nT, sizeof(u32));
+        return v;
+    }
 
     void uploadStrategy(const DevStrategy& st) {
         bStrategy.ensure(be, sizeof(DevStrategy));
@@ -245,10 +260,11 @@ template <typename BE> struct Pipeline {
         B.err = &M->err;
         // per-group arrays: 2 x (G+1)
         const size_t pr = (size_t)(G + 1);
-        bPerRead.ensure(be, pr * 2 * 4);
-        be.zero(bPerRead.p, pr * 2 * 4);
+        bPerRead.ensure(be, pr * 2 * 4 + R + 16);
+        be.zero(bPerRead.p, pr * 2 * 4 + R + 16);
         B.outCount = (u32*)bPerRead.p;
         B.outStart = B.outCount + pr;
+        B.readStatus = (u8*)(B.outStart + pr);
         // sort buffers of stages 4-6: two (u64 key, u32 value) arrays of capSort + 2 entries each
         const size_t capSort = (size_t)tmax(capFm, capTx) + 2;
         u32 groupBits = 1;
@@ -446,9 +462,18 @@ template <typename BE> struct Pipeline {
                     be.d2hAsync(res->occ.data(), bOut.p, (size_t)n * sizeof(OutOcc));
                     be.d2hAsync(res->cig.data(), bOutCig.p, (size_t)n * B.cigW * 2);
                 }
+                res->readStatus.resize(be, R);
+                res->nShort = 0;
+                if (err & ERR_SHORT_READ)
+                    be.d2hAsync(res->readStatus.data(), B.readStatus, R);
+                else
+                    memset(res->readStatus.data(), 0, R);
                 be.d2hAsync(res->outStart.data(), B.outStart, (size_t)G * 4);
                 be.d2hAsync(res->outCount.data(), B.outCount, (size_t)G * 4);
                 be.sync();
+                if (err & ERR_SHORT_READ)
+                    for (u32 i = 0; i < R; i++)
+                        res->nShort += res->readStatus.data()[i] != 0;
             }
         }
         return err;

@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define CLB_ABI_VERSION 3
+#define CLB_ABI_VERSION 4
 
 enum {
     CLB_OK = 0,
@@ -88,6 +88,10 @@ typedef struct clb_result {
     uint32_t cigar_stride;
     const uint32_t* read_start;   /* n_groups */
     const uint32_t* read_count;   /* n_groups : hit counts */
+    const uint8_t* read_status;   /* n_reads : 0 = mapped as asked; 1 = the read is not longer than the number of
+                                     parts of the search scheme: the reference falls back to naive backtracking
+                                     (src/searchstrategy.cpp:442-459), this library reports no hits for it */
+    uint32_t n_short_reads;       /* number of reads with read_status 1 */
     uint64_t counters[CLB_N_COUNTERS];
     uint64_t stats[CLB_N_STATS];
     float stage_ms[CLB_N_STAGES]; /* device time per stage (CUDA events) */

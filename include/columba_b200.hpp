@@ -125,8 +125,7 @@ class SearchStrategy {
         clb_result r;
         int rc = clb_map_batch(ctx, (const uint8_t*)cat.data(), off.data(), (uint32_t)reads.size(), (int)maxED,
                                (int)minED, &r);
-        if (rc && !(rc == CLB_E_UNSUPPORTED && r.n_reads == reads.size())) // reads too short for the scheme are skipped
-            check(rc);
+        check(rc); // reads too short for the scheme are skipped (clb_result::read_status), not an error
         groups.assign(r.n_groups, {});
         for (uint32_t g = 0; g < r.n_groups; g++)
             for (uint32_t j = r.read_start[g]; j < r.read_start[g] + r.read_count[g]; j++) {

@@ -108,11 +108,21 @@ def test_error_conventions(emu_indexes, hostemu_lib, tmp_path):
     reads, off = cb.Mapper.pack(["ACGT" * 30])
     with pytest.raises(cb.ClbError):
         m.map_batch(reads, off, 5)
-    # a read shorter than the number of parts is reported, not silently dropped
-    reads, off = cb.Mapper.pack(["ACG", "ACGT" * 30])
-    with pytest.raises(cb.ClbError) as e:
-        m.map_batch(reads, off, 4)
-    assert e.value.code == -4
+    # reads not longer than the number of parts (the reference falls back to naive backtracking for them) and
+    # empty reads are flagged per read; the other reads of the batch keep their results
+    names, seqs = gu.read_fastq_gz(os.path.join(gu.GOLD, "g1_edit.fq.gz"))
+    sub = seqs[:40]
+    mixed = sub[:10] + ["ACG"] + sub[10:20] + [""] + sub[20:] + ["ACGTA"]
+    reads, off = cb.Mapper.pack(mixed)
+    res = m.map_batch(reads, off, 4)
+    assert res.n_short_reads == 3 and list(np.flatnonzero(res.read_status)) == [10, 21, 42]
+    assert res.read_count[10] == 0 and res.read_count[21] == 0 and res.read_count[42] == 0
+    ref = m.map_batch(*cb.Mapper.pack(sub), 4)
+    keep = [i for i in range(len(mixed)) if i not in (10, 21, 42)]
+    assert [int(res.read_count[i]) for i in keep] == [int(c) for c in ref.read_count]
+    a = np.concatenate([res.occ[int(res.read_start[i]):int(res.read_start[i]) + int(res.read_count[i])] for i in keep])
+    for f in ("seq_id", "pos", "end", "strand", "dist"):
+        assert (a[f] == ref.occ[f]).all()
     m.close()
 
 
@@ -123,7 +133,7 @@ def test_cuda_library_exports_the_whole_abi(cuda_lib):
     lib = cb.load_library(cuda_lib)
     for name in declared:
         assert hasattr(lib, name), name
-    assert lib.clb_abi_version() == 3
+    assert lib.clb_abi_version() == 4
 
 
 def test_product_has_no_cpu_fallback(cuda_lib, golden_index):
