@@ -152,10 +152,12 @@ __global__ void __launch_bounds__(128) clb_kernel_warp(const K k, u32 nMax, cons
         u32 v = *nDev;
         n = v < nMax ? v : nMax;
     }
+    extern __shared__ __align__(16) u8 clb_smem[];
     const u32 warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const u32 lane = threadIdx.x & 31;
     typename K::State st;
     k.begin(st, warp);
+    bindSharedOf(k, st, clb_smem, 0);
     for (;;) {
         u32 i = 0;
         if (lane == 0)

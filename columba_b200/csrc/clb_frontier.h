@@ -208,11 +208,18 @@ template <typename W, int GS> struct Frontier {
     FGroup grp[MAXP];
     u32 nGroups;
     LV<FCounters> ctr;
+    // on-chip copy of the frontier (warp groups on the GPU): the first fcCap nodes of the level that is being
+    // expanded are read from fc[level & 1], the first fcCap children go to fc[(level + 1) & 1] as well as to the
+    // node array in HBM (which the ranking and the cluster walks use later), so that the only HBM round trip on
+    // the critical path of a level is the pair of rank lookups
+    Node* fc[2];
+    u32 fcCap;
 
     CLB_HD Frontier(const IndexView& ix_, const Batch& B_, const DevSearch& s_, const PartInfo& pi_, u32 t_, u32 si,
                     u8* scr_, u32 cap_)
         : ix(ix_), B(B_), s(s_), pi(pi_), t(t_), searchIdx(si), scr(scr_), cap(cap_), top(0), err(0),
-          edit(B_.metric == METRIC_EDIT), nGroups(0) {
+          edit(B_.metric == METRIC_EDIT), nGroups(0), fcCap(0) {
+        fc[0] = fc[1] = (Node*)0;
         CLB_LANES_G(l, GS) {
             ctr[l].nodes = 0;
             ctr[l].lookups = 0;
@@ -362,7 +369,7 @@ template <typename W, int GS> struct Frontier {
                     const u32 i = base + (u32)l;
                     if (i >= b1)
                         continue;
-                    const Node x = nodes[i];
+                    const Node x = (level > 0 && i - b0 < fcCap) ? fc[level & 1u][i - b0] : nodes[i];
                     if (x.kind() != FK_ALIVE)
                         continue;
                     const FPI& P = pisOf(G)[x.pi];
@@ -484,8 +491,12 @@ template <typename W, int GS> struct Frontier {
                     CLB_LANES_G(l, GS) {
 #pragma unroll
                         for (u32 q = 0; q < 4; q++)
-                            if (q < nKids[l])
-                                nodes[outBase + off[l] + q] = kid[q][l];
+                            if (q < nKids[l]) {
+                                const u32 at = outBase + off[l] + q;
+                                nodes[at] = kid[q][l];
+                                if (at - b1 < fcCap)
+                                    fc[(level + 1u) & 1u][at - b1] = kid[q][l];
+                            }
                     }
                     outBase += total;
                 }

@@ -116,8 +116,16 @@ template <typename W, int GS> struct FrontierKernel {
         LV<u64> started, immediate;
         u64 tasks;
         u8* scr;
+        u8* fc; // on-chip frontier buffers of this warp (null: none)
     };
+    // warp groups on the GPU keep the frontier of the level under expansion in shared memory
+    static const u32 kFcNodes = 12288 / (2 * sizeof(FNode<W>)); // two buffers in 12 KB per warp
+    CLB_HD size_t smemBytes(u32 nThreads) const { return GS == 32 ? (size_t)(nThreads / 32) * 2 * kFcNodes * sizeof(FNode<W>) : 0; }
+    CLB_HD void bindShared(State& s, u8* smem, u32 tid, u32) const {
+        s.fc = GS == 32 ? smem + (size_t)(tid / 32) * 2 * kFcNodes * sizeof(FNode<W>) : (u8*)0;
+    }
     CLB_HD void begin(State& s, u32 warp) const {
+        s.fc = (u8*)0;
         CLB_LANES_G(l, GS) {
             s.ctr[l].nodes = s.ctr[l].lookups = s.ctr[l].rows = s.ctr[l].fmOccs = 0;
             s.started[l] = 0;
@@ -132,6 +140,11 @@ template <typename W, int GS> struct FrontierKernel {
         const PartInfo pi = B.parts.load(task.t, st->P);
         const DevSearch& se = st->sc[pi.scheme].s[task.search];
         Frontier<W, GS> F(ix, B, se, pi, task.t, task.search, s.scr, (u32)slabBytes);
+        if (s.fc) {
+            F.fc[0] = (FNode<W>*)s.fc;
+            F.fc[1] = F.fc[0] + kFcNodes;
+            F.fcCap = kFcNodes;
+        }
         LV<u64> started, immediate;
         CLB_LANES_G(l, GS) {
             started[l] = 0;
