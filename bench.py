@@ -43,6 +43,7 @@ sys.path.insert(0, os.path.join(ROOT, "tools"))
 REF_BIN = os.path.join(ROOT, "oracle", "_ref", "columba")
 BUILDER = os.path.join(ROOT, "columba_b200", "bin", "clb_gpu_build")
 METRIC_NAME = "reads/sec (150bp, k=4 edit, ALL) on 3.1 Gbp ref"
+METRIC_NAME_C5 = "reads/sec (250bp, k=5 Hamming, ALL, custom pigeon scheme) on 3.1 Gbp ref"
 
 
 def env_int(name, default):
@@ -88,7 +89,8 @@ class RefText:
 
 def make_reads(args, ref, rank, batch):
     import gen_data
-    return gen_data.gen_reads_cat(ref.cat, ref.starts, args.reads, 150, args.read_seed + 1000 * batch + rank, "edit",
+    return gen_data.gen_reads_cat(ref.cat, ref.starts, args.reads, args.read_len,
+                                  (250 if args.config == 5 else args.read_seed) + 1000 * batch + rank, args.metric,
                                   args.k, over_e=args.k + 2)
 
 
@@ -156,17 +158,20 @@ def write_fastq_matrix(path, reads, first=0):
                              for i in range(len(blk))))
 
 
+REF_EXTRA = []  # extra command-line arguments of the reference for the selected config
+
+
 def run_reference_cpu(base, reads, k, threads, out_dir, tag="s"):
     """The reference's own CPU implementation (oracle/_ref/columba, compiled from the unmodified sources) on
     `reads`; returns (reads/s, mapping seconds from its own log, kind)."""
     n = len(reads)
     if os.path.exists(REF_BIN):
-        fq = os.path.join(out_dir, "sample_%s_%d.fq" % (tag, n))
+        fq = os.path.join(out_dir, "sample_%s_%d_%d.fq" % (tag, n, reads.shape[1]))
         if not os.path.exists(fq):
             write_fastq_matrix(fq, reads)
         shm = "/dev/shm" if os.path.isdir("/dev/shm") else out_dir
         sam = os.path.join(shm, "clb_ref_out_%d.sam" % os.getpid())
-        cmd = [REF_BIN, "-r", base, "-f", fq, "-a", "all", "-e", str(k), "-t", str(threads), "-o", sam]
+        cmd = [REF_BIN, "-r", base, "-f", fq, "-a", "all", "-e", str(k), "-t", str(threads), "-o", sam] + REF_EXTRA
         p = subprocess.run(cmd, capture_output=True, text=True)
         if os.path.exists(sam):
             os.unlink(sam)
@@ -223,7 +228,12 @@ def main():
     ap.add_argument("--profile", default="human", choices=["human", "ecoli", "none"])
     ap.add_argument("--ref-seed", type=int, default=3100)
     ap.add_argument("--read-seed", type=int, default=150)
-    ap.add_argument("--k", type=int, default=4)
+    ap.add_argument("--k", type=int, default=None, help="maximal distance (default: 4, or 5 with --config 5)")
+    ap.add_argument("--config", type=int, default=3, choices=[3, 5],
+                    help="BASELINE.json configs[] entry (1-based as SURVEY.md counts them): 3 = the metric's workload "
+                         "(150 bp, edit distance k=4, ALL); 5 = 250 bp reads, Hamming distance k=5, custom pigeon scheme "
+                         "of the reference's search_schemes/ (or --scheme-dir), dynamic partitioning")
+    ap.add_argument("--scheme-dir", default=None, help="config 5: search scheme directory (-c DIR of the reference)")
     ap.add_argument("--batches", type=int, default=2, help="distinct read batches the steps rotate through")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="mapping time the cpu_baseline sample is sized for")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -231,13 +241,30 @@ def main():
     ap.add_argument("--host-threads", type=int, default=2, help="host threads (one context each) of the e2e leg")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    hamming = args.config == 5
+    if args.k is None:
+        args.k = 5 if hamming else 4
+    args.read_len = 250 if hamming else 150
+    args.metric = "hamming" if hamming else "edit"
+    if hamming and not args.scheme_dir:
+        args.scheme_dir = os.path.join(ROOT, "tests", "golden", "schemes", "ref", "pigeon")
+    if hamming and not args.scheme_dir.endswith("/"):
+        args.scheme_dir += "/"
 
     rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
-    config = {"workload": "configs[2]: synthetic %.2f Gbp GRCh38-sized reference (%s repeat profile, seed %d), %d SE "
-                          "150 bp reads per step per GPU, edit distance k=%d, ALL mode, dynamic scheme selection, "
-                          "dynamic partitioning" % (args.ref_bp / 1e9, args.profile, args.ref_seed, args.reads, args.k),
+    if hamming:
+        REF_EXTRA.extend(["-m", "hamming", "-c", args.scheme_dir, "-p", "dynamic"])
+    config = {"workload": ("configs[4]: synthetic %.2f Gbp GRCh38-sized reference (%s repeat profile, seed %d), %d SE "
+                           "250 bp reads per step per GPU, Hamming distance k=%d, ALL mode, custom scheme %s, "
+                           "dynamic partitioning" % (args.ref_bp / 1e9, args.profile, args.ref_seed, args.reads, args.k,
+                                                     os.path.basename(args.scheme_dir.rstrip("/")))) if hamming else
+                          ("configs[2]: synthetic %.2f Gbp GRCh38-sized reference (%s repeat profile, seed %d), %d SE "
+                           "150 bp reads per step per GPU, edit distance k=%d, ALL mode, dynamic scheme selection, "
+                           "dynamic partitioning" % (args.ref_bp / 1e9, args.profile, args.ref_seed, args.reads, args.k)),
               "ref_bp": args.ref_bp, "repeat_profile": args.profile, "reads_per_step_per_gpu": args.reads,
-              "read_len": 150, "k": args.k, "mode": "ALL", "scheme": "columba (dynamic selection)",
+              "read_len": args.read_len, "k": args.k, "mode": "ALL",
+              "scheme": ("custom (dynamic selection): " + args.scheme_dir) if hamming else "columba (dynamic selection)",
+              "distance": args.metric,
               "partitioning": "dynamic", "in_text_switch": 4, "sa_sparseness": 4, "kmer": 10,
               "l2": "the index (about 2.5 B per reference base in HBM) exceeds the 126 MB L2 for any ref_bp above "
                     "50 Mbp; inputs per step (150 B per read) exceed it from 840 k reads on",
@@ -265,7 +292,7 @@ def main():
         sample = "first %d reads of the first batch per step, all %d host threads (%s), mapping time from the " \
                  "reference's own log line (it includes FASTQ parsing and SAM formatting/writing to /dev/shm, which " \
                  "the GPU arm's e2e does not)" % (n, threads, cpu_model())
-        line = {"impl": "reference", "metric": METRIC_NAME, "value": val, "unit": "reads/s", "n_gpus": args.gpus,
+        line = {"impl": "reference", "metric": METRIC_NAME_C5 if hamming else METRIC_NAME, "value": val, "unit": "reads/s", "n_gpus": args.gpus,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic", "config": config,
                 "cpu_baseline": {"value": val, "unit": "reads/s", "cores": threads if kind == "reference" else 1,
@@ -308,7 +335,8 @@ def main():
     n, L = batches[0].shape
     off = (np.arange(n + 1, dtype=np.int64) * L).astype(np.uint32)
 
-    m = cb.Mapper(ix)
+    mapper_args = ((("custom_dynamic", args.scheme_dir.rstrip("/")), "hamming", "dynamic") if hamming else ())
+    m = cb.Mapper(ix, *mapper_args)
     stream = torch.cuda.current_stream()
     m.set_stream(stream.cuda_stream)
     h_reads = [torch.from_numpy(b.reshape(-1)).pin_memory() for b in batches]
@@ -361,7 +389,7 @@ def main():
     # context overlap the kernels of the other.  Every step still moves its reads host->device and its
     # occurrences device->host inside the timed region.
     n_thr = max(1, min(args.host_threads, args.steps))
-    mappers = [m] + [cb.Mapper(ix) for _ in range(n_thr - 1)]
+    mappers = [m] + [cb.Mapper(ix, *mapper_args) for _ in range(n_thr - 1)]
     m.set_stream(None)  # every context on its own stream
 
     def host_call(mp, b):
@@ -468,7 +496,7 @@ def main():
             dist.destroy_process_group()
         return
     R_total = world * n * args.steps
-    line = {"metric": METRIC_NAME, "value": value, "unit": "reads/s", "n_gpus": world, "steps": args.steps,
+    line = {"metric": METRIC_NAME_C5 if hamming else METRIC_NAME, "value": value, "unit": "reads/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u64", "data": "synthetic", "config": config,
             "e2e": {"value": e2e_val, "unit": "reads/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,

@@ -6,6 +6,7 @@
 #include <cuda_runtime.h>
 
 #include <cstdio>
+#include <cstdlib>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -145,8 +146,8 @@ template <class K> constexpr bool isStepped(long) { return false; }
 
 // Warp-task functors (K::kWarpTask): a task is run by all 32 lanes of a warp
 // together (K::runWarp); warps claim tasks one at a time from a global counter.
-template <class K>
-__global__ void __launch_bounds__(128) clb_kernel_warp(const K k, u32 nMax, const u32* __restrict__ nDev, u32* workCtr) {
+template <class K, int MINB>
+__global__ void __launch_bounds__(128, MINB) clb_kernel_warp(const K k, u32 nMax, const u32* __restrict__ nDev, u32* workCtr) {
     u32 n = nMax;
     if (nDev) {
         u32 v = *nDev;
@@ -481,6 +482,10 @@ struct CudaBackend {
         CLB_CUDA(cudaDeviceGetAttribute(&numSMs, cudaDevAttrMultiProcessorCount, dev));
         CLB_CUDA(cudaStreamCreateWithFlags(&ownStream, cudaStreamNonBlocking));
         stream = ownStream;
+        if (const char* e = getenv("COLUMBA_B200_SEARCH_OCC"))
+            warpOcc = atoi(e) == 8 ? 8 : 4;
+        if (const char* e = getenv("COLUMBA_B200_FRONTIER_SMEM"))
+            fcBytesEnv = atoi(e);
         CLB_CUDA(cudaMalloc(&workCtrs, N_CTRS * sizeof(u32)));
         CLB_CUDA(cudaEventCreate(&evBegin));
         CLB_CUDA(cudaEventCreate(&evEnd));
@@ -566,7 +571,7 @@ struct CudaBackend {
     void copyWait(u32 slice) { CLB_CUDA(cudaStreamWaitEvent(stream, evCopy[slice], 0)); }
     u32 blocksFor(int kind) const {
         switch (kind) {
-        case WK_SEARCH: return (u32)numSMs * 4;   // x128 threads: 16 warps per SM, one task per warp
+        case WK_SEARCH: return (u32)numSMs * (warpOcc == 8 ? 8u : 4u); // x128 threads, one task per warp
         case WK_SEARCH_HEAVY: return (u32)numSMs * HEAVY_CTAS_PER_SM; // CTAs of HEAVY_GROUP threads, with large scratch
         case WK_VERIFY: return (u32)numSMs * 8;
         case WK_FILTER: return (u32)numSMs * 4;
@@ -574,6 +579,11 @@ struct CudaBackend {
         }
     }
     static const int kHeavyGroup = HEAVY_GROUP; // lanes per heavy search task
+    // Resident CTAs per SM of the warp-per-task search launch: 4 (126 registers per thread, 12 KB of frontier
+    // buffers per warp) or, with COLUMBA_B200_SEARCH_OCC=8, 8 (64 registers, 6 KB per warp)
+    int warpOcc = 4;
+    int fcBytesEnv = -1; // COLUMBA_B200_FRONTIER_SMEM: bytes of frontier buffers per warp (-1: default)
+    u32 frontierCacheBytes() const { return fcBytesEnv >= 0 ? (u32)fcBytesEnv : (warpOcc == 8 ? 6144u : 12288u); }
     u32 workers(int kind) { return blocksFor(kind) * (kind == WK_SEARCH_HEAVY ? (u32)HEAVY_GROUP : 128u); }
     u32 laneStride() const { return 32; }
     u32 fallbackWorkers() const { return 0; }
@@ -590,7 +600,7 @@ struct CudaBackend {
             launches++;
             return;
         } else if constexpr (isWarpTask<K>(0))
-            fn = clb_kernel_warp<K>;
+            fn = warpOcc == 8 ? clb_kernel_warp<K, 8> : clb_kernel_warp<K, 4>;
         else if constexpr (isStepped<K>(0))
             fn = clb_kernel_stepped<K>;
         else

@@ -118,11 +118,13 @@ template <typename W, int GS> struct FrontierKernel {
         u8* scr;
         u8* fc; // on-chip frontier buffers of this warp (null: none)
     };
-    // warp groups on the GPU keep the frontier of the level under expansion in shared memory
-    static const u32 kFcNodes = 12288 / (2 * sizeof(FNode<W>)); // two buffers in 12 KB per warp
-    CLB_HD size_t smemBytes(u32 nThreads) const { return GS == 32 ? (size_t)(nThreads / 32) * 2 * kFcNodes * sizeof(FNode<W>) : 0; }
+    // warp groups on the GPU keep the frontier of the level under expansion in shared memory:
+    // two buffers of fcNodes records per warp (fcBytes = the backend's budget per warp)
+    u32 fcBytes;
+    CLB_HD u32 fcNodes() const { return GS == 32 ? fcBytes / (2u * (u32)sizeof(FNode<W>)) : 0u; }
+    CLB_HD size_t smemBytes(u32 nThreads) const { return (size_t)(nThreads / 32) * 2 * fcNodes() * sizeof(FNode<W>); }
     CLB_HD void bindShared(State& s, u8* smem, u32 tid, u32) const {
-        s.fc = GS == 32 ? smem + (size_t)(tid / 32) * 2 * kFcNodes * sizeof(FNode<W>) : (u8*)0;
+        s.fc = fcNodes() ? smem + (size_t)(tid / 32) * 2 * fcNodes() * sizeof(FNode<W>) : (u8*)0;
     }
     CLB_HD void begin(State& s, u32 warp) const {
         s.fc = (u8*)0;
@@ -142,8 +144,8 @@ template <typename W, int GS> struct FrontierKernel {
         Frontier<W, GS> F(ix, B, se, pi, task.t, task.search, s.scr, (u32)slabBytes);
         if (s.fc) {
             F.fc[0] = (FNode<W>*)s.fc;
-            F.fc[1] = F.fc[0] + kFcNodes;
-            F.fcCap = kFcNodes;
+            F.fc[1] = F.fc[0] + fcNodes();
+            F.fcCap = fcNodes();
         }
         LV<u64> started, immediate;
         CLB_LANES_G(l, GS) {

@@ -340,14 +340,14 @@ template <typename BE> struct Pipeline {
             const u32 nHeavyGroups = tmax<u32>(1u, be.workers(WK_SEARCH_HEAVY) / ((u32)BE::kHeavyGroup / 32u * be.laneStride()));
             bSlabSearch.ensure(be, tmax<size_t>(sb * nWarps, hb * nHeavyGroups));
             if (wide) {
-                FrontierKernel<u128, 32> k2{ix, dst, B, (u8*)bSlabSearch.p, sb, 0};
+                FrontierKernel<u128, 32> k2{ix, dst, B, (u8*)bSlabSearch.p, sb, 0, be.frontierCacheBytes()};
                 be.launch(k2, capTasks, &M->nTasks, WK_SEARCH);
-                FrontierKernel<u128, BE::kHeavyGroup> k2h{ix, dst, B, (u8*)bSlabSearch.p, hb, 1};
+                FrontierKernel<u128, BE::kHeavyGroup> k2h{ix, dst, B, (u8*)bSlabSearch.p, hb, 1, 0};
                 be.launch(k2h, capTasks, &M->nHeavy, WK_SEARCH_HEAVY);
             } else {
-                FrontierKernel<u64, 32> k2{ix, dst, B, (u8*)bSlabSearch.p, sb, 0};
+                FrontierKernel<u64, 32> k2{ix, dst, B, (u8*)bSlabSearch.p, sb, 0, be.frontierCacheBytes()};
                 be.launch(k2, capTasks, &M->nTasks, WK_SEARCH);
-                FrontierKernel<u64, BE::kHeavyGroup> k2h{ix, dst, B, (u8*)bSlabSearch.p, hb, 1};
+                FrontierKernel<u64, BE::kHeavyGroup> k2h{ix, dst, B, (u8*)bSlabSearch.p, hb, 1, 0};
                 be.launch(k2h, capTasks, &M->nHeavy, WK_SEARCH_HEAVY);
             }
             be.mark(STG_SEARCH);

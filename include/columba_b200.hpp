@@ -20,6 +20,7 @@
 #ifndef COLUMBA_B200_HPP
 #define COLUMBA_B200_HPP
 #include <algorithm>
+#include <cmath>
 #include <cstdint>
 #include <stdexcept>
 #include <string>
@@ -53,6 +54,48 @@ struct TextOcc {
     uint32_t distanceBeforeTrimming = 0; // the distance the occurrence was found with (== distance unless trimmed)
     std::string cigar;       // "*" when CIGARs are switched off
 };
+
+// The SAM records the reference writes for one single-end read (ALL mode): generateOutputSingleEnd
+// src/searchstrategy.cpp:1824-1902 (stable sort on the distance: the first occurrence is the primary one),
+// generateSE_SAM src/searchstrategy.h:1633-1641, TextOcc::generateSAMSingleEnd src/indexhelpers.cpp:56-87, flags
+// getFlagsSE src/indexhelpers.h:321-331, MAPQ getMapQ :378-388, unmapped record createUnmappedSAMOccurrenceSE.
+// Sequence and quality are printed on the primary record only (reverse-complemented / reversed on the reverse strand).
+inline void samSingleEnd(const std::string& name, const std::string& seq, const std::string& qual, std::vector<TextOcc> occs,
+                         const std::vector<std::string>& seqNames, std::string& out, bool unmappedRecord = true) {
+    const std::string q = qual.empty() ? "*" : qual;
+    if (occs.empty()) {
+        if (unmappedRecord)
+            out += name + "\t4\t*\t0\t0\t*\t*\t0\t0\t" + seq + "\t" + q + "\tPG:Z:Columba\n";
+        return;
+    }
+    std::stable_sort(occs.begin(), occs.end(), [](const TextOcc& a, const TextOcc& b) { return a.distance < b.distance; });
+    const uint32_t minScore = occs.front().distance;
+    uint32_t nHits = 0;
+    for (const auto& t : occs)
+        nHits += t.distance == minScore;
+    for (size_t i = 0; i < occs.size(); i++) {
+        const TextOcc& t = occs[i];
+        const bool rc = t.strand == REVERSE_C_STRAND;
+        std::string s = "*", ql = "*";
+        if (i == 0) {
+            s = seq;
+            ql = q;
+            if (rc) {
+                std::reverse(s.begin(), s.end());
+                for (auto& c : s)
+                    c = c == 'A' ? 'T' : c == 'C' ? 'G' : c == 'G' ? 'C' : c == 'T' ? 'A' : c;
+                if (ql != "*")
+                    std::reverse(ql.begin(), ql.end());
+            }
+        }
+        int mapq = 0;
+        if (t.distance == minScore)
+            mapq = nHits == 1 ? 60 : (int)std::lround(-10.0 * std::log10(1.0 - 1.0 / nHits));
+        out += name + "\t" + std::to_string((rc ? 16 : 0) | (i ? 256 : 0)) + "\t" + seqNames[t.seqID] + "\t" +
+               std::to_string(t.begin + 1) + "\t" + std::to_string(mapq) + "\t" + t.cigar + "\t*\t0\t0\t" + s + "\t" + ql +
+               "\tAS:i:" + std::to_string(t.distance) + "\tNM:i:" + std::to_string(t.distance) + "\tPG:Z:Columba\n";
+    }
+}
 
 class FMIndex {
   public:

@@ -25,6 +25,8 @@ def build_and_run(lib, base, mode, value, reads="g1_edit", x=0):
             o.write(i.read())
     p = subprocess.run([exe, base, fq, cb.SCHEMES_DIR, mode, str(value), str(x)], capture_output=True, text=True)
     assert p.returncode == 0, p.stderr[-500:]
+    if mode == "sam":
+        return p.stdout.splitlines(keepends=True)
     rows = []
     for line in p.stdout.splitlines():
         a = line.split("\t")
@@ -33,6 +35,9 @@ def build_and_run(lib, base, mode, value, reads="g1_edit", x=0):
 
 
 def all_and_best(lib, golden_index):
+    # SAM body of single-end ALL mode from the C++ layer, byte for byte
+    from test_sam_records import expected_sam
+    assert build_and_run(lib, golden_index, "sam", 4) == expected_sam("edit_k4_columba")
     assert build_and_run(lib, golden_index, "all", 4) == gu.expected("edit_k4_columba")[0]
     assert build_and_run(lib, golden_index, "best", 95) == expected_best("best_I95")
     assert build_and_run(lib, golden_index, "best", 95, x=2) == expected_best("best_I95_x2")

@@ -124,6 +124,66 @@ def test_best_mode_sample_equals_reference(human):
     assert got == exp
 
 
+def test_paired_end_sample_equals_reference(human, cuda_lib):
+    """BASELINE.json configs[3] shape on the 3.1 Gbp index: FR pairs of 2 x 150 bp, fragments ~N(400, 50), BEST mode
+    with minimal identity 95 (and ALL mode k = 2), through the C++ paired-end layer on the CUDA library against
+    `columba_dev -f/-F -nI`: every SAM record (flags, MAPQ, mate fields, TLEN, NM) of every pair."""
+    import time
+
+    import gen_data
+    from test_paired_end import SRC as PE_SRC
+    if not os.path.exists(REF_DEV):
+        pytest.skip("reference binary did not travel")
+    n = 3_000
+    n_text = int(np.fromfile(human["base"] + ".txt.bin", dtype=np.uint32, count=1)[0])
+    cat = np.memmap(human["base"] + ".txt.bin", dtype=np.uint8, mode="r", offset=4, shape=(n_text,))
+    starts = np.fromfile(human["base"] + ".pos", dtype=np.uint32).astype(np.int64)
+    m1, m2 = gen_data.gen_pairs_cat(cat, starts, n, 150, 2150)
+    fq1, fq2 = os.path.join(human["dir"], "pe_1.fq"), os.path.join(human["dir"], "pe_2.fq")
+    gen_data.write_fastq_matrix(fq1, m1)
+    gen_data.write_fastq_matrix(fq2, m2)
+    exe = os.path.join(gu.WORK, "pe_cpp_test_cuda")
+    os.makedirs(gu.WORK, exist_ok=True)
+    libdir = os.path.dirname(cuda_lib)
+    subprocess.check_call(["g++", "-std=c++14", "-O2", "-I", os.path.join(gu.ROOT, "include"), PE_SRC, "-L", libdir,
+                           "-lcolumba_b200", "-Wl,-rpath," + libdir, "-o", exe])
+
+    def records(path):
+        rows = []
+        for line in open(path):
+            if line.startswith("@"):
+                continue
+            f = line.rstrip("\n").split("\t")
+            nm = [x for x in f[11:] if x.startswith("NM:i:")]
+            rows.append((f[0], int(f[1]), f[2], int(f[3]), int(f[4]), f[5], f[6], int(f[7]), int(f[8]),
+                         int(nm[0][5:]) if nm else -1))
+        return sorted(rows)
+
+    for mode, value, ref_args in (("best", 95, ["-a", "best", "-I", "95"]), ("all", 2, ["-a", "all", "-e", "2"])):
+        t0 = time.perf_counter()
+        r = subprocess.run([exe, human["base"], fq1, fq2, cb.SCHEMES_DIR, mode, str(value), "fr", "700", "200", "0", "0"],
+                           capture_output=True, text=True)
+        t_gpu = time.perf_counter() - t0
+        assert r.returncode == 0, r.stderr[-500:]
+        got = []
+        for line in r.stdout.splitlines():
+            a = line.split("\t")
+            got.append((a[0], int(a[1]), a[2], int(a[3]), int(a[4]), a[5], a[6], int(a[7]), int(a[8]), int(a[9])))
+        got.sort()
+        sam = os.path.join(human["dir"], "pe_ref.sam")
+        t0 = time.perf_counter()
+        p = subprocess.run([REF_DEV, "-r", human["base"], "-f", fq1, "-F", fq2, "-nI", "-O", "fr", "-X", "700", "-N", "200",
+                            "-t", str(os.cpu_count() or 1), "-o", sam] + ref_args, capture_output=True, text=True)
+        t_ref = time.perf_counter() - t0
+        assert p.returncode == 0, p.stdout[-400:] + p.stderr[-400:]
+        exp = records(sam)
+        os.unlink(sam)
+        print("paired-end %s: %d pairs, %d records; C++ layer on the GPU %.1f s (incl. index load), reference %.1f s "
+              "(incl. index load)" % (mode, n, len(exp), t_gpu, t_ref))
+        assert len(got) == len(exp), (mode, len(got), len(exp))
+        assert got == exp, mode
+
+
 def test_batch_split_invariance(human):
     """One batch of 100 000 reads == four batches of 25 000 (device-side list growth, re-runs after list
     overflows and the global sort do not depend on how reads are batched)."""

@@ -234,6 +234,37 @@ def gen_reads_cat(cat, starts, n_reads, read_len, seed, metric="edit", max_e=4, 
     return out
 
 
+def gen_pairs_cat(cat, starts, n_pairs, read_len, seed, max_e=3, frag_mean=400, frag_sd=50, frag_min=200, frag_max=700):
+    """FR read pairs (SURVEY.md section 8d, configs[3]): fragments of length ~N(frag_mean, frag_sd) clipped to
+    [frag_min, frag_max] drawn from the concatenated text `cat` (never across a sequence end), mate 1 = the first
+    read_len characters, mate 2 = the reverse complement of the last read_len characters, fragment strand 50/50,
+    0..max_e substitutions per mate.  Returns two uint8 matrices."""
+    rng = np.random.default_rng(seed)
+    starts = np.asarray(starts, dtype=np.int64)
+    lens = np.diff(starts)
+    ok = lens > frag_max + 16
+    prob = np.where(ok, lens, 0).astype(np.float64)
+    prob /= prob.sum()
+    sid = rng.choice(len(lens), size=n_pairs, p=prob)
+    fl = np.clip(rng.normal(frag_mean, frag_sd, n_pairs), frag_min, frag_max).astype(np.int64)
+    p = (rng.random(n_pairs) * (lens[sid] - frag_max - 8)).astype(np.int64) + starts[sid]
+    J = np.arange(read_len, dtype=np.int64)[None, :]
+    a = np.array(cat[p[:, None] + J])
+    b = np.array(cat[(p + fl - read_len)[:, None] + J])
+    b = COMP[b[:, ::-1]]
+    flip = rng.integers(0, 2, n_pairs) == 1  # fragment from the reverse strand: the mates swap roles
+    m1 = np.where(flip[:, None], b, a)
+    m2 = np.where(flip[:, None], a, b)
+    for m in (m1, m2):
+        ne = rng.integers(0, max_e + 1, n_pairs)
+        for e in range(max_e):
+            rows = np.nonzero(ne > e)[0]
+            q = rng.integers(0, read_len, len(rows))
+            cur = np.searchsorted(ACGT, m[rows, q])
+            m[rows, q] = ACGT[(cur + rng.integers(1, 4, len(rows))) % 4]
+    return m1, m2
+
+
 def write_fastq_matrix(path, reads, first=0):
     """FASTQ of a uint8 read matrix; read i is named r<first+i>."""
     n, L = reads.shape
