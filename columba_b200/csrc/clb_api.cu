@@ -178,9 +178,9 @@ template <class K> constexpr int groupOfK(long) { return 32; }
 
 // Group-task functors with K::kGroup > 32: a task is run by all threads of a CTA of K::kGroup threads
 // together (the functor's collectives use __syncthreads); CTAs claim tasks one at a time.
-static const int HEAVY_GROUP = 256, HEAVY_CTAS_PER_SM = 2;
-template <class K>
-__global__ void __launch_bounds__(HEAVY_GROUP, HEAVY_CTAS_PER_SM) clb_kernel_cta(const K k, u32 nMax, const u32* __restrict__ nDev, u32* workCtr) {
+static const int HEAVY_GROUP = 256, HEAVY_THREADS_PER_SM = 512;
+template <class K, int THREADS>
+__global__ void __launch_bounds__(THREADS, HEAVY_THREADS_PER_SM / THREADS) clb_kernel_cta(const K k, u32 nMax, const u32* __restrict__ nDev, u32* workCtr) {
     __shared__ u32 claimed;
     u32 n = nMax;
     if (nDev) {
@@ -486,6 +486,8 @@ struct CudaBackend {
             warpOcc = atoi(e) == 8 ? 8 : 4;
         if (const char* e = getenv("COLUMBA_B200_FRONTIER_SMEM"))
             fcBytesEnv = atoi(e);
+        if (const char* e = getenv("COLUMBA_B200_HEAVY_GROUP"))
+            heavyGroup = atoi(e) == 128 ? 128 : HEAVY_GROUP;
         CLB_CUDA(cudaMalloc(&workCtrs, N_CTRS * sizeof(u32)));
         CLB_CUDA(cudaEventCreate(&evBegin));
         CLB_CUDA(cudaEventCreate(&evEnd));
@@ -572,19 +574,21 @@ struct CudaBackend {
     u32 blocksFor(int kind) const {
         switch (kind) {
         case WK_SEARCH: return (u32)numSMs * (warpOcc == 8 ? 8u : 4u); // x128 threads, one task per warp
-        case WK_SEARCH_HEAVY: return (u32)numSMs * HEAVY_CTAS_PER_SM; // CTAs of HEAVY_GROUP threads, with large scratch
+        case WK_SEARCH_HEAVY: return (u32)numSMs * (u32)(HEAVY_THREADS_PER_SM / heavyGroup); // CTAs of heavyGroup threads
         case WK_VERIFY: return (u32)numSMs * 8;
         case WK_FILTER: return (u32)numSMs * 4;
         default: return (u32)numSMs * 16;
         }
     }
-    static const int kHeavyGroup = HEAVY_GROUP; // lanes per heavy search task
+    static const int kHeavyGroup = HEAVY_GROUP; // lanes per heavy search task (default)
+    int heavyGroup = HEAVY_GROUP;               // COLUMBA_B200_HEAVY_GROUP=128: CTAs of 128 threads, four per SM
+    u32 heavyGroupSize() const { return (u32)heavyGroup; }
     // Resident CTAs per SM of the warp-per-task search launch: 4 (126 registers per thread, 12 KB of frontier
     // buffers per warp) or, with COLUMBA_B200_SEARCH_OCC=8, 8 (64 registers, 6 KB per warp)
     int warpOcc = 4;
     int fcBytesEnv = -1; // COLUMBA_B200_FRONTIER_SMEM: bytes of frontier buffers per warp (-1: default)
     u32 frontierCacheBytes() const { return fcBytesEnv >= 0 ? (u32)fcBytesEnv : (warpOcc == 8 ? 6144u : 12288u); }
-    u32 workers(int kind) { return blocksFor(kind) * (kind == WK_SEARCH_HEAVY ? (u32)HEAVY_GROUP : 128u); }
+    u32 workers(int kind) { return blocksFor(kind) * (kind == WK_SEARCH_HEAVY ? (u32)heavyGroup : 128u); }
     u32 laneStride() const { return 32; }
     u32 fallbackWorkers() const { return 0; }
     template <class K> void launch(const K& k, u32 nMax, const u32* nDev, int kind) {
@@ -592,10 +596,11 @@ struct CudaBackend {
             return;
         void (*fn)(const K, u32, const u32*, u32*);
         if constexpr (isWarpTask<K>(0) && groupOfK<K>(0) > 32) {
-            static_assert(groupOfK<K>(0) == HEAVY_GROUP, "CTA size of the group-task launcher");
+            constexpr int G = groupOfK<K>(0);
+            static_assert(G == 256 || G == 128, "CTA size of the group-task launcher");
             if (nextCtr >= N_CTRS)
                 throw BackendError("work counter pool exhausted");
-            clb_kernel_cta<K><<<blocksFor(kind), HEAVY_GROUP, 0, stream>>>(k, nMax, nDev, workCtrs + nextCtr++);
+            clb_kernel_cta<K, G><<<(u32)numSMs * (u32)(HEAVY_THREADS_PER_SM / G), G, 0, stream>>>(k, nMax, nDev, workCtrs + nextCtr++);
             CLB_CUDA(cudaGetLastError());
             launches++;
             return;

@@ -337,7 +337,7 @@ template <typename BE> struct Pipeline {
             const size_t minSlab = ((size_t)(maxLen + 128) * 4 * (P + 2) + 65536 + 255) & ~(size_t)255;
             const size_t sb = tmax<size_t>(searchSlabBytes, minSlab), hb = tmax<size_t>(heavySlabBytes, sb);
             // heavy tasks: one group of BE::kHeavyGroup lanes (a CTA on the GPU) per task
-            const u32 nHeavyGroups = tmax<u32>(1u, be.workers(WK_SEARCH_HEAVY) / ((u32)BE::kHeavyGroup / 32u * be.laneStride()));
+            const u32 nHeavyGroups = tmax<u32>(1u, be.workers(WK_SEARCH_HEAVY) / (be.heavyGroupSize() / 32u * be.laneStride()));
             bSlabSearch.ensure(be, tmax<size_t>(sb * nWarps, hb * nHeavyGroups));
             if (wide) {
                 FrontierKernel<u128, 32> k2{ix, dst, B, (u8*)bSlabSearch.p, sb, 0, be.frontierCacheBytes()};
@@ -347,8 +347,18 @@ template <typename BE> struct Pipeline {
             } else {
                 FrontierKernel<u64, 32> k2{ix, dst, B, (u8*)bSlabSearch.p, sb, 0, be.frontierCacheBytes()};
                 be.launch(k2, capTasks, &M->nTasks, WK_SEARCH);
-                FrontierKernel<u64, BE::kHeavyGroup> k2h{ix, dst, B, (u8*)bSlabSearch.p, hb, 1, 0};
-                be.launch(k2h, capTasks, &M->nHeavy, WK_SEARCH_HEAVY);
+                bool launched = false;
+                if constexpr (BE::kHeavyGroup > 128) {
+                    if (be.heavyGroupSize() == 128) {
+                        FrontierKernel<u64, 128> k2s{ix, dst, B, (u8*)bSlabSearch.p, hb, 1, 0};
+                        be.launch(k2s, capTasks, &M->nHeavy, WK_SEARCH_HEAVY);
+                        launched = true;
+                    }
+                }
+                if (!launched) {
+                    FrontierKernel<u64, BE::kHeavyGroup> k2h{ix, dst, B, (u8*)bSlabSearch.p, hb, 1, 0};
+                    be.launch(k2h, capTasks, &M->nHeavy, WK_SEARCH_HEAVY);
+                }
             }
             be.mark(STG_SEARCH);
         }

@@ -53,6 +53,7 @@ struct HostEmuBackend {
         launches++;
     }
     static const int kHeavyGroup = 32; // lanes per heavy search task (the emulation always runs groups of 32)
+    u32 heavyGroupSize() const { return 32; }
     u32 frontierCacheBytes() const { return 0; } // no shared memory here
     static u32 sortResult(u32) { return 0; }
     void sortPairs(u64* k0, u32* v0, u64*, u32*, u32 nMax, const u32* nDev, u32) {
