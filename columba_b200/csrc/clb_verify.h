@@ -654,14 +654,35 @@ CLB_HD void verifyHammingTask(const IndexView& ix, const Batch& B, u32 ci, Local
     u32 Te = Tb + pSize;
     if (Te > ix.textLength)
         return;
-    const u8* codes = seqCodes(B, c.t);
+    // 32 characters per round: the read's codes (one byte each, 4 = not ACGT) are packed to the text's
+    // 2-bit layout eight at a time, XOR with the text window, one population count per round
+    const u64* cw = (const u64*)seqCodes(B, c.t); // seqStride is a multiple of 64: whole words are readable
     u32 score = 0;
-    for (u32 j = 0; j < pSize; j++) {
-        u32 p = Tb + j;
-        bool mism = (p == ix.textLength - 1) || textAt(ix, p) != codes[j];
-        score += mism ? 1u : 0u;
-        if (score > c.maxED)
-            break;
+    for (u32 j0 = 0; j0 < pSize && score <= c.maxED; j0 += 32) {
+        const u64 tw = textWindow64(ix, Tb + j0);
+        u64 rd = 0, bad = 0; // read in 2-bit layout; both bits set where the read has no ACGT
+#pragma unroll
+        for (u32 q = 0; q < 4; q++) {
+            const u64 w = cw[j0 / 8 + q];
+            u64 x = w & 0x0303030303030303ull;
+            x = (x | (x >> 6)) & 0x000F000F000F000Full;
+            x = (x | (x >> 12)) & 0x000000FF000000FFull;
+            x = (x | (x >> 24)) & 0xFFFFull;
+            u64 y = (w >> 2) & 0x0101010101010101ull; // code 4
+            y |= y << 1;
+            y = (y | (y >> 6)) & 0x000F000F000F000Full;
+            y = (y | (y >> 12)) & 0x000000FF000000FFull;
+            y = (y | (y >> 24)) & 0xFFFFull;
+            rd |= x << (16 * q);
+            bad |= y << (16 * q);
+        }
+        const u32 nc = tmin<u32>(32u, pSize - j0);
+        const u64 live = nc == 32 ? ~0ull : ((1ull << (2 * nc)) - 1ull);
+        u64 d = (tw ^ rd) | bad;
+        d = (d | (d >> 1)) & 0x5555555555555555ull & live;
+        score += (u32)popc64(d);
+        if (Te == ix.textLength && j0 + nc == pSize && !((d >> (2 * (nc - 1))) & 1ull))
+            score++; // the sentinel at the end of the text matches nothing (fmindex.cpp:386-388)
     }
     if (score <= c.maxED && score >= c.minED) {
         TextOccRec r;
