@@ -93,6 +93,16 @@ struct PairResult {
     std::vector<bool> unpairedPrimary;
 };
 
+// result of the parameter inference (inferPairedEndParameters, src/parallel.cpp:376-465)
+struct PEInference {
+    bool inferred = false;       // false: no pair mapped unambiguously, the given options were kept
+    Orientation orientation = FR;
+    uint32_t maxInsertSize = 500, minInsertSize = 0;
+    float meanInsertSize = 0, stddevInsertSize = 0;
+    size_t pairsProcessed = 0;   // leading pairs that went through the single-end pre-pass
+    size_t unambiguousPairs = 0;
+};
+
 struct PEOptions {
     Orientation orientation = FR;
     uint32_t maxFragSize = 500, minFragSize = 0;
@@ -105,54 +115,99 @@ class PairedEndMapper {
   public:
     explicit PairedEndMapper(SearchStrategy& s) : strategy(s) {}
 
-    // ALL mode (best == false: maxEDOrIdentity = maximal distance) or BEST mode (minimal identity)
+    // ALL mode (best == false: maxEDOrIdentity = maximal distance) or BEST mode (minimal identity) with the given
+    // orientation and fragment bounds (-nI)
     void matchApproxPEBatch(const std::vector<ReadPair>& input, bool best, uint32_t maxEDOrIdentity,
                             const PEOptions& opt, Counters& counters, std::vector<PairResult>& out) {
+        runBatch(input, best, maxEDOrIdentity, opt, counters, out, nullptr, nullptr, nullptr);
+        addPairCounters(out, counters);
+    }
+
+    // The reference's default paired-end flow (inferParametersAndStartWorkers, src/parallel.cpp:880-930): the
+    // leading pairs are mapped single-ended in ALL mode (mate 2 only when mate 1 has exactly one occurrence) until
+    // 750 pairs are mapped unambiguously or 10 000 reads have been given out (the reference stops at the granularity
+    // of its reader's chunks, which depends on timing; here: chunks of `inferChunk` pairs), orientation and
+    // insert-size bounds are inferred from them (median / MAD outlier removal, mean +- 6 sd), those pairs are paired
+    // from their single-end results (pairSingleEnd, src/searchstrategy.h:1433-1463) and the remaining pairs go
+    // through matchApproxPE with the inferred parameters.  All sequences are taken to come from the first reference
+    // file (IndexInterface::isInFirstFile, src/indexinterface.h:622-625).
+    void matchApproxPEInfer(const std::vector<ReadPair>& input, bool best, uint32_t maxEDOrIdentity, PEOptions opt,
+                            Counters& counters, std::vector<PairResult>& out, PEInference& inf, size_t inferChunk = 512) {
         const size_t n = input.size();
-        out.assign(n, PairResult());
-        std::vector<PairContext> ctx(n);
-        std::vector<bool> done(n, false);
-        for (size_t i = 0; i < n; i++) {
-            ctx[i].owner = this;
-            ctx[i].pair = &input[i];
-        }
-        for (int round = 0; round < 200; round++) {
-            bool pending = false;
-            for (size_t i = 0; i < n; i++) {
-                if (done[i])
-                    continue;
-                try {
-                    PairResult r;
-                    if (best)
-                        evalBest(ctx[i], maxEDOrIdentity, opt, r);
-                    else
-                        evalAll(ctx[i], maxEDOrIdentity, opt, r);
-                    out[i] = std::move(r);
-                    done[i] = true;
-                    ctx[i].cache.clear();
-                } catch (const NeedMapping&) {
-                    pending = true;
+        std::vector<std::vector<MateOcc>> se1, se2;
+        std::vector<bool> read2done;
+        std::vector<uint32_t> fragSizes;
+        std::vector<Orientation> orientations;
+        size_t given = 0, unambiguous = 0;
+        while (given < n && unambiguous < 750 && 2 * given < 10000) {
+            const size_t c0 = given, c1 = std::min(n, given + inferChunk);
+            std::vector<std::string> r1;
+            std::vector<uint32_t> k1;
+            for (size_t i = c0; i < c1; i++) {
+                r1.push_back(input[i].read1);
+                k1.push_back(best ? strategy.getMaxED(maxEDOrIdentity, (uint32_t)input[i].read1.size()) : maxEDOrIdentity);
+            }
+            std::vector<std::vector<MateOcc>> m1 = mapSingleEndAll(r1, k1, true, counters);
+            std::vector<std::string> r2;
+            std::vector<uint32_t> k2;
+            std::vector<size_t> who;
+            for (size_t i = c0; i < c1; i++)
+                if (m1[i - c0].size() == 1) { // hasUnambiguousMatchInFirstFile, src/parallel.cpp:229-258
+                    who.push_back(i);
+                    r2.push_back(input[i].read2);
+                    k2.push_back(best ? strategy.getMaxED(maxEDOrIdentity, (uint32_t)input[i].read2.size()) : maxEDOrIdentity);
+                }
+            std::vector<std::vector<MateOcc>> m2 = mapSingleEndAll(r2, k2, false, counters);
+            se1.resize(c1);
+            se2.resize(c1);
+            read2done.resize(c1, false);
+            for (size_t i = c0; i < c1; i++)
+                se1[i] = std::move(m1[i - c0]);
+            for (size_t j = 0; j < who.size(); j++) {
+                const size_t i = who[j];
+                read2done[i] = true;
+                se2[i] = std::move(m2[j]);
+                if (se2[i].size() == 1) { // addFragmentAndOrientation, src/parallel.cpp:327-358
+                    const MateOcc &a = se1[i][0], &b = se2[i][0];
+                    const bool firstFirst = a.indexBegin < b.indexBegin;
+                    fragSizes.push_back(firstFirst ? b.indexEnd() - a.indexBegin : a.indexEnd() - b.indexBegin);
+                    const bool aRc = a.strand == REVERSE_C_STRAND, bRc = b.strand == REVERSE_C_STRAND;
+                    orientations.push_back(aRc == bRc ? FF : (firstFirst == aRc ? RF : FR));
+                    unambiguous++;
                 }
             }
-            if (!pending)
-                break;
-            serveRequests(ctx, best, maxEDOrIdentity, counters);
+            given = c1;
         }
-        for (size_t i = 0; i < n; i++)
-            if (!done[i])
-                throw std::runtime_error("paired-end mapping did not converge");
-        // pair counters, src/fastq.cpp:662-688
-        uint64_t c[CLB_N_COUNTERS] = {};
-        for (const auto& r : out) {
-            const bool mapped = !r.pairs.empty() && r.pairs.front().up.valid && r.pairs.front().down.valid;
-            const bool mappedHalf = !mapped && !r.pairs.empty() && (r.pairs.front().up.valid || r.pairs.front().down.valid);
-            c[CLB_CTR_TOTAL_UNIQUE_PAIRS] += mapped ? r.pairs.size() : 0;
-            c[CLB_CTR_MAPPED_PAIRS] += mapped;
-            c[CLB_CTR_DISCORDANTLY_MAPPED_PAIRS] += mapped && r.pairs.front().discordant;
-            c[CLB_CTR_MAPPED_HALF_PAIRS] += mappedHalf;
-            c[CLB_CTR_UNPAIRED_BUT_MAPPED_PAIRS] += !r.unpaired.empty();
+        inf = PEInference();
+        inf.orientation = opt.orientation;
+        inf.maxInsertSize = opt.maxFragSize;
+        inf.minInsertSize = opt.minFragSize;
+        inf.pairsProcessed = given;
+        inf.unambiguousPairs = unambiguous;
+        inferParameters(fragSizes, orientations, inf);
+        opt.orientation = inf.orientation;
+        opt.maxFragSize = inf.maxInsertSize;
+        opt.minFragSize = inf.minInsertSize;
+        out.assign(n, PairResult());
+        // the pairs of the pre-pass: paired from their single-end results
+        {
+            std::vector<ReadPair> head(input.begin(), input.begin() + given);
+            std::vector<PairResult> res;
+            PEOptions o2 = opt;
+            if (best)
+                o2.x = 0; // pairSingleEndedMatchesBest: x = 0
+            runBatch(head, best, maxEDOrIdentity, o2, counters, res, &se1, &se2, &read2done);
+            for (size_t i = 0; i < given; i++)
+                out[i] = std::move(res[i]);
         }
-        counters.add(c);
+        if (given < n) {
+            std::vector<ReadPair> tail(input.begin() + given, input.end());
+            std::vector<PairResult> res;
+            runBatch(tail, best, maxEDOrIdentity, opt, counters, res, nullptr, nullptr, nullptr);
+            for (size_t i = given; i < n; i++)
+                out[i] = std::move(res[i - given]);
+        }
+        addPairCounters(out, counters);
     }
 
     // the records the reference writes for one pair, in its order (OutputWriter, src/fastq.cpp:690-710)
@@ -196,6 +251,138 @@ class PairedEndMapper {
 
   private:
     struct NeedMapping {};
+    // the replay driver: evaluates every pair, serves the mappings they ask for, evaluates again.  se1 / se2 /
+    // read2done: single-end results of the inference pre-pass (pairSingleEnd), else null.
+    void runBatch(const std::vector<ReadPair>& input, bool best, uint32_t maxEDOrIdentity, const PEOptions& opt,
+                  Counters& counters, std::vector<PairResult>& out, const std::vector<std::vector<MateOcc>>* se1,
+                  const std::vector<std::vector<MateOcc>>* se2, const std::vector<bool>* read2done) {
+        const size_t n = input.size();
+        out.assign(n, PairResult());
+        std::vector<PairContext> ctx(n);
+        std::vector<bool> done(n, false);
+        for (size_t i = 0; i < n; i++) {
+            ctx[i].owner = this;
+            ctx[i].pair = &input[i];
+            if (se1) {
+                ctx[i].se[0] = &(*se1)[i];
+                ctx[i].se[1] = &(*se2)[i];
+                ctx[i].read2done = (*read2done)[i];
+            }
+        }
+        for (int round = 0; round < 200; round++) {
+            bool pending = false;
+            for (size_t i = 0; i < n; i++) {
+                if (done[i])
+                    continue;
+                try {
+                    PairResult r;
+                    if (best)
+                        evalBest(ctx[i], maxEDOrIdentity, opt, r);
+                    else
+                        evalAll(ctx[i], maxEDOrIdentity, opt, r);
+                    out[i] = std::move(r);
+                    done[i] = true;
+                    ctx[i].cache.clear();
+                } catch (const NeedMapping&) {
+                    pending = true;
+                }
+            }
+            if (!pending)
+                break;
+            serveRequests(ctx, best, maxEDOrIdentity, counters);
+        }
+        for (size_t i = 0; i < n; i++)
+            if (!done[i])
+                throw std::runtime_error("paired-end mapping did not converge");
+    }
+    // pair counters, src/fastq.cpp:662-688
+    static void addPairCounters(const std::vector<PairResult>& out, Counters& counters) {
+        uint64_t c[CLB_N_COUNTERS] = {};
+        for (const auto& r : out) {
+            const bool mapped = !r.pairs.empty() && r.pairs.front().up.valid && r.pairs.front().down.valid;
+            const bool mappedHalf = !mapped && !r.pairs.empty() && (r.pairs.front().up.valid || r.pairs.front().down.valid);
+            c[CLB_CTR_TOTAL_UNIQUE_PAIRS] += mapped ? r.pairs.size() : 0;
+            c[CLB_CTR_MAPPED_PAIRS] += mapped;
+            c[CLB_CTR_DISCORDANTLY_MAPPED_PAIRS] += mapped && r.pairs.front().discordant;
+            c[CLB_CTR_MAPPED_HALF_PAIRS] += mappedHalf;
+            c[CLB_CTR_UNPAIRED_BUT_MAPPED_PAIRS] += !r.unpaired.empty();
+        }
+        counters.add(c);
+    }
+    // single-end ALL mode (both strands filtered together, matchApproxAllMap src/searchstrategy.cpp:495-535) for the
+    // inference pre-pass: reads[i] at distance k[i]
+    std::vector<std::vector<MateOcc>> mapSingleEndAll(const std::vector<std::string>& reads, const std::vector<uint32_t>& k,
+                                                      bool first, Counters& counters) {
+        std::vector<std::vector<MateOcc>> out(reads.size());
+        std::map<uint32_t, std::vector<size_t>> byK;
+        for (size_t i = 0; i < reads.size(); i++)
+            byK[k[i]].push_back(i);
+        for (auto& g : byK) {
+            std::vector<std::string> sub;
+            for (size_t i : g.second)
+                sub.push_back(reads[i]);
+            std::vector<std::vector<TextOcc>> res;
+            strategy.mapChunk(sub, g.first, 0, counters, res);
+            for (size_t j = 0; j < g.second.size(); j++)
+                for (auto& t : res[j]) {
+                    MateOcc m;
+                    static_cast<TextOcc&>(m) = t;
+                    m.first = first;
+                    out[g.second[j]].push_back(std::move(m));
+                }
+        }
+        return out;
+    }
+    // inferPairedEndParameters, src/parallel.cpp:376-465
+    static uint32_t calcMedian(std::vector<uint32_t>& d) {
+        std::sort(d.begin(), d.end());
+        return d.size() % 2 == 0 ? (d[d.size() / 2 - 1] + d[d.size() / 2]) / 2 : d[d.size() / 2];
+    }
+    static float average(const std::vector<uint32_t>& v) {
+        double s = 0.0;
+        for (uint32_t x : v)
+            s += x;
+        return (float)(s / v.size());
+    }
+    static float stddev(const std::vector<uint32_t>& v, float mean) {
+        float accum = 0.0f;
+        for (uint32_t x : v) {
+            const float d = (float)x;
+            accum += (d - mean) * (d - mean);
+        }
+        return std::sqrt(accum / (v.size() - 1));
+    }
+    static void inferParameters(std::vector<uint32_t>& fragSizes, const std::vector<Orientation>& orientations, PEInference& inf) {
+        if (fragSizes.empty())
+            return;
+        inf.inferred = true;
+        const int32_t median = (int32_t)calcMedian(fragSizes);
+        std::vector<uint32_t> absDev;
+        for (uint32_t f : fragSizes)
+            absDev.push_back((uint32_t)std::abs((int32_t)f - median));
+        const uint32_t mad = calcMedian(absDev);
+        std::vector<uint32_t> filtered;
+        for (uint32_t f : fragSizes)
+            if ((uint32_t)std::abs((int32_t)f - median) < 6u * mad)
+                filtered.push_back(f);
+        float mean = average(filtered), sd = stddev(filtered, mean);
+        if (mean == 0 || sd == 0) {
+            mean = average(fragSizes);
+            sd = stddev(fragSizes, mean);
+        }
+        inf.meanInsertSize = mean;
+        inf.stddevInsertSize = sd;
+        const uint32_t maxDev = (uint32_t)(6 * sd);
+        inf.maxInsertSize = (uint32_t)(mean + maxDev);
+        inf.minInsertSize = mean > maxDev ? (uint32_t)(mean - maxDev) : 0u;
+        size_t rf = 0, fr = 0, ff = 0;
+        for (Orientation o : orientations) {
+            rf += o == RF;
+            fr += o == FR;
+            ff += o == FF;
+        }
+        inf.orientation = (fr >= rf && fr >= ff) ? FR : (rf >= ff ? RF : FF);
+    }
     typedef std::tuple<int, int, uint32_t, uint32_t> Key; // mate, strand, maximal distance, minimal distance
     struct BoolAndVector {
         bool first = false;
@@ -209,6 +396,8 @@ class PairedEndMapper {
         const ReadPair* pair = nullptr;
         std::map<Key, std::vector<MateOcc>> cache;
         std::set<Key> wanted;
+        const std::vector<MateOcc>* se[2] = {nullptr, nullptr}; // single-end results of the inference pre-pass
+        bool read2done = false;
         const std::string& seq(int mate) const { return mate == 0 ? pair->read1 : pair->read2; }
         // SearchStrategy::mapRead, src/searchstrategy.h:490-517
         std::vector<MateOcc> mapRead(int mate, int strand, uint32_t maxD, uint32_t minD = 0) {
@@ -336,6 +525,13 @@ class PairedEndMapper {
     static std::vector<MateOcc>::iterator findFirstOccAfter(std::vector<MateOcc>& occs, uint32_t position) {
         return std::lower_bound(occs.begin(), occs.end(), position,
                                 [](const MateOcc& o, uint32_t pos) { return o.indexBegin < pos; });
+    }
+    static bool occLess(const MateOcc& a, const MateOcc& b) { // TextOcc::operator<, src/indexhelpers.h:779-798
+        if (a.indexBegin != b.indexBegin)
+            return a.indexBegin < b.indexBegin;
+        if (a.distance != b.distance)
+            return a.distance < b.distance;
+        return (a.end - a.begin) < (b.end - b.begin);
     }
     static PairedTextOccs makePair(const MateOcc& up, const MateOcc& down) {
         PairedTextOccs p;
@@ -468,6 +664,17 @@ class PairedEndMapper {
     }
     void evalAll(PairContext& c, uint32_t maxED, const PEOptions& opt, PairResult& r) {
         BoolAndVector m[2][2]; // [mate][strand]
+        if (c.se[0]) { // pairSingleEndedMatchesAll, src/searchstrategy.cpp:1345-1396: split by strand, sort on position
+            for (int mate = 0; mate < 2; mate++) {
+                for (const MateOcc& o : *c.se[mate])
+                    m[mate][o.strand == REVERSE_C_STRAND ? 1 : 0].second.push_back(o);
+                for (int strand = 0; strand < 2; strand++) {
+                    auto& v = m[mate][strand].second;
+                    std::stable_sort(v.begin(), v.end(), occLess);
+                    m[mate][strand].first = mate == 0 ? true : c.read2done;
+                }
+            }
+        }
         auto lazy = [&](int mate, int strand) -> BoolAndVector& {
             BoolAndVector& v = m[mate][strand];
             if (!v.first) {
@@ -850,6 +1057,18 @@ class PairedEndMapper {
         v[0][1].resize(cutOff1 + 1);
         v[1][0].resize(cutOff2 + 1);
         v[1][1].resize(cutOff2 + 1);
+        if (c.se[0]) { // addSingleEndedForBest, src/searchstrategy.cpp:1065-1089
+            for (int mate = 0; mate < 2; mate++) {
+                for (const MateOcc& o : *c.se[mate]) {
+                    OccVector& ov = v[mate][o.strand == REVERSE_C_STRAND ? 1 : 0];
+                    if (o.distanceBeforeTrimming < ov.size())
+                        ov[o.distanceBeforeTrimming].second.push_back(o);
+                }
+                for (int strand = 0; strand < 2; strand++)
+                    for (auto& bv : v[mate][strand])
+                        bv.first = mate == 0 ? true : c.read2done;
+            }
+        }
         uint32_t minDistNotExplored = 0;
         if (x == 0) {
             processOriBest(c, v, r.pairs, opt, 0, 0);

@@ -1,7 +1,7 @@
 // Test program of the paired-end host layer (include/columba_b200_pe.hpp): maps two FASTQ files as pairs
 // and prints the fields of every SAM record the reference would write.
 //   pe_cpp_test <index base> <fastq 1> <fastq 2> <schemes dir> all <k> | best <min identity>
-//               <fr|rf|ff> <max frag> <min frag> <discordant 0|1> <x>
+//               <fr|rf|ff> <max frag> <min frag> <discordant 0|1> <x> [infer]
 #include <fstream>
 #include <iostream>
 
@@ -43,7 +43,14 @@ int main(int argc, char** argv) {
         clb::PairedEndMapper pe(strategy);
         clb::Counters counters;
         std::vector<clb::PairResult> res;
-        pe.matchApproxPEBatch(pairs, std::string(argv[5]) == "best", (uint32_t)std::stoul(argv[6]), opt, counters, res);
+        const bool infer = argc > 12 && std::string(argv[12]) == "infer";
+        if (infer) {
+            clb::PEInference inf;
+            pe.matchApproxPEInfer(pairs, std::string(argv[5]) == "best", (uint32_t)std::stoul(argv[6]), opt, counters, res, inf);
+            std::cerr << "inferred " << inf.inferred << " orientation " << (inf.orientation == clb::FR ? "FR" : inf.orientation == clb::RF ? "RF" : "FF")
+                      << " min " << inf.minInsertSize << " max " << inf.maxInsertSize << " unambiguous " << inf.unambiguousPairs << "\n";
+        } else
+            pe.matchApproxPEBatch(pairs, std::string(argv[5]) == "best", (uint32_t)std::stoul(argv[6]), opt, counters, res);
         for (size_t i = 0; i < pairs.size(); i++)
             for (const auto& s : pe.samRecords(pairs[i], res[i], index.getSeqNames()))
                 std::cout << s.qname << '\t' << s.flag << '\t' << s.rname << '\t' << s.pos << '\t' << s.mapq << '\t' << s.cigar

@@ -43,6 +43,11 @@ CASES = {
     "pe_best_I95_disc": ("g1", ["-a", "best", "-I", "95", "-D"], dict(mode="best", value=95, ori="fr", max_frag=700, min_frag=200, disc=1, x=0)),
     "pe_best_I97_x1": ("g1", ["-a", "best", "-I", "97", "-x", "1"], dict(mode="best", value=97, ori="fr", max_frag=700, min_frag=200, disc=0, x=1)),
     "pe_best_I95_ff_disc": ("g1", ["-a", "best", "-I", "95", "-O", "ff", "-D"], dict(mode="best", value=95, ori="ff", max_frag=700, min_frag=200, disc=1, x=0)),
+    # parameter inference on (the reference's default): all pairs go through the single-end pre-pass
+    "pe_infer_all_k2": ("g1", ["-a", "all", "-e", "2"], dict(mode="all", value=2, ori="fr", max_frag=500, min_frag=0, disc=0, x=0, infer=1)),
+    "pe_infer_best_I95": ("g1", ["-a", "best", "-I", "95"], dict(mode="best", value=95, ori="fr", max_frag=500, min_frag=0, disc=0, x=0, infer=1)),
+    "pe_infer_best_I95_disc": ("g1", ["-a", "best", "-I", "95", "-D"], dict(mode="best", value=95, ori="fr", max_frag=500, min_frag=0, disc=1, x=0, infer=1)),
+    "pe_g2_infer_all_k2_disc": ("g2", ["-a", "all", "-e", "2", "-D"], dict(mode="all", value=2, ori="fr", max_frag=500, min_frag=0, disc=1, x=0, infer=1)),
     "pe_g2_all_k2": ("g2", ["-a", "all", "-e", "2"], dict(mode="all", value=2, ori="fr", max_frag=700, min_frag=200, disc=0, x=0)),
     "pe_g2_best_I95_disc": ("g2", ["-a", "best", "-I", "95", "-D"], dict(mode="best", value=95, ori="fr", max_frag=700, min_frag=200, disc=1, x=0)),
 }
@@ -157,10 +162,11 @@ def main():
     for name, (g, args, params) in CASES.items():
         sam = os.path.join(tmp, name + ".sam")
         cmd = [os.path.join(REF, "columba_dev"), "-r", os.path.join(tmp, g), "-f", os.path.join(tmp, "pe_%s_1.fq" % g),
-               "-F", os.path.join(tmp, "pe_%s_2.fq" % g), "-nI", "-X", str(params["max_frag"]), "-N",
-               str(params["min_frag"]), "-t", "1", "-v", "-o", sam] + args
-        if "-O" not in args:
-            cmd += ["-O", "fr"]
+               "-F", os.path.join(tmp, "pe_%s_2.fq" % g), "-t", "1", "-v", "-o", sam] + args
+        if not params.get("infer"):
+            cmd += ["-nI", "-X", str(params["max_frag"]), "-N", str(params["min_frag"])]
+            if "-O" not in args:
+                cmd += ["-O", "fr"]
         log = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
         if log.returncode != 0:
             print(log.stdout[-1500:], log.stderr[-1500:])
@@ -175,7 +181,8 @@ def main():
             ctr[key] = int(m.group(1)) if m else None
         json.dump(ctr, open(os.path.join(out, name + ".json"), "w"), sort_keys=True)
         meta[name] = dict(set=g, **params)
-        print(name, len(rows), ctr, flush=True)
+        inf = re.findall(r"(?i)(inferred[^\n]*|orientation[^\n]*|insert size[^\n]*)", log.stdout)
+        print(name, len(rows), ctr, inf[-4:] if params.get("infer") else "", flush=True)
     json.dump(meta, open(os.path.join(HERE, "pe_cases.json"), "w"), indent=1, sort_keys=True)
     shutil.rmtree(tmp)
 

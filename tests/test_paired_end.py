@@ -44,7 +44,8 @@ def run_pe(lib, case):
                 o.write(i.read())
         fqs.append(fq)
     r = subprocess.run([exe, base, fqs[0], fqs[1], cb.SCHEMES_DIR, p["mode"], str(p["value"]), p["ori"],
-                        str(p["max_frag"]), str(p["min_frag"]), str(p["disc"]), str(p["x"])], capture_output=True, text=True)
+                        str(p["max_frag"]), str(p["min_frag"]), str(p["disc"]), str(p["x"])] + (["infer"] if p.get("infer") else []),
+                       capture_output=True, text=True)
     assert r.returncode == 0, r.stderr[-500:]
     rows = []
     for line in r.stdout.splitlines():
