@@ -217,7 +217,19 @@ def sized_cpu_sample(base, reads, k, threads, out_dir, target_s, max_n):
 
 
 # --------------------------------------------------------------------------- main
+def progress(msg):
+    """Phase marks on stderr (stdout carries the one JSON line)."""
+    sys.stderr.write("[bench %7.1f s] %s\n" % (time.perf_counter() - T_START, msg))
+    sys.stderr.flush()
+
+
+T_START = time.perf_counter()
+
+
 def main():
+    if os.environ.get("BENCH_TRACE_AFTER"):  # dump the Python stacks if the run is still going after that many seconds
+        import faulthandler
+        faulthandler.dump_traceback_later(float(os.environ["BENCH_TRACE_AFTER"]), exit=False)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
@@ -326,13 +338,16 @@ def main():
     barrier()
     base = make_reference(args, local)
     t_build = time.perf_counter() - t_build
+    progress("reference + index files ready")
     ref = RefText(base)
     t_load = time.perf_counter()
     ix = cb.Index(base, 4, 10, 4, device=local)
     t_load = time.perf_counter() - t_load
+    progress("index in HBM")
     nb = max(1, args.batches)
     batches = [make_reads(args, ref, rank, b) for b in range(nb)]
     n, L = batches[0].shape
+    progress("read batches generated")
     off = (np.arange(n + 1, dtype=np.int64) * L).astype(np.uint32)
 
     mapper_args = ((("custom_dynamic", args.scheme_dir.rstrip("/")), "hamming", "dynamic") if hamming else ())
@@ -375,6 +390,7 @@ def main():
     # ---- value: inputs resident in HBM
     ms, wall, results, clocks = timed(step_device, args.steps, args.warmup)
     ms_per_step = ms / args.steps
+    progress("device-resident leg done: %.1f ms per step" % ms_per_step)
     value = world * n * args.steps / (ms / 1e3)
     launches = int(sum(r.gpu_launches for r in results))
     stage = {s: float(np.mean([r.stage_ms[s] for r in results])) for s in cb.STAGE_NAMES}
@@ -438,6 +454,7 @@ def main():
         return float(ms.item()), wall, out, clocks
 
     ms2, wall2, results2, clocks2 = timed_host(args.steps, 2)
+    progress("end-to-end leg done: %.1f ms per step" % (ms2 / args.steps))
     n_occ_mean = float(np.mean([r[0] for r in results2]))
     cig_stride = results2[-1][1]
     h2d = int(h_reads[0].numel() + h_off.numel() * 4)
