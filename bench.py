@@ -367,8 +367,11 @@ def main():
         return m.map_batch_device(d_reads[b].data_ptr(), d_off.data_ptr(), n, L, args.k, 0, fetch=False)
 
     def timed(fn, steps, warmup):
-        for _ in range(warmup):
+        for w in range(warmup):
+            t0 = time.perf_counter()
             fn()
+            torch.cuda.synchronize()
+            progress("warm-up step %d: %.2f s" % (w, time.perf_counter() - t0))
         step_no[0] = 0
         barrier()
         clk = ClockSampler(local)

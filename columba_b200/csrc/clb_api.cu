@@ -46,7 +46,9 @@ __device__ __forceinline__ auto runOf(const K& k, S& st, u32 i, unsigned act, in
 template <class K, class S> __device__ __forceinline__ void runOf(const K& k, S& st, u32 i, unsigned, long) { k.run(st, i); }
 
 template <class K>
-__global__ void __launch_bounds__(128) clb_kernel(const K k, u32 nMax, const u32* __restrict__ nDev, u32* workCtr) {
+__global__ void __launch_bounds__(128) clb_kernel(const K k, u32 nMax, const u32* __restrict__ nDev, u32* workCtr, const u32* __restrict__ abortWord) {
+    if (abortWord && (*abortWord & ERR_ABORT_MASK))
+        return; // an earlier stage of this attempt overflowed a list: what follows would read unwritten records
     extern __shared__ __align__(16) u8 clb_smem[];
     u32 n = nMax;
     if (nDev) {
@@ -91,7 +93,9 @@ __global__ void __launch_bounds__(128) clb_kernel(const K k, u32 nMax, const u32
 // lanes keep stepping, so the step loop runs with (almost) full warps even
 // when the tasks differ a lot in their number of steps.
 template <class K>
-__global__ void __launch_bounds__(128) clb_kernel_stepped(const K k, u32 nMax, const u32* __restrict__ nDev, u32* workCtr) {
+__global__ void __launch_bounds__(128) clb_kernel_stepped(const K k, u32 nMax, const u32* __restrict__ nDev, u32* workCtr, const u32* __restrict__ abortWord) {
+    if (abortWord && (*abortWord & ERR_ABORT_MASK))
+        return; // an earlier stage of this attempt overflowed a list: what follows would read unwritten records
     u32 n = nMax;
     if (nDev) {
         u32 v = *nDev;
@@ -147,7 +151,9 @@ template <class K> constexpr bool isStepped(long) { return false; }
 // Warp-task functors (K::kWarpTask): a task is run by all 32 lanes of a warp
 // together (K::runWarp); warps claim tasks one at a time from a global counter.
 template <class K, int MINB>
-__global__ void __launch_bounds__(128, MINB) clb_kernel_warp(const K k, u32 nMax, const u32* __restrict__ nDev, u32* workCtr) {
+__global__ void __launch_bounds__(128, MINB) clb_kernel_warp(const K k, u32 nMax, const u32* __restrict__ nDev, u32* workCtr, const u32* __restrict__ abortWord) {
+    if (abortWord && (*abortWord & ERR_ABORT_MASK))
+        return; // an earlier stage of this attempt overflowed a list: what follows would read unwritten records
     u32 n = nMax;
     if (nDev) {
         u32 v = *nDev;
@@ -180,7 +186,9 @@ template <class K> constexpr int groupOfK(long) { return 32; }
 // together (the functor's collectives use __syncthreads); CTAs claim tasks one at a time.
 static const int HEAVY_GROUP = 256, HEAVY_THREADS_PER_SM = 512;
 template <class K, int THREADS>
-__global__ void __launch_bounds__(THREADS, HEAVY_THREADS_PER_SM / THREADS) clb_kernel_cta(const K k, u32 nMax, const u32* __restrict__ nDev, u32* workCtr) {
+__global__ void __launch_bounds__(THREADS, HEAVY_THREADS_PER_SM / THREADS) clb_kernel_cta(const K k, u32 nMax, const u32* __restrict__ nDev, u32* workCtr, const u32* __restrict__ abortWord) {
+    if (abortWord && (*abortWord & ERR_ABORT_MASK))
+        return; // an earlier stage of this attempt overflowed a list: what follows would read unwritten records
     __shared__ u32 claimed;
     u32 n = nMax;
     if (nDev) {
@@ -585,6 +593,9 @@ struct CudaBackend {
     u32 heavyGroupSize() const { return (u32)heavyGroup; }
     // Resident CTAs per SM of the warp-per-task search launch: 4 (126 registers per thread, 12 KB of frontier
     // buffers per warp) or, with COLUMBA_B200_SEARCH_OCC=8, 8 (64 registers, 6 KB per warp)
+    // error word of the batch in flight: kernels return at once when an earlier one raised an overflow bit
+    const u32* abortWord = nullptr;
+    void setAbortWord(const u32* w) { abortWord = w; }
     int warpOcc = 4;
     int fcBytesEnv = -1; // COLUMBA_B200_FRONTIER_SMEM: bytes of frontier buffers per warp (-1: default)
     u32 frontierCacheBytes() const { return fcBytesEnv >= 0 ? (u32)fcBytesEnv : (warpOcc == 8 ? 6144u : 12288u); }
@@ -594,13 +605,13 @@ struct CudaBackend {
     template <class K> void launch(const K& k, u32 nMax, const u32* nDev, int kind) {
         if (nMax == 0)
             return;
-        void (*fn)(const K, u32, const u32*, u32*);
+        void (*fn)(const K, u32, const u32*, u32*, const u32*);
         if constexpr (isWarpTask<K>(0) && groupOfK<K>(0) > 32) {
             constexpr int G = groupOfK<K>(0);
             static_assert(G == 256 || G == 128, "CTA size of the group-task launcher");
             if (nextCtr >= N_CTRS)
                 throw BackendError("work counter pool exhausted");
-            clb_kernel_cta<K, G><<<(u32)numSMs * (u32)(HEAVY_THREADS_PER_SM / G), G, 0, stream>>>(k, nMax, nDev, workCtrs + nextCtr++);
+            clb_kernel_cta<K, G><<<(u32)numSMs * (u32)(HEAVY_THREADS_PER_SM / G), G, 0, stream>>>(k, nMax, nDev, workCtrs + nextCtr++, abortWord);
             CLB_CUDA(cudaGetLastError());
             launches++;
             return;
@@ -634,7 +645,7 @@ struct CudaBackend {
             if (need < blocks)
                 blocks = need;
         }
-        fn<<<blocks, 128, smem, stream>>>(k, nMax, nDev, ctr);
+        fn<<<blocks, 128, smem, stream>>>(k, nMax, nDev, ctr, abortWord);
         CLB_CUDA(cudaGetLastError());
         launches++;
     }

@@ -186,6 +186,11 @@ enum ErrBit {
     ERR_INTERNAL = 512
 };
 
+// list overflows: the attempt is void (the host grows the list and runs the batch again), and the tail of an
+// overflowed list holds unwritten records, so the kernels after the one that raised the bit do nothing
+enum { ERR_ABORT_MASK = ERR_CAND_OVERFLOW | ERR_FMOCC_OVERFLOW | ERR_TEXTOCC_OVERFLOW | ERR_OUT_OVERFLOW |
+                        ERR_TASK_OVERFLOW | ERR_ROWS_OVERFLOW | ERR_STACK_OVERFLOW };
+
 enum { DIR_FWD = 0, DIR_BWD = 1 };
 enum { PART_UNIFORM = 0, PART_STATIC = 1, PART_DYNAMIC = 2 };
 enum { METRIC_HAMMING = 0, METRIC_EDIT = 1 };

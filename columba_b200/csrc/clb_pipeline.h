@@ -19,7 +19,10 @@
 //   void mark(int stage) (timing hook)
 #pragma once
 #include "clb_kernels.h"
+#include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
+#include <chrono>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -142,6 +145,7 @@ template <typename BE> struct Pipeline {
         bMisc.ensure(be, sizeof(Misc));
         be.zero(bMisc.p, sizeof(Misc));
         Misc* M = (Misc*)bMisc.p;
+        be.setAbortWord(nullptr);
         MaxLenKernel k{dOff, &M->nT};
         be.launch(k, R, nullptr, WK_LIGHT);
         u32 v = 0;
@@ -258,6 +262,7 @@ template <typename BE> struct Pipeline {
         B.counters = M->counters;
         B.stats = M->stats;
         B.err = &M->err;
+        be.setAbortWord(&M->err);
         // per-group arrays: 2 x (G+1)
         const size_t pr = (size_t)(G + 1);
         bPerRead.ensure(be, pr * 2 * 4 + R + 16);
@@ -441,6 +446,7 @@ template <typename BE> struct Pipeline {
             be.mark(STG_TEXT);
         }
         // ---- results
+        be.setAbortWord(nullptr);
         be.d2h(&hm, bMisc.p, sizeof(hm));
         u32 err = hm.err;
         if (err & ERR_CAND_OVERFLOW)
@@ -494,8 +500,14 @@ template <typename BE> struct Pipeline {
             bool readsOnDevice, const MapOptions& opt, MapResult<BE>* res, bool fetch) {
         const u32 retry = ERR_CAND_OVERFLOW | ERR_FMOCC_OVERFLOW | ERR_TEXTOCC_OVERFLOW | ERR_OUT_OVERFLOW | ERR_STACK_OVERFLOW;
         u32 err = 0;
-        for (int attempt = 0; attempt < 8; attempt++) {
+        static const bool debug = getenv("COLUMBA_B200_DEBUG") != nullptr;
+        for (int attempt = 0; attempt < 12; attempt++) {
+            const auto t0 = std::chrono::steady_clock::now();
             err = runOnce(st, reads, off, R, maxLen, totalBytes, readsOnDevice, opt, res, fetch);
+            if (debug)
+                fprintf(stderr, "[clb] attempt %d: %.3f s, error bits %u, lists per read: cand %.1f fm %.1f tx %.1f out %.1f, heavy scratch %zu MB\n",
+                        attempt, std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count(), err, candPerRead,
+                        fmPerRead, txPerRead, outPerRead, heavySlabBytes >> 20);
             if (!(err & retry))
                 break;
         }

@@ -41,6 +41,8 @@ struct HostEmuBackend {
     template <class K> static constexpr bool isWarpTask(long) { return false; }
     template <class K> void launch(const K& k, u32 nMax, const u32* nDev, int) {
         u32 n = nDev ? (*nDev < nMax ? *nDev : nMax) : nMax;
+        if (abortWord && (*abortWord & ERR_ABORT_MASK))
+            return;
         typename K::State st;
         k.begin(st, 0);
         for (u32 i = 0; i < n; i++) {
@@ -55,6 +57,8 @@ struct HostEmuBackend {
     static const int kHeavyGroup = 32; // lanes per heavy search task (the emulation always runs groups of 32)
     u32 heavyGroupSize() const { return 32; }
     u32 frontierCacheBytes() const { return 0; } // no shared memory here
+    const u32* abortWord = nullptr;
+    void setAbortWord(const u32* w) { abortWord = w; }
     static u32 sortResult(u32) { return 0; }
     void sortPairs(u64* k0, u32* v0, u64*, u32*, u32 nMax, const u32* nDev, u32) {
         const u32 n = nDev ? (*nDev < nMax ? *nDev : nMax) : nMax;
