@@ -491,11 +491,11 @@ struct CudaBackend {
         CLB_CUDA(cudaStreamCreateWithFlags(&ownStream, cudaStreamNonBlocking));
         stream = ownStream;
         if (const char* e = getenv("COLUMBA_B200_SEARCH_OCC"))
-            warpOcc = atoi(e) == 8 ? 8 : 4;
+            warpOcc = atoi(e) == 4 ? 4 : 8;
         if (const char* e = getenv("COLUMBA_B200_FRONTIER_SMEM"))
             fcBytesEnv = atoi(e);
         if (const char* e = getenv("COLUMBA_B200_HEAVY_GROUP"))
-            heavyGroup = atoi(e) == 128 ? 128 : HEAVY_GROUP;
+            heavyGroup = atoi(e) == 256 ? 256 : 128;
         CLB_CUDA(cudaMalloc(&workCtrs, N_CTRS * sizeof(u32)));
         CLB_CUDA(cudaEventCreate(&evBegin));
         CLB_CUDA(cudaEventCreate(&evEnd));
@@ -589,7 +589,7 @@ struct CudaBackend {
         }
     }
     static const int kHeavyGroup = HEAVY_GROUP; // lanes per heavy search task (default)
-    int heavyGroup = HEAVY_GROUP;               // COLUMBA_B200_HEAVY_GROUP=128: CTAs of 128 threads, four per SM
+    int heavyGroup = 128;                       // CTAs of 128 threads, four per SM (COLUMBA_B200_HEAVY_GROUP=256: 256 x 2)
     u32 heavyGroupSize() const { return (u32)heavyGroup; }
     // Resident CTAs per SM of the warp-per-task search launch: 4 (126 registers per thread, 12 KB of frontier
     // buffers per warp) or, with COLUMBA_B200_SEARCH_OCC=8, 8 (64 registers, 6 KB per warp)
