@@ -707,6 +707,11 @@ struct CudaBackend {
             lastStage = stage;
         }
     }
+    // a batch that is re-run after a list overflow times the stages of its last attempt
+    void restartStages() {
+        CLB_CUDA(cudaEventRecord(evStage[0], stream));
+        lastStage = -1;
+    }
     void beginBatch() {
         CLB_CUDA(cudaSetDevice(device));
         launches = 0;

@@ -119,6 +119,9 @@ template <typename BE> struct Pipeline {
     double candPerRead = 24, fmPerRead = 4, txPerRead = 24, outPerRead = 8;
     size_t searchSlabBytes = (size_t)1 << 20, heavySlabBytes = (size_t)32 << 20; // scratch per warp of the search
     u32 minCap = 1 << 16;
+    bool dedupPays = true;   // the last batch's candidate de-duplication removed at least 3 %
+    u32 dedupProbe = 0;      // batches since dedup was last tried (0: try it in the next batch)
+    bool dedupOn = true;     // de-duplication was on in the batch in flight
     std::string lastError;
 
     Pipeline(BE& b) : be(b) {}
@@ -163,6 +166,7 @@ template <typename BE> struct Pipeline {
     // caller may simply call again).
     u32 runOnce(const DevStrategy& st, const u8* reads, const u32* off, u32 R, u32 maxLen, size_t totalBytes,
                 bool readsOnDevice, const MapOptions& opt, MapResult<BE>* res, bool fetch) {
+        be.restartStages();
         Batch B;
         B.R = R;
         B.maxLen = maxLen;
@@ -380,7 +384,11 @@ template <typename BE> struct Pipeline {
             if (opt.metric == METRIC_EDIT) {
                 LocateKernel l1{ix, B};
                 be.launch(l1, capCands, &M->nCands, WK_LIGHT);
-                DedupKernel l2{B, wide ? 0u : 1u};
+                // collapsing equal windows pays when seeds of a read share their diagonal (45 % of the candidates on
+                // a small genome); on repeat-rich input it removes under 1 %, and the 32-neighbour compare is skipped
+                // while the previous batch of this context says so
+                dedupOn = dedupPays || dedupProbe == 0;
+                DedupKernel l2{B, (wide || !dedupOn) ? 0u : 1u};
                 be.launch(l2, capCands, &M->nCands, WK_LIGHT);
                 ScreenKernel l3{ix, B};
                 be.launch(l3, capCands, &M->nUniq, WK_LIGHT);
@@ -467,6 +475,16 @@ template <typename BE> struct Pipeline {
             memcpy(res->stats, hm.stats, sizeof(hm.stats));
             res->stats[ST_UNIQUE_CANDS] = opt.metric == METRIC_EDIT ? tmin(hm.nUniq, capCands) : tmin(hm.nCands, capCands);
             res->stats[ST_HEAVY_TASKS] = hm.nHeavy;
+        }
+        if (opt.metric == METRIC_EDIT && !(err & ERR_ABORT_MASK) && hm.nCands > 100000) {
+            if (dedupOn) {
+                dedupPays = (double)hm.nUniq < 0.97 * (double)tmin(hm.nCands, capCands);
+                dedupProbe = dedupPays ? 0u : 1u;
+            } else {
+                dedupProbe = (dedupProbe + 1) % 64; // try again every 64 batches
+            }
+        }
+        if (res) {
             res->cigW = B.cigW;
             if (fetch && !(err & ~(u32)ERR_SHORT_READ)) {
                 u32 n = hm.nOut;

@@ -83,6 +83,7 @@ struct HostEmuBackend {
         out[n] = run;
     }
     void mark(int) {}
+    void restartStages() {}
     void setStream(void*) {}
     void beginBatch() { launches = 0; }
     void endBatch() {}
