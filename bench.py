@@ -42,6 +42,7 @@ sys.path.insert(0, os.path.join(ROOT, "tools"))
 
 REF_BIN = os.path.join(ROOT, "oracle", "_ref", "columba")
 BUILDER = os.path.join(ROOT, "columba_b200", "bin", "clb_gpu_build")
+MAPPER = os.path.join(ROOT, "columba_b200", "bin", "clb_map")
 METRIC_NAME = "reads/sec (150bp, k=4 edit, ALL) on 3.1 Gbp ref"
 METRIC_NAME_C5 = "reads/sec (250bp, k=5 Hamming, ALL, custom pigeon scheme) on 3.1 Gbp ref"
 
@@ -249,6 +250,7 @@ def main():
     ap.add_argument("--batches", type=int, default=2, help="distinct read batches the steps rotate through")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="mapping time the cpu_baseline sample is sized for")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e-sam", action="store_true", help="skip the FASTQ-to-SAM leg (batch driver clb_map)")
     ap.add_argument("--no-numa-bind", action="store_true", help="do not bind the process to the GPU's local CPUs")
     ap.add_argument("--host-threads", type=int, default=2, help="host threads (one context each) of the e2e leg")
     args = ap.parse_args()
@@ -532,6 +534,34 @@ def main():
             "matches_per_read": counters_all["TOTAL_UNIQUE_MATCHES"] / R_total,
             "wall_ms_per_step": wall / args.steps, "index_device_bytes": ix.device_bytes,
             "index_build_or_cache_s": t_build, "index_load_s": t_load, "distinct_batches": nb}
+    if world == 1 and not args.no_e2e_sam and not hamming and os.path.exists(MAPPER):
+        # the same timer as the reference's: FASTQ parsing, mapping, SAM formatting and writing (to /dev/shm), index
+        # load excluded, no warm-up (the first batch of every context grows its lists)
+        try:
+            d = data_dir(args)
+            fq = os.path.join(d, "e2e_sam_%d.fq" % n)
+            if not os.path.exists(fq):
+                write_fastq_matrix(fq, batches[0])
+            shm = "/dev/shm" if os.path.isdir("/dev/shm") else d
+            sam = os.path.join(shm, "clb_map_out_%d.sam" % os.getpid())
+            p = subprocess.run([MAPPER, "-r", base, "-f", fq, "-o", sam, "-e", str(args.k), "-t", str(max(2, n_thr)),
+                                "-b", "262144", "-d", str(local), "-D", cb.SCHEMES_DIR], capture_output=True, text=True)
+            mt = re.search(r"(\d+) mapping threads finished mapping in ([0-9.]+)s", p.stderr)
+            sam_bytes = os.path.getsize(sam) if os.path.exists(sam) else 0
+            if os.path.exists(sam):
+                os.unlink(sam)
+            if p.returncode == 0 and mt:
+                line["e2e_sam"] = {"value": n / float(mt.group(2)), "unit": "reads/s", "seconds": float(mt.group(2)),
+                                   "reads": n, "sam_bytes": sam_bytes, "host_threads": int(mt.group(1)),
+                                   "includes": "FASTQ parsing, H2D, kernels, D2H, SAM formatting and writing to /dev/shm by "
+                                               "the batch driver columba_b200/bin/clb_map (one context per host thread, "
+                                               "batches of 262144 reads, no warm-up); index load excluded, as in the "
+                                               "reference's 'mapping threads finished mapping in' timer"}
+            else:
+                line["e2e_sam"] = {"value": None, "error": (p.stderr or "")[-200:]}
+        except Exception as e:  # informative leg
+            line["e2e_sam"] = {"value": None, "error": str(e)[:200]}
+        progress("FASTQ-to-SAM leg done")
     if world == 1 and not args.no_cpu_baseline:
         threads = cpu_threads()
         try:
