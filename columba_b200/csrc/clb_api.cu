@@ -591,14 +591,17 @@ struct CudaBackend {
     static const int kHeavyGroup = HEAVY_GROUP; // lanes per heavy search task (default)
     int heavyGroup = 128;                       // CTAs of 128 threads, four per SM (COLUMBA_B200_HEAVY_GROUP=256: 256 x 2)
     u32 heavyGroupSize() const { return (u32)heavyGroup; }
-    // Resident CTAs per SM of the warp-per-task search launch: 4 (126 registers per thread, 12 KB of frontier
-    // buffers per warp) or, with COLUMBA_B200_SEARCH_OCC=8, 8 (64 registers, 6 KB per warp)
     // error word of the batch in flight: kernels return at once when an earlier one raised an overflow bit
     const u32* abortWord = nullptr;
     void setAbortWord(const u32* w) { abortWord = w; }
-    int warpOcc = 4;
-    int fcBytesEnv = -1; // COLUMBA_B200_FRONTIER_SMEM: bytes of frontier buffers per warp (-1: default)
-    u32 frontierCacheBytes() const { return fcBytesEnv >= 0 ? (u32)fcBytesEnv : (warpOcc == 8 ? 6144u : 12288u); }
+    // Resident CTAs per SM of the warp-per-task search launch: 8 (64 registers per thread; the kernel waits on
+    // dependent HBM round trips, more resident warps hide more of them) or, with COLUMBA_B200_SEARCH_OCC=4, 4 (120
+    // registers).  COLUMBA_B200_FRONTIER_SMEM = bytes of shared-memory frontier buffers per warp; 0 by default: on
+    // the 3.1 Gbp workload staging the frontier on chip made the search 10 % slower (profiles/r2k_*: the buffers take
+    // their 192 KB from the L1 that serves the rank records and the read's bit planes, and every child is stored twice)
+    int warpOcc = 8;
+    int fcBytesEnv = -1;
+    u32 frontierCacheBytes() const { return fcBytesEnv >= 0 ? (u32)fcBytesEnv : 0u; }
     u32 workers(int kind) { return blocksFor(kind) * (kind == WK_SEARCH_HEAVY ? (u32)heavyGroup : 128u); }
     u32 laneStride() const { return 32; }
     u32 fallbackWorkers() const { return 0; }

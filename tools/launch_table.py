@@ -12,10 +12,13 @@ def load(path):
     rows = list(csv.DictReader(lines[i:]))
     out = []
     for r in rows:
+        if r["Metric Name"] != "gpu__time_duration.sum":
+            continue
         n = r["Kernel Name"]
         m = re.search(r"<(?:clb::)?(\w+)", n)
         short = m.group(1) if (m and "clb_kernel" in n) else n.split("(")[0].replace("void ", "").replace("clb::", "")
-        out.append((short, float(r["Metric Value"]) / 1e6, r["Grid Size"], r["Block Size"]))
+        scale = {"ns": 1e-6, "us": 1e-3, "ms": 1.0, "s": 1e3}.get(r["Metric Unit"], 1e-6)
+        out.append((short, float(r["Metric Value"].replace(",", "")) * scale, r["Grid Size"], r["Block Size"]))
     return out
 
 
