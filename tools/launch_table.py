@@ -35,7 +35,7 @@ def steps_of(launches):
 
 if __name__ == "__main__":
     st = steps_of(load(sys.argv[1]))
-    k = int(sys.argv[2]) if len(sys.argv) > 2 else 4
+    k = int(sys.argv[2]) if len(sys.argv) > 2 else max(range(len(st)), key=lambda q: sum(x[1] for x in st[q]))
     agg = collections.OrderedDict()
     for name, ms, g, b in st[k]:
         key = name + (" " + b if name == "FrontierKernel" else "")

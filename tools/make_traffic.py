@@ -33,7 +33,9 @@ def main():
             cur = []
         cur.append(l)
     steps.append(cur)
-    k = int(sys.argv[4]) if len(sys.argv) > 4 else 4
+    # default: the full step with the longest device time (attempts that a list overflow voided are short)
+    dur = [sum(x.get("gpu__time_duration.sum", 0.0) for x in st_) for st_ in steps]
+    k = int(sys.argv[4]) if len(sys.argv) > 4 else max(range(len(steps)), key=lambda q: dur[q])
     st = steps[k]
     out = {"reads_per_step": reads, "ref_bp": ref_bp, "source": path, "step": k, "launches": len(st),
            "stage_dram_bytes": {}, "stage_ms_under_ncu": {}, "kernel_dram_bytes": {}}
