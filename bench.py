@@ -458,7 +458,18 @@ def main():
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms.item()), wall, out, clocks
 
-    ms2, wall2, results2, clocks2 = timed_host(args.steps, 2)
+    try:
+        ms2, wall2, results2, clocks2 = timed_host(args.steps, 2)
+    except cb.ClbError as e:
+        if "out of memory" not in str(e) or n_thr == 1:
+            raise
+        # a second context does not fit beside the first (every context owns its lists and scratch): one host thread
+        progress("end-to-end leg: second context out of memory, falling back to one host thread")
+        for mp in mappers[1:]:
+            mp.close()
+        mappers[:] = mappers[:1]
+        n_thr = 1
+        ms2, wall2, results2, clocks2 = timed_host(args.steps, 2)
     progress("end-to-end leg done: %.1f ms per step" % (ms2 / args.steps))
     n_occ_mean = float(np.mean([r[0] for r in results2]))
     cig_stride = results2[-1][1]
@@ -534,6 +545,11 @@ def main():
             "matches_per_read": counters_all["TOTAL_UNIQUE_MATCHES"] / R_total,
             "wall_ms_per_step": wall / args.steps, "index_device_bytes": ix.device_bytes,
             "index_build_or_cache_s": t_build, "index_load_s": t_load, "distinct_batches": nb}
+    # the contexts of this process own tens of GB of lists and scratch: release them before other processes map
+    for mp in mappers:
+        mp.close()
+    ix.close()
+    torch.cuda.empty_cache()
     if world == 1 and not args.no_e2e_sam and not hamming and os.path.exists(MAPPER):
         # the same timer as the reference's: FASTQ parsing, mapping, SAM formatting and writing (to /dev/shm), index
         # load excluded, no warm-up (the first batch of every context grows its lists)

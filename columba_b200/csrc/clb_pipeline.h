@@ -117,7 +117,7 @@ template <typename BE> struct Pipeline {
         bMisc, bSlabPart, bSlabSearch, bSlabVerify, bSlabVerifyWide, bSlabFilter, bStrategy;
     // list capacities (per read multipliers, grown after an overflow)
     double candPerRead = 24, fmPerRead = 4, txPerRead = 24, outPerRead = 8;
-    size_t searchSlabBytes = (size_t)1 << 20, heavySlabBytes = (size_t)32 << 20; // scratch per warp of the search
+    size_t searchSlabBytes = (size_t)1 << 20, heavySlabBytes = (size_t)16 << 20; // 592 heavy groups: 9.5 GB; x4 on overflow // scratch per warp of the search
     u32 minCap = 1 << 16;
     bool dedupPays = true;   // the last batch's candidate de-duplication removed at least 3 %
     u32 dedupProbe = 0;      // batches since dedup was last tried (0: try it in the next batch)
