@@ -50,7 +50,9 @@ EXPORTS = ["clb_abi_version", "clb_sizeof_result", "clb_device_count", "clb_inde
            "clb_index_num_seqs", "clb_index_seq_name", "clb_index_seq_start", "clb_index_device_bytes",
            "clb_ctx_create", "clb_ctx_free", "clb_last_error", "clb_ctx_set_strategy", "clb_ctx_set_options",
            "clb_ctx_set_stream", "clb_ctx_set_trim_max", "clb_ctx_set_filter_per_strand", "clb_ctx_supports_distance", "clb_ctx_num_parts", "clb_map_batch", "clb_map_batch_device", "clb_occ4",
-           "clb_extend", "clb_find_sa", "clb_kmer_lookup", "clb_build_index", "clb_gather_ceiling"]
+           "clb_extend", "clb_find_sa", "clb_kmer_lookup", "clb_build_index", "clb_gather_ceiling", "clb_find_sa_static"]
+
+STATIC_MAX_ROWS = 1 << 20  # CLB_STATIC_MAX_ROWS
 
 _libs = {}
 
@@ -98,6 +100,8 @@ def load_library(path=None):
     lib.clb_build_index.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_char_p, C.c_size_t]
     if hasattr(lib, "clb_gather_ceiling"):  # CUDA library only (the CPU unit-test harness has no such kernel)
         lib.clb_gather_ceiling.argtypes = [vp, C.c_uint64, C.POINTER(C.c_float), C.POINTER(C.c_uint64)]
+    if hasattr(lib, "clb_find_sa_static"):  # CUDA library only
+        lib.clb_find_sa_static.argtypes = [vp, vp, C.c_uint32, vp]
     lib.clb_sizeof_result.restype = C.c_size_t
     if lib.clb_sizeof_result() != C.sizeof(ClbResult):
         raise ClbError(-6, "clb_result layout of %s differs from this binding's" % path)
@@ -277,6 +281,14 @@ class Mapper:
         p = np.ascontiguousarray(rows, np.uint32)
         out = np.zeros(len(p), np.uint32)
         self._check(self.lib.clb_find_sa(self.h, _ptr(p), len(p), _ptr(out)))
+        return out
+
+    def find_sa_static(self, rows):
+        """clb_find_sa_static: find_sa staged in the library's static device array, no device allocation
+        (at most STATIC_MAX_ROWS rows per call)."""
+        p = np.ascontiguousarray(rows, np.uint32)
+        out = np.zeros(len(p), np.uint32)
+        self._check(self.lib.clb_find_sa_static(self.h, _ptr(p), len(p), _ptr(out)))
         return out
 
     def kmer_lookup(self, codes):

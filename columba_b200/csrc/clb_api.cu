@@ -7,6 +7,7 @@
 
 #include <cstdio>
 #include <cstdlib>
+#include <mutex>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -810,6 +811,95 @@ extern "C" int clb_gather_ceiling(clb_ctx* c, uint64_t n_lookups, float* ms_out,
         cudaEventDestroy(e0);
         cudaEventDestroy(e1);
         be.free(sink);
+    } catch (std::exception& e) {
+        c->err = e.what();
+        return CLB_E_CUDA;
+    }
+    return CLB_OK;
+}
+
+// ---- clb_find_sa_static: clb_find_sa for callers that must not allocate (include/columba_b200.h).
+// clb_find_sa stages the rows and the results in two device buffers it allocates per call; this variant
+// stages them in the file-scope array below instead: CLB_STATIC_MAX_ROWS rows in, as many results out,
+// 8 MB that every GPU which loads this library holds until the process exits.  No counterpart in the
+// reference.
+//
+// `clbStaticScratch` named in HOST code is the host-side stand-in of the symbol, not a device address:
+// the address a kernel may use comes from cudaGetSymbolAddress, asked once per device with that device
+// current (staticScratchOn), and is what the kernel below is given.
+namespace clb {
+static const u32 STATIC_MAX_ROWS = CLB_STATIC_MAX_ROWS;
+static __device__ __align__(256) u32 clbStaticScratch[2 * (size_t)STATIC_MAX_ROWS];
+
+__global__ void __launch_bounds__(256) clb_find_sa_static_kernel(IndexView ix, const u32* __restrict__ rows,
+                                                                  u32* __restrict__ out, u32 n) {
+    for (u32 i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        u64 lf = 0;
+        out[i] = findSA(ix, rows[i], lf) + 1; // + 1: a slot still holding the 0 it was cleared to was never written
+    }
+}
+
+static const int STATIC_MAX_DEVICES = 64;
+static std::mutex staticScratchMutex;
+static u32* staticScratchPtr[STATIC_MAX_DEVICES] = {};
+
+// device address of clbStaticScratch on `device` (which the caller has made current)
+static u32* staticScratchOn(int device) {
+    if (device < 0 || device >= STATIC_MAX_DEVICES)
+        throw BackendError("clb_find_sa_static: device ordinal beyond " + std::to_string(STATIC_MAX_DEVICES));
+    std::lock_guard<std::mutex> lock(staticScratchMutex);
+    if (!staticScratchPtr[device]) {
+        u32* p = nullptr;
+        CLB_CUDA(cudaGetSymbolAddress((void**)&p, clbStaticScratch));
+        if (!p)
+            throw BackendError("clb_find_sa_static: cudaGetSymbolAddress returned a null address");
+        staticScratchPtr[device] = p;
+    }
+    return staticScratchPtr[device];
+}
+} // namespace clb
+
+extern "C" int clb_find_sa_static(clb_ctx* c, const uint32_t* rows, uint32_t n, uint32_t* out) {
+    if (!c)
+        return CLB_E_INVALID;
+    if (n > CLB_STATIC_MAX_ROWS) {
+        c->err = "clb_find_sa_static: " + std::to_string(n) + " rows in one call, the static scratch holds " +
+                 std::to_string((unsigned)CLB_STATIC_MAX_ROWS) + " (CLB_STATIC_MAX_ROWS); split the call or use clb_find_sa";
+        return CLB_E_OVERFLOW;
+    }
+    if (n == 0)
+        return CLB_OK;
+    if (!rows || !out) {
+        c->err = "clb_find_sa_static: null rows / out";
+        return CLB_E_INVALID;
+    }
+    const clb::IndexView ix = c->pipe->ix;
+    for (uint32_t i = 0; i < n; i++)
+        if (rows[i] >= ix.textLength) {
+            c->err = "row out of range";
+            return CLB_E_INVALID;
+        }
+    try {
+        using namespace clb;
+        CudaBackend& be = *c->be;
+        CLB_CUDA(cudaSetDevice(be.device));
+        u32* dRows = staticScratchOn(be.device);
+        u32* dOut = dRows + STATIC_MAX_ROWS;
+        // the array keeps what the previous call left: the result slots of this call start at zero
+        CLB_CUDA(cudaMemsetAsync(dOut, 0, (size_t)n * sizeof(u32), be.stream));
+        CLB_CUDA(cudaMemcpyAsync(dRows, rows, (size_t)n * sizeof(u32), cudaMemcpyHostToDevice, be.stream));
+        const u32 blocks = tmin((n + 255u) / 256u, (u32)be.numSMs * 8u);
+        clb_find_sa_static_kernel<<<blocks, 256, 0, be.stream>>>(ix, dRows, dOut, n);
+        CLB_CUDA(cudaGetLastError());
+        CLB_CUDA(cudaMemcpyAsync(out, dOut, (size_t)n * sizeof(u32), cudaMemcpyDeviceToHost, be.stream));
+        CLB_CUDA(cudaStreamSynchronize(be.stream));
+        for (uint32_t i = 0; i < n; i++) {
+            if (out[i] == 0) {
+                c->err = "clb_find_sa_static: result slot " + std::to_string(i) + " was not written";
+                return CLB_E_INTERNAL;
+            }
+            out[i]--;
+        }
     } catch (std::exception& e) {
         c->err = e.what();
         return CLB_E_CUDA;

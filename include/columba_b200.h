@@ -174,6 +174,18 @@ int clb_extend(clb_ctx*, int mode, const uint32_t* parents, uint32_t n, uint32_t
 int clb_find_sa(clb_ctx*, const uint32_t* rows, uint32_t n, uint32_t* out);
 int clb_kmer_lookup(clb_ctx*, const uint32_t* codes, uint32_t n, uint32_t* out4);
 
+/* clb_find_sa for callers that cannot allocate device memory (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  No counterpart in the reference.
+ * Same arguments, results and errors as clb_find_sa (HOST pointers), but the device staging of
+ * rows and results lives in a static device array of the library -- 2 x CLB_STATIC_MAX_ROWS x 4 bytes = 8 MB
+ * that every GPU which loads the library holds until the process exits -- and the call makes no cudaMalloc /
+ * cudaFree or other allocating call.  n > CLB_STATIC_MAX_ROWS is refused with CLB_E_OVERFLOW (split the call,
+ * or use clb_find_sa).  All calls on one GPU share the array, from every context and thread: calls that
+ * overlap on the GPU race; serialise them.  The first call on a GPU resolves the array's device address
+ * (cudaGetSymbolAddress), so make one call before starting a capture. */
+#define CLB_STATIC_MAX_ROWS (1u << 20)
+int clb_find_sa_static(clb_ctx*, const uint32_t* rows, uint32_t n, uint32_t* out);
+
 /* Measured ceiling of the path's roofline unit: n_lookups independent random 32-byte rank-record reads from
  * the loaded index (8 in flight per thread); *ms = kernel time (CUDA events), *done = reads issued. */
 int clb_gather_ceiling(clb_ctx*, uint64_t n_lookups, float* ms, uint64_t* done);
