@@ -220,7 +220,15 @@ def sized_cpu_sample(base, reads, k, threads, out_dir, target_s, max_n):
 # --------------------------------------------------------------------------- main
 def progress(msg):
     """Phase marks on stderr (stdout carries the one JSON line)."""
-    sys.stderr.write("[bench %7.1f s] %s\n" % (time.perf_counter() - T_START, msg))
+    mem = ""
+    try:
+        import torch
+        if torch.cuda.is_available() and torch.cuda.is_initialized():
+            free, total = torch.cuda.mem_get_info()
+            mem = " [HBM in use %.1f GB]" % ((total - free) / 1e9)
+    except Exception:  # noqa: BLE001
+        pass
+    sys.stderr.write("[bench %7.1f s] %s%s\n" % (time.perf_counter() - T_START, msg, mem))
     sys.stderr.flush()
 
 

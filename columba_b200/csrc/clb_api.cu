@@ -538,7 +538,12 @@ struct CudaBackend {
     void* alloc(size_t n) {
         void* p = nullptr;
         CLB_CUDA(cudaSetDevice(device));
-        CLB_CUDA(cudaMalloc(&p, n ? n : 16));
+        const cudaError_t e = cudaMalloc(&p, n ? n : 16);
+        if (e != cudaSuccess) {
+            cudaGetLastError(); // not sticky: the context stays usable, the next launch check must not see it
+            throw BackendError(std::string("CUDA error: ") + cudaGetErrorString(e) + " at cudaMalloc of " +
+                               std::to_string(n >> 20) + " MB");
+        }
         return p;
     }
     void free(void* p) {

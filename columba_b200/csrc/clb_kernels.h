@@ -28,6 +28,17 @@ struct MaxLenKernel {
     }
 };
 
+// *dst = *src & mask (the error word the search stage aborts on, see Pipeline::runOnce)
+struct MaskWordKernel {
+    const u32* src;
+    u32* dst;
+    u32 mask;
+    struct State {};
+    CLB_HD void begin(State&, u32) const {}
+    CLB_HD void run(State&, u32) const { *dst = *src & mask; }
+    CLB_HD void end(State&) const {}
+};
+
 // stage 0
 struct PrepKernel {
     Batch B;

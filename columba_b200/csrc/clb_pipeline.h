@@ -42,9 +42,10 @@ template <typename BE> struct DevBuf {
     void ensure(BE& be, size_t n) {
         if (n <= bytes)
             return;
-        if (p)
-            be.free(p);
-        size_t want = n + n / 4 + 256;
+        // released first and forgotten before the new allocation: alloc() throws when the device is full
+        release(be);
+        // head-room so that batches of slightly different size do not re-allocate: a quarter, at most 256 MB
+        const size_t want = n + tmin<size_t>(n / 4, (size_t)256 << 20) + 256;
         p = be.alloc(want);
         bytes = want;
     }
@@ -124,7 +125,13 @@ template <typename BE> struct Pipeline {
     bool dedupOn = true;     // de-duplication was on in the batch in flight
     std::string lastError;
 
-    Pipeline(BE& b) : be(b) {}
+    Pipeline(BE& b) : be(b) {
+        // test hook: small lists make the overflow / re-run path run on small batches
+        if (const char* e = getenv("COLUMBA_B200_MIN_LIST_CAP")) {
+            minCap = tmax<u32>(16u, (u32)atoi(e));
+            candPerRead = fmPerRead = txPerRead = outPerRead = 0;
+        }
+    }
     ~Pipeline() {
         DevBuf<BE>* all[] = {&bReads, &bOff, &bCodes, &bPlanes, &bParts, &bTasks, &bCands, &bCandAux, &bExtra, &bFm, &bTx, &bTxCig, &bCigJobs, &bOut,
                              &bOutCig, &bPerRead, &bSort, &bFmCig, &bTrim, &bMisc, &bSlabPart, &bSlabSearch, &bSlabVerify, &bSlabVerifyWide, &bSlabFilter,
@@ -141,6 +148,7 @@ template <typename BE> struct Pipeline {
         u32 nTasks, nCands, nFm, nTx, nOut, nExtra, nCigJobs, nUniq, nHeavy, nTrim, nSurv;
         u32 fmSlots[2];
         u32 nT, nR; // 2R and R as device-side task counts
+        u32 errSearch; // err without the candidate / index-occurrence overflow bits: what the search stage aborts on
     };
 
     // longest read of a batch whose offsets are on the device
@@ -339,6 +347,14 @@ template <typename BE> struct Pipeline {
         }
         // ---- stage 2
         {
+            // The search only appends to the candidate and index-occurrence lists, and an append beyond the capacity
+            // still counts: when one of them overflows the search runs to its end, so that the re-run is sized from
+            // the full count instead of from wherever the kernels stopped (one re-run instead of several, no
+            // doubling past what the batch needs).  Every other overflow stops it at once, as it does all later stages.
+            be.setAbortWord(nullptr);
+            MaskWordKernel mw{&M->err, &M->errSearch, ~(u32)(ERR_CAND_OVERFLOW | ERR_FMOCC_OVERFLOW)};
+            be.launch(mw, 1, nullptr, WK_LIGHT);
+            be.setAbortWord(&M->errSearch);
             // one warp per task; a second launch with large scratch takes the tasks whose frontier
             // outgrew the first launch's
             const bool wide = opt.k > BPC<u64>::MAX_ED;
@@ -369,6 +385,7 @@ template <typename BE> struct Pipeline {
                     be.launch(k2h, capTasks, &M->nHeavy, WK_SEARCH_HEAVY);
                 }
             }
+            be.setAbortWord(&M->err);
             be.mark(STG_SEARCH);
         }
         // ---- stage 3
@@ -457,10 +474,13 @@ template <typename BE> struct Pipeline {
         be.setAbortWord(nullptr);
         be.d2h(&hm, bMisc.p, sizeof(hm));
         u32 err = hm.err;
+        // the search stage counted every append unless something else stopped it (see stage 2): then the count is
+        // what the batch needs, otherwise it is a lower bound
+        const bool searchComplete = !(err & ERR_ABORT_MASK & ~(u32)(ERR_CAND_OVERFLOW | ERR_FMOCC_OVERFLOW));
         if (err & ERR_CAND_OVERFLOW)
-            candPerRead = tmax(candPerRead * 2, (double)hm.nCands / R * 1.25);
+            candPerRead = tmax(candPerRead * (searchComplete ? 1.0 : 2.0), (double)hm.nCands / R * 1.25);
         if (err & ERR_FMOCC_OVERFLOW)
-            fmPerRead = tmax(fmPerRead * 2, (double)hm.nFm / R * 1.25);
+            fmPerRead = tmax(fmPerRead * (searchComplete ? 1.0 : 2.0), (double)hm.nFm / R * 1.25);
         if (err & ERR_TEXTOCC_OVERFLOW)
             txPerRead = tmax(txPerRead * 2, (double)hm.nTx / R * 1.25 + 1);
         if (err & ERR_OUT_OVERFLOW)

@@ -143,3 +143,25 @@ def test_product_has_no_cpu_fallback(cuda_lib, golden_index):
     with pytest.raises(cb.ClbError) as e:
         cb.Index(golden_index, lib_path=cuda_lib)
     assert e.value.code == -3 and "no CPU fallback" in str(e.value)
+
+
+def test_list_overflow_reruns_give_the_same_result(emu_indexes, monkeypatch):
+    """Lists that start far too small (test hook COLUMBA_B200_MIN_LIST_CAP): the batch is re-run with lists sized
+    from the counts of the overflowing run -- the search stage keeps counting after a candidate / index-occurrence
+    overflow -- and returns what a context with ample lists returns."""
+    ix = emu_indexes(10, 4)
+    names, seqs = gu.read_fastq_gz(os.path.join(gu.GOLD, "g1_edit.fq.gz"))
+    reads, off = cb.Mapper.pack(seqs[:200])
+    for metric, k in (("edit", 4), ("hamming", 3)):
+        m = cb.Mapper(ix, ("named", "columba"), metric)
+        ref = m.map_batch(reads, off, k)
+        m.close()
+        monkeypatch.setenv("COLUMBA_B200_MIN_LIST_CAP", "16")
+        m = cb.Mapper(ix, ("named", "columba"), metric)
+        monkeypatch.delenv("COLUMBA_B200_MIN_LIST_CAP")
+        got = m.map_batch(reads, off, k)
+        m.close()
+        assert got.counters == ref.counters
+        assert (got.read_count == ref.read_count).all()
+        for f in ("seq_id", "pos", "end", "strand", "dist", "n_cigar"):
+            assert (got.occ[f] == ref.occ[f]).all(), f
