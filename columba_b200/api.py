@@ -12,7 +12,7 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-DEFAULT_LIB = os.path.join(HERE, "libcolumba_b200.so")
+DEFAULT_LIB = os.environ.get("COLUMBA_B200_LIB") or os.path.join(HERE, "libcolumba_b200.so")  # override: A/B runs of two builds
 SCHEMES_DIR = os.path.join(HERE, "schemes")
 
 N_COUNTERS, N_STATS, N_STAGES = 17, 11, 6  # CLB_N_COUNTERS, CLB_N_STATS, CLB_N_STAGES of include/columba_b200.h

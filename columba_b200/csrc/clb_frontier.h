@@ -350,6 +350,29 @@ template <typename W, int GS> struct Frontier {
     }
 
     // expand the levels of group G until no node is alive
+    // what a lane keeps of the node it expands between the two passes over its children
+    struct Expand {
+        RowS<W> prs;     // matrix row of the node
+        RangePair ch[4]; // ranges of its children (a node on a chain: ch[0] = the next descendant)
+        const FPI* P;
+        u32 i, row, pi;
+        u32 mode;        // 0: nothing to expand, 1: next descendant of a chain, 2: index extension
+        u32 chainC;
+        u32 sv;          // children that survive, bit q = q-th child in the reference's order
+    };
+    static CLB_HD RangePair pick4(const RangePair ch[4], u32 c) {
+        const RangePair lo = (c & 1u) ? ch[1] : ch[0], hi = (c & 1u) ? ch[3] : ch[2];
+        return (c & 2u) ? hi : lo;
+    }
+
+    // Levels of group G until no node is alive.  A lane expands one node of the level: two rank lookups give
+    // the ranges of its children, one matrix row each decides which of them survive.  The children of a chunk
+    // of GS nodes are appended in depth-first order, which needs the number of surviving children of the
+    // lanes before (one prefix sum) before anything can be written: the children are therefore gone through
+    // twice -- once to count, once to build and store them at their final place -- instead of being parked
+    // between the two (four 64-byte records per lane, dynamically indexed, used to be the bulk of the
+    // kernel's local-memory traffic).  The loop body is written once for both passes and for the chain /
+    // extension / Hamming variants, which keeps the hot code within the instruction cache.
     CLB_HD void expandGroup(FGroup& G, const PartSeq& ps) {
         const u32 idx = G.idx, dir = s.dir[idx], uni = s.isUniBack(idx) ? 1u : 0u, maxED = s.U[idx];
         const u32 part = s.order[idx];
@@ -362,144 +385,149 @@ template <typename W, int GS> struct Frontier {
         while (b1 > b0 && !err) {
             u32 outBase = b1; // children are appended to the node array
             for (u32 base = b0; base < b1 && !err; base += GS) {
-                LV<u32> nKids;
-                LV<Node> kid[4];
-                CLB_LANES_G(l, GS) {
-                    nKids[l] = 0;
-                    const u32 i = base + (u32)l;
-                    if (i >= b1)
-                        continue;
-                    const Node x = (level > 0 && i - b0 < fcCap) ? fc[level & 1u][i - b0] : nodes[i];
-                    if (x.kind() != FK_ALIVE)
-                        continue;
-                    const FPI& P = pisOf(G)[x.pi];
-                    const u32 row = (u32)x.row + 1;
-                    RowS<W> prs;
-                    prs.HP = x.HP;
-                    prs.HN = x.HN;
-                    prs.RAC = x.RAC;
-                    prs.score = x.score;
-                    if (x.flags() & FF_CHAIN) {
-                        // the next node is the next descendant handed over by the previous phase
-                        const FDesc d = ((const FDesc*)(scr + P.descOff))[x.row];
-                        Node k;
-                        k.r = d.r;
-                        k.row = (u16)row;
-                        k.parent = i;
-                        k.pi = x.pi;
-                        k.cnt = 0;
-                        k.base = 0;
-                        u32 kfl = FF_FROM_CHAIN;
-                        RowS<W> rs;
-                        const bool valid = rowStep<W>(P.g, ps, prs, row, d.c, rs);
-                        ctr[l].rows++;
-                        u32 ed;
-                        u32 kind = classify(P.g, rs, valid, row, 0xFFFFFFFFu, true, idx, ed);
-                        if (kind == 0xFFu)
-                            continue;
-                        if (kind == FK_ALIVE) {
-                            if (row < P.nDesc) {
-                                kfl |= FF_CHAIN;
-                            } else if (P.nDesc == P.g.m - 1) {
-                                kind = FK_DEAD; // the last descendant sits on the last row
-                            } else if (s.dsw[idx]) {
-                                kfl |= FF_USE_SM; // after a switch the children come from the start range
+                LV<u32> nKids, off;
+                LV<Expand> st;
+                u32 total = 0;
+#pragma unroll 1
+                for (u32 pass = 0; pass < 2; pass++) {
+                    CLB_LANES_G(l, GS) {
+                        Expand& S = st[l];
+                        if (pass == 0) {
+                            nKids[l] = 0;
+                            off[l] = 0;
+                            S.mode = 0;
+                            S.sv = 0;
+                            const u32 i = base + (u32)l;
+                            if (i >= b1)
+                                continue;
+                            const Node x = (level > 0 && i - b0 < fcCap) ? fc[level & 1u][i - b0] : nodes[i];
+                            if (x.kind() != FK_ALIVE)
+                                continue;
+                            const FPI* P = pisOf(G) + x.pi;
+                            S.P = P;
+                            S.i = i;
+                            S.pi = x.pi;
+                            S.row = (u32)x.row + 1;
+                            S.prs.HP = x.HP;
+                            S.prs.HN = x.HN;
+                            S.prs.RAC = x.RAC;
+                            S.prs.score = x.score;
+                            if (x.flags() & FF_CHAIN) {
+                                // the next node is the next descendant handed over by the previous phase
+                                const FDesc d = ((const FDesc*)(scr + P->descOff))[x.row];
+                                S.ch[0] = d.r;
+                                S.chainC = d.c;
+                                S.mode = 1;
+                            } else {
+                                // extendFMPos: all four children with two rank lookups
+                                const RangePair parentRange = (x.flags() & FF_USE_SM) ? P->sm.r : x.r;
+                                extendAll(ix, (int)dir, uni != 0, parentRange, S.ch);
+                                ctr[l].lookups += 2;
+                                S.mode = 2;
                             }
                         }
-                        k.setMeta(d.c & 3u, kind, kfl, ed);
-                        k.HP = rs.HP;
-                        k.HN = rs.HN;
-                        k.RAC = rs.RAC;
-                        k.score = rs.score;
-                        if (kind == FK_GD)
-                            k.cnt = 1;
-                        kid[0][l] = k;
-                        nKids[l] = 1;
-                        continue;
-                    }
-                    // extendFMPos: children in the order the reference's stack pops them (T, G, C, A)
-                    const RangePair parentRange = (x.flags() & FF_USE_SM) ? P.sm.r : x.r;
-                    RangePair ch[4];
-                    extendAll(ix, (int)dir, uni != 0, parentRange, ch);
-                    ctr[l].lookups += 2;
-                    u32 nk = 0;
-#pragma unroll
-                    for (int cc = 3; cc >= 0; cc--) {
-                        if (ch[cc].empty())
+                        if (S.mode == 0)
                             continue;
-                        ctr[l].nodes++;
-                        Node k;
-                        k.r = ch[cc];
-                        k.row = (u16)row;
-                        k.parent = i;
-                        k.pi = x.pi;
-                        k.cnt = 0;
-                        k.base = 0;
-                        k.HP = k.HN = k.RAC = W(0);
-                        u32 kind, ked = F_ED_NONE;
-                        if (edit) {
-                            if (row >= P.g.m) {
-                                atomOr(B.err, ERR_INTERNAL);
+                        const FPI& P = *S.P;
+                        const bool chain = S.mode == 1, count = pass == 0;
+                        const u32 row = S.row;
+                        u32 at = outBase + off[l];
+                        const u32 nq = chain ? 1u : 4u;
+#pragma unroll 1
+                        for (u32 q = 0; q < nq; q++) {
+                            if (!count && !((S.sv >> q) & 1u))
                                 continue;
+                            // children in the order the reference's stack pops them (T, G, C, A)
+                            const u32 cc = chain ? S.chainC : 3u - q;
+                            const RangePair r = chain ? S.ch[0] : pick4(S.ch, cc);
+                            if (!chain) {
+                                if (r.empty())
+                                    continue;
+                                if (count)
+                                    ctr[l].nodes++;
                             }
                             RowS<W> rs;
-                            const bool valid = rowStep<W>(P.g, ps, prs, row, (u32)cc, rs);
-                            ctr[l].rows++;
-                            u32 ed;
-                            kind = classify(P.g, rs, valid, row, k.r.width(), false, idx, ed);
-                            if (kind == 0xFFu)
+                            rs.HP = rs.HN = rs.RAC = W(0);
+                            rs.score = 0;
+                            u32 kind, ked = F_ED_NONE, kfl = 0;
+                            if (chain || edit) {
+                                if (!chain && row >= P.g.m) {
+                                    if (count)
+                                        atomOr(B.err, ERR_INTERNAL);
+                                    continue;
+                                }
+                                const bool valid = rowStep<W>(P.g, ps, S.prs, row, cc, rs);
+                                if (count)
+                                    ctr[l].rows++;
+                                kind = classify(P.g, rs, valid, row, chain ? 0xFFFFFFFFu : r.width(), chain, idx, ked);
+                                if (kind == 0xFFu)
+                                    continue;
+                                if (chain) {
+                                    kfl = FF_FROM_CHAIN;
+                                    if (kind == FK_ALIVE) {
+                                        if (row < P.nDesc) {
+                                            kfl |= FF_CHAIN;
+                                        } else if (P.nDesc == P.g.m - 1) {
+                                            kind = FK_DEAD; // the last descendant sits on the last row
+                                        } else if (s.dsw[idx]) {
+                                            kfl |= FF_USE_SM; // after a switch the children come from the start range
+                                        }
+                                    }
+                                }
+                            } else { // recApproxMatchHamming, src/indexinterface.cpp:1211-1304
+                                if (r.width() <= ix.switchPoint) {
+                                    kind = FK_IT;
+                                    rs.score = S.prs.score;
+                                } else {
+                                    const u32 v = S.prs.score + ((cc != partChar(part, dir, row - 1)) ? 1u : 0u);
+                                    rs.score = v;
+                                    if (v > maxED)
+                                        continue;
+                                    if (row == ps.len) {
+                                        if (v < s.L[idx])
+                                            continue;
+                                        kind = FK_HAM_END;
+                                    } else {
+                                        kind = FK_ALIVE;
+                                    }
+                                }
+                            }
+                            if (count) {
+                                S.sv |= 1u << q;
+                                nKids[l]++;
                                 continue;
-                            ked = ed;
+                            }
+                            Node k;
+                            k.r = r;
                             k.HP = rs.HP;
                             k.HN = rs.HN;
                             k.RAC = rs.RAC;
                             k.score = rs.score;
-                        } else { // recApproxMatchHamming, src/indexinterface.cpp:1211-1304
-                            if (k.r.width() <= ix.switchPoint) {
-                                kind = FK_IT;
-                                k.score = x.score;
-                            } else {
-                                const u32 v = x.score + (((u32)cc != partChar(part, dir, row - 1)) ? 1u : 0u);
-                                k.score = v;
-                                if (v > maxED)
-                                    continue;
-                                if (row == ps.len) {
-                                    if (v < s.L[idx])
-                                        continue;
-                                    kind = FK_HAM_END;
-                                } else {
-                                    kind = FK_ALIVE;
-                                }
-                            }
+                            k.parent = S.i;
+                            k.cnt = chain ? (kind == FK_GD ? 1u : 0u) : (kind != FK_ALIVE ? 1u : 0u);
+                            k.base = 0;
+                            k.pi = S.pi;
+                            k.row = (u16)row;
+                            k.setMeta(cc & 3u, kind, kfl, ked);
+                            // the node array of the group is the last allocation: it grows in place
+                            nodes[at] = k;
+                            if (at - b1 < fcCap)
+                                fc[(level + 1u) & 1u][at - b1] = k;
+                            at++;
                         }
-                        k.setMeta((u32)cc, kind, 0, ked);
-                        if (kind != FK_ALIVE)
-                            k.cnt = 1;
-                        kid[nk][l] = k;
-                        nk++;
                     }
-                    nKids[l] = nk;
-                }
-                LV<u32> off;
-                const u32 total = grpExScanG<GS>(nKids, off);
-                if (total) {
-                    const u32 need = alloc((size_t)total * sizeof(Node));
-                    (void)need;
-                    if (err)
-                        break;
-                    // the node array of the group is the last allocation: it grows in place
-                    CLB_LANES_G(l, GS) {
-#pragma unroll
-                        for (u32 q = 0; q < 4; q++)
-                            if (q < nKids[l]) {
-                                const u32 at = outBase + off[l] + q;
-                                nodes[at] = kid[q][l];
-                                if (at - b1 < fcCap)
-                                    fc[(level + 1u) & 1u][at - b1] = kid[q][l];
-                            }
+                    if (pass == 0) {
+                        total = grpExScanG<GS>(nKids, off);
+                        if (!total)
+                            break;
+                        (void)alloc((size_t)total * sizeof(Node));
+                        if (err)
+                            break;
                     }
-                    outBase += total;
                 }
+                if (err)
+                    break;
+                outBase += total;
                 grpSyncG<GS>();
             }
             if (err)
