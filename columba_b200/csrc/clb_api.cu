@@ -151,7 +151,9 @@ template <class K> constexpr bool isStepped(long) { return false; }
 
 // Warp-task functors (K::kWarpTask): a task is run by all 32 lanes of a warp
 // together (K::runWarp); warps claim tasks one at a time from a global counter.
-template <class K, int MINB>
+template <class K> constexpr auto groupOfK(int) -> decltype(K::kGroup) { return K::kGroup; }
+template <class K> constexpr int groupOfK(long) { return 32; }
+template <class K, int MINB, int G>
 __global__ void __launch_bounds__(128, MINB) clb_kernel_warp(const K k, u32 nMax, const u32* __restrict__ nDev, u32* workCtr, const u32* __restrict__ abortWord) {
     if (abortWord && (*abortWord & ERR_ABORT_MASK))
         return; // an earlier stage of this attempt overflowed a list: what follows would read unwritten records
@@ -161,27 +163,28 @@ __global__ void __launch_bounds__(128, MINB) clb_kernel_warp(const K k, u32 nMax
         n = v < nMax ? v : nMax;
     }
     extern __shared__ __align__(16) u8 clb_smem[];
-    const u32 warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const u32 lane = threadIdx.x & 31;
+    // a group is a warp or an aligned part of one (K::kGroup = 8, 16): the groups of a warp claim and run their
+    // tasks independently, every collective below names the group's lanes only
+    const u32 group = (blockIdx.x * blockDim.x + threadIdx.x) / (u32)G;
+    const u32 lane = threadIdx.x & (u32)(G - 1);
+    const unsigned gm = G == 32 ? 0xFFFFFFFFu : (((1u << (G & 31)) - 1u) << ((threadIdx.x & 31u) & ~(u32)(G - 1)));
     typename K::State st;
-    k.begin(st, warp);
+    k.begin(st, group);
     bindSharedOf(k, st, clb_smem, 0);
     for (;;) {
         u32 i = 0;
         if (lane == 0)
             i = atomicAdd(workCtr, 1u);
-        i = __shfl_sync(0xFFFFFFFFu, i, 0);
+        i = __shfl_sync(gm, i, 0, G);
         if (i >= n)
             break;
         k.runWarp(st, i);
-        __syncwarp();
+        __syncwarp(gm);
     }
     k.end(st);
 }
 template <class K> constexpr auto isWarpTask(int) -> decltype(K::kWarpTask) { return K::kWarpTask; }
 template <class K> constexpr bool isWarpTask(long) { return false; }
-template <class K> constexpr auto groupOfK(int) -> decltype(K::kGroup) { return K::kGroup; }
-template <class K> constexpr int groupOfK(long) { return 32; }
 
 // Group-task functors with K::kGroup > 32: a task is run by all threads of a CTA of K::kGroup threads
 // together (the functor's collectives use __syncthreads); CTAs claim tasks one at a time.
@@ -497,6 +500,10 @@ struct CudaBackend {
             fcBytesEnv = atoi(e);
         if (const char* e = getenv("COLUMBA_B200_HEAVY_GROUP"))
             heavyGroup = atoi(e) == 256 ? 256 : 128;
+        if (const char* e = getenv("COLUMBA_B200_SEARCH_GROUP")) {
+            const int v = atoi(e);
+            searchGroup = v == 8 ? 8 : (v == 16 ? 16 : 32);
+        }
         CLB_CUDA(cudaMalloc(&workCtrs, N_CTRS * sizeof(u32)));
         CLB_CUDA(cudaEventCreate(&evBegin));
         CLB_CUDA(cudaEventCreate(&evEnd));
@@ -597,6 +604,11 @@ struct CudaBackend {
     static const int kHeavyGroup = HEAVY_GROUP; // lanes per heavy search task (default)
     int heavyGroup = 128;                       // CTAs of 128 threads, four per SM (COLUMBA_B200_HEAVY_GROUP=256: 256 x 2)
     u32 heavyGroupSize() const { return (u32)heavyGroup; }
+    // lanes per task of the first search launch: a warp, or (COLUMBA_B200_SEARCH_GROUP = 16, 8) half or a quarter
+    // of one -- most levels of a light task hold fewer nodes than a warp has lanes, and the kernel waits on
+    // dependent HBM round trips: smaller groups put 2x / 4x as many tasks in flight with the same registers
+    int searchGroup = 32;
+    u32 searchGroupSize() const { return (u32)searchGroup; }
     // error word of the batch in flight: kernels return at once when an earlier one raised an overflow bit
     const u32* abortWord = nullptr;
     void setAbortWord(const u32* w) { abortWord = w; }
@@ -625,7 +637,8 @@ struct CudaBackend {
             launches++;
             return;
         } else if constexpr (isWarpTask<K>(0))
-            fn = warpOcc == 8 ? clb_kernel_warp<K, 8> : clb_kernel_warp<K, 4>;
+            fn = warpOcc == 8 ? clb_kernel_warp<K, 8, (groupOfK<K>(0) < 32 ? groupOfK<K>(0) : 32)>
+                              : clb_kernel_warp<K, 4, (groupOfK<K>(0) < 32 ? groupOfK<K>(0) : 32)>;
         else if constexpr (isStepped<K>(0))
             fn = clb_kernel_stepped<K>;
         else

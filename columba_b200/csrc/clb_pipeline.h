@@ -358,20 +358,31 @@ template <typename BE> struct Pipeline {
             // one warp per task; a second launch with large scratch takes the tasks whose frontier
             // outgrew the first launch's
             const bool wide = opt.k > BPC<u64>::MAX_ED;
-            const u32 nWarps = be.workers(WK_SEARCH) / be.laneStride();
+            // the first launch runs one task per group of be.searchGroupSize() lanes: a warp, or an aligned half or
+            // quarter of one (the groups of a warp then work on different tasks independently of each other)
+            const u32 sg = be.searchGroupSize();
+            const u32 nGroups = be.workers(WK_SEARCH) / be.laneStride() * (32u / sg);
             const size_t minSlab = ((size_t)(maxLen + 128) * 4 * (P + 2) + 65536 + 255) & ~(size_t)255;
             const size_t sb = tmax<size_t>(searchSlabBytes, minSlab), hb = tmax<size_t>(heavySlabBytes, sb);
             // heavy tasks: one group of BE::kHeavyGroup lanes (a CTA on the GPU) per task
             const u32 nHeavyGroups = tmax<u32>(1u, be.workers(WK_SEARCH_HEAVY) / (be.heavyGroupSize() / 32u * be.laneStride()));
-            bSlabSearch.ensure(be, tmax<size_t>(sb * nWarps, hb * nHeavyGroups));
+            bSlabSearch.ensure(be, tmax<size_t>(sb * nGroups, hb * nHeavyGroups));
             if (wide) {
                 FrontierKernel<u128, 32> k2{ix, dst, B, (u8*)bSlabSearch.p, sb, 0, be.frontierCacheBytes()};
                 be.launch(k2, capTasks, &M->nTasks, WK_SEARCH);
                 FrontierKernel<u128, BE::kHeavyGroup> k2h{ix, dst, B, (u8*)bSlabSearch.p, hb, 1, 0};
                 be.launch(k2h, capTasks, &M->nHeavy, WK_SEARCH_HEAVY);
             } else {
-                FrontierKernel<u64, 32> k2{ix, dst, B, (u8*)bSlabSearch.p, sb, 0, be.frontierCacheBytes()};
-                be.launch(k2, capTasks, &M->nTasks, WK_SEARCH);
+                if (sg == 8) {
+                    FrontierKernel<u64, 8> k2{ix, dst, B, (u8*)bSlabSearch.p, sb, 0, 0};
+                    be.launch(k2, capTasks, &M->nTasks, WK_SEARCH);
+                } else if (sg == 16) {
+                    FrontierKernel<u64, 16> k2{ix, dst, B, (u8*)bSlabSearch.p, sb, 0, 0};
+                    be.launch(k2, capTasks, &M->nTasks, WK_SEARCH);
+                } else {
+                    FrontierKernel<u64, 32> k2{ix, dst, B, (u8*)bSlabSearch.p, sb, 0, be.frontierCacheBytes()};
+                    be.launch(k2, capTasks, &M->nTasks, WK_SEARCH);
+                }
                 bool launched = false;
                 if constexpr (BE::kHeavyGroup > 128) {
                     if (be.heavyGroupSize() == 128) {

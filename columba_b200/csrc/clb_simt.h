@@ -57,20 +57,44 @@ __device__ __forceinline__ u32 grpMax(const LV<u32>& x) {
 }
 __device__ __forceinline__ u32 grpBcast(const LV<u32>& x, int src) { return __shfl_sync(0xFFFFFFFFu, x.v, src); }
 __device__ __forceinline__ u32 atomMinU32(u32* p, u32 v) { return atomicMin(p, v); }
-// The same collectives for a group of GS lanes: GS == 32 is a warp, a larger GS is
-// the whole CTA (blockDim.x == GS), whose collectives go through shared memory and
-// __syncthreads.  A routine written with these runs unchanged with either group.
-template <int GS> __device__ __forceinline__ int grpLaneG() { return GS == 32 ? (int)(threadIdx.x & 31u) : (int)threadIdx.x; }
+// The same collectives for a group of GS lanes.  GS == 32 is a warp.  A larger GS is the whole CTA
+// (blockDim.x == GS), whose collectives go through shared memory and __syncthreads.  A smaller GS (8, 16) is an
+// aligned part of a warp: the warp then runs 32 / GS independent groups, each with its own task and its own
+// control flow; their collectives name only the group's lanes (shuffles of width GS, __syncwarp on the group's
+// mask), so the groups of a warp never wait for each other.  A routine written with these runs unchanged with
+// any group.
+template <int GS> __device__ __forceinline__ int grpLaneG() {
+    return GS > 32 ? (int)threadIdx.x : (int)(threadIdx.x & (u32)((GS < 32 ? GS : 32) - 1));
+}
+template <int GS> __device__ __forceinline__ unsigned grpMaskG() {
+    if (GS >= 32)
+        return 0xFFFFFFFFu;
+    return ((1u << (GS & 31)) - 1u) << ((threadIdx.x & 31u) & ~(u32)((GS & 31) - 1));
+}
 #define CLB_LANES_G(l, GS) for (int l = grpLaneG<GS>(), l##_go = 1; l##_go; l##_go = 0)
 template <int GS> __device__ __forceinline__ void grpSyncG() {
-    if (GS == 32)
-        __syncwarp();
+    if (GS <= 32)
+        __syncwarp(grpMaskG<GS>());
     else
         __syncthreads();
 }
 template <int GS> __device__ __forceinline__ u32 grpExScanG(const LV<u32>& x, LV<u32>& out) {
     if (GS == 32)
         return grpExScan(x, out);
+    if (GS < 32) {
+        constexpr int G = GS < 32 ? GS : 32;
+        const unsigned m = grpMaskG<GS>();
+        const u32 lane = threadIdx.x & (u32)(G - 1);
+        u32 incl = x.v;
+#pragma unroll
+        for (u32 o = 1; o < (u32)G; o <<= 1) {
+            const u32 t = __shfl_up_sync(m, incl, o, G);
+            if (lane >= o)
+                incl += t;
+        }
+        out.v = incl - x.v;
+        return __shfl_sync(m, incl, G - 1, G);
+    }
     __shared__ u32 wsum[GS / 32 + 1];
     const u32 lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     u32 incl = x.v;
@@ -85,7 +109,7 @@ template <int GS> __device__ __forceinline__ u32 grpExScanG(const LV<u32>& x, LV
     __syncthreads();
     u32 before = 0, total = 0;
 #pragma unroll
-    for (u32 w = 0; w < GS / 32; w++) {
+    for (u32 w = 0; w < (u32)(GS / 32 + (GS < 32 ? 1 : 0)); w++) {
         const u32 v = wsum[w];
         before += w < warp ? v : 0u;
         total += v;
@@ -97,6 +121,8 @@ template <int GS> __device__ __forceinline__ u32 grpExScanG(const LV<u32>& x, LV
 template <int GS> __device__ __forceinline__ u32 grpBcastG(const LV<u32>& x, int src) {
     if (GS == 32)
         return grpBcast(x, src);
+    if (GS < 32)
+        return __shfl_sync(grpMaskG<GS>(), x.v, src, GS < 32 ? GS : 32);
     __shared__ u32 slot;
     if ((int)threadIdx.x == src)
         slot = x.v;
@@ -141,10 +167,19 @@ inline u32 grpMax(const LV<u32>& x) {
     return s;
 }
 inline u32 grpBcast(const LV<u32>& x, int src) { return x.v[src]; }
-// the CPU harness always emulates a group of 32 lanes
-#define CLB_LANES_G(l, GS) for (int l = 0; l < GRP; l++)
-template <int GS> inline void grpSyncG() { static_assert(GS == GRP, "the host emulation runs groups of 32 lanes"); }
-template <int GS> inline u32 grpExScanG(const LV<u32>& x, LV<u32>& out) { return grpExScan(x, out); }
+// the CPU harness emulates a group of min(GS, 32) lanes (groups above a warp are emulated by 32 lanes that
+// stride by GS: their chunks then hold GS - 32 empty places, which changes nothing but the work per chunk)
+#define CLB_LANES_G(l, GS) for (int l = 0; l < ((GS) < GRP ? (GS) : GRP); l++)
+template <int GS> inline void grpSyncG() {}
+template <int GS> inline u32 grpExScanG(const LV<u32>& x, LV<u32>& out) {
+    u32 run = 0;
+    for (int l = 0; l < (GS < GRP ? GS : GRP); l++) {
+        const u32 v = x.v[l];
+        out.v[l] = run;
+        run += v;
+    }
+    return run;
+}
 template <int GS> inline u32 grpBcastG(const LV<u32>& x, int src) { return grpBcast(x, src); }
 inline u32 atomMinU32(u32* p, u32 v) {
     const u32 o = *p;
