@@ -34,6 +34,13 @@ CLB_HD int popc64(u64 x) {
     return __builtin_popcountll(x);
 #endif
 }
+CLB_HD int popc32(u32 x) {
+#if defined(__CUDA_ARCH__)
+    return __popc(x);
+#else
+    return __builtin_popcount(x);
+#endif
+}
 CLB_HD int ctz64(u64 x) { // x != 0
 #if defined(__CUDA_ARCH__)
     return __ffsll((long long)x) - 1;

@@ -284,6 +284,7 @@ struct VerifyKernel {
 struct ScreenKernel {
     IndexView ix;
     Batch B;
+    u32 band32; // use the 32-bit band where it fits (clb_verify.h screenStep32)
     static const bool kStepped = true;
     struct State {
         LocalCtr lc;
@@ -296,7 +297,7 @@ struct ScreenKernel {
         }
         finish(st);
     }
-    CLB_HD void start(State& st, u32 i) const { screenStart(ix, B, B.uniq.data[i], st.s); }
+    CLB_HD void start(State& st, u32 i) const { screenStart(ix, B, B.uniq.data[i], st.s, band32 != 0); }
     CLB_HD bool step(State& st) const { return screenStep(ix, st.s); }
     CLB_HD void finish(State& st) const { screenFinish(B, st.s, st.lc); }
     CLB_HD void end(State& st) const { st.lc.flush(B.counters, B.stats); }

@@ -124,8 +124,11 @@ template <typename BE> struct Pipeline {
     u32 dedupProbe = 0;      // batches since dedup was last tried (0: try it in the next batch)
     bool dedupOn = true;     // de-duplication was on in the batch in flight
     std::string lastError;
+    bool screen32 = true;    // screening pass on a 32-bit band where it fits (COLUMBA_B200_SCREEN32=0: 64-bit window)
 
     Pipeline(BE& b) : be(b) {
+        if (const char* e = getenv("COLUMBA_B200_SCREEN32"))
+            screen32 = atoi(e) != 0;
         // test hook: small lists make the overflow / re-run path run on small batches
         if (const char* e = getenv("COLUMBA_B200_MIN_LIST_CAP")) {
             minCap = tmax<u32>(16u, (u32)atoi(e));
@@ -418,7 +421,7 @@ template <typename BE> struct Pipeline {
                 dedupOn = dedupPays || dedupProbe == 0;
                 DedupKernel l2{B, (wide || !dedupOn) ? 0u : 1u};
                 be.launch(l2, capCands, &M->nCands, WK_LIGHT);
-                ScreenKernel l3{ix, B};
+                ScreenKernel l3{ix, B, screen32 ? 1u : 0u};
                 be.launch(l3, capCands, &M->nUniq, WK_LIGHT);
                 be.launch(k3, capCands, &M->nSurv, WK_VERIFY);
             } else {

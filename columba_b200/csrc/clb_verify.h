@@ -488,8 +488,10 @@ struct ScreenState {
     u32 ci, start, size, i, score, mult;
     u32 Wv, firstRow, col, sofc, nw, len;
     u8 maxED, minED, run, considered, ok, done;
+    u8 b32, dB; // 32-bit band (see screenStep32): in use, bit of the main diagonal
     u8 eds[3 * BPC<u64>::MAX_ED + 4];
 };
+enum { SCREEN_ROWS = 8 };
 CLB_HD u32 screenEdAtCol(const ScreenState& s, u32 i) {
     typedef BPC<u64> K;
     const u32 bit = (i % K::BLOCK) + K::DIAG_R0, col = s.col;
@@ -499,7 +501,85 @@ CLB_HD u32 screenEdAtCol(const ScreenState& s, u32 i) {
     const int neg = popc64(s.HN & mask), pos = popc64(s.HP & mask);
     return s.score + ((i > col) ? (u32)(neg - pos) : (u32)(pos - neg));
 }
-CLB_HD void screenStart(const IndexView& ix, const Batch& B, u32 ci, ScreenState& s) {
+// The same recurrence on a 32-bit word that moves with the band.  Bit b of row i is the read position
+// i - 1 - dB + b, i.e. the diagonal b - dB (bit dB = the main diagonal, whose value `score` follows): the band
+// [-Wv, Wh] sits in the middle of the word with mu >= 1 spare columns on its left and R >= 1 on its right, the
+// word moves one column per row (the previous row is re-aligned with a shift by one, the column that enters on
+// the right gets a horizontal delta of +1), the right-most active column stays on its bit.  What the two spare
+// sides compute is not the true matrix, as little as what the 64-bit window computes outside its band: a value
+// that enters the band from the left edge is at least maxED + 2 mu, one from the right edge at least
+// maxED + 2 R + 2, and every cell of the band whose true value is <= maxED + 1 has its optimal path within the
+// diagonals [-Wv - 1, Wh + 1].  The abort decision, the position of the right-most active column and the
+// final-column values <= maxED depend on nothing else, so they equal those of the 64-bit window
+// (bitparallelmatrix.h:352-415) -- at half the instructions per row.  tests/test_prep_unit.py compares the two
+// forms row by row on random and repeat-rich windows.
+CLB_HD u32 screenEdAtCol32(const ScreenState& s, u32 HP, u32 HN, u32 i) {
+    const u32 bit = s.dB, col = s.col;
+    const u32 b = (i > col) ? bit - (i - col) + 1 : bit + 1;
+    const u32 e = (i > col) ? bit + 1 : bit + (col - i) + 1;
+    const u32 mask = ((1u << (e - b)) - 1u) << b;
+    const int neg = popc32(HN & mask), pos = popc32(HP & mask);
+    return s.score + ((i > col) ? (u32)(neg - pos) : (u32)(pos - neg));
+}
+CLB_HD bool screenStep32(const IndexView& ix, ScreenState& s) {
+    typedef BPC<u64> K;
+    PartSeq ps;
+    ps.planes = s.planes;
+    ps.nw = s.nw;
+    ps.base = 0;
+    ps.len = s.len;
+    u32 i = s.i;
+    const u32 last = tmin(s.size, i + SCREEN_ROWS - 1);
+    u32 HP = (u32)s.HP, HN = (u32)s.HN, RAC = (u32)s.RAC;
+    const u32 dB = s.dB, stop = 1u << (dB - s.Wv);
+    for (; i <= last; ++i) {
+        const u32 l = i % K::BLOCK;
+        if (l == 0) {
+            s.tcur = s.tnxt;
+            s.tnxt = textWindow64(ix, s.start + i + K::BLOCK - 1);
+            const i32 w0 = (i32)i - 1 - (i32)dB;
+            s.M0 = seqWindow64(ps, 0, w0);
+            s.M1 = seqWindow64(ps, 1, w0);
+            s.M2 = seqWindow64(ps, 2, w0);
+            s.M3 = seqWindow64(ps, 3, w0);
+        }
+        const u32 Y = (u32)(s.tcur >> (2 * l)) & 3u;
+        const u32 M = (u32)(pickM(s.M0, s.M1, s.M2, s.M3, Y) >> l);
+        const u32 HPa = (HP >> 1) | 0x80000000u, HNa = HN >> 1; // the previous row on this row's columns
+        const u32 D0 = (((M & HPa) + HPa) ^ HPa) | M | HNa;
+        const u32 VP = HNa | ~(D0 | HPa);
+        const u32 VN = D0 & HPa;
+        HP = (VN << 1) | ~(D0 | (VP << 1));
+        HN = D0 & (VP << 1);
+        s.score += ((D0 >> dB) & 1u) ^ 1u;
+        if (!(D0 & RAC)) {
+            u32 val = 1u;
+            while (val > 0) {
+                if (HP & RAC)
+                    val--;
+                if (HN & RAC)
+                    val++;
+                if (RAC == stop) {
+                    s.ok = 0;
+                    break;
+                }
+                RAC >>= 1;
+            }
+        }
+        if (!s.ok)
+            break;
+        if (i >= s.firstRow)
+            s.eds[i - s.firstRow] = (u8)screenEdAtCol32(s, HP, HN, i);
+    }
+    s.HP = HP;
+    s.HN = HN;
+    s.RAC = RAC;
+    s.i = i;
+    if (!s.ok || i > s.size)
+        s.done = 1;
+    return s.done != 0;
+}
+CLB_HD void screenStart(const IndexView& ix, const Batch& B, u32 ci, ScreenState& s, bool screenBand32) {
     typedef BPC<u64> K;
     const Cand c = B.cands.data[ci];
     s.ci = ci;
@@ -542,6 +622,28 @@ CLB_HD void screenStart(const IndexView& ix, const Batch& B, u32 ci, ScreenState
         s.done = 2;
         return;
     }
+    s.b32 = 0;
+    if (screenBand32 && s.Wv + Wh + 1 + 2 <= 32) {
+        // band + at least one column on either side fit a 32-bit word: screenStep32
+        const u32 mu = (32 - (s.Wv + Wh + 1)) / 2;
+        s.b32 = 1;
+        s.dB = (u8)(s.Wv + mu);
+        s.HP = (u64)((~0u) << (s.dB + 1));                       // read positions >= 0: +1 per column
+        s.HN = (u64)((1u << (s.dB + 2 - nZeros)) - 1u);          // left of the free start rows: -1 per column
+        s.RAC = (u64)(1u << (s.dB + Wh));
+        if (s.firstRow == 0)
+            s.eds[0] = (u8)screenEdAtCol32(s, (u32)s.HP, (u32)s.HN, 0);
+        const i32 w0 = -1 - (i32)s.dB;
+        s.M0 = seqWindow64(ps, 0, w0);
+        s.M1 = seqWindow64(ps, 1, w0);
+        s.M2 = seqWindow64(ps, 2, w0);
+        s.M3 = seqWindow64(ps, 3, w0);
+        s.tcur = textWindow64(ix, s.start) << 2;
+        s.tnxt = textWindow64(ix, s.start + K::BLOCK - 1);
+        if (s.size == 0)
+            s.done = 1;
+        return;
+    }
     s.HP = (~0ull) << K::LEFT;
     s.HN = ~s.HP;
     {
@@ -562,11 +664,12 @@ CLB_HD void screenStart(const IndexView& ix, const Batch& B, u32 ci, ScreenState
         s.done = 1;
 }
 // up to SCREEN_ROWS rows; true when the candidate is decided
-enum { SCREEN_ROWS = 8 };
 CLB_HD bool screenStep(const IndexView& ix, ScreenState& s) {
     typedef BPC<u64> K;
     if (s.done)
         return true;
+    if (s.b32)
+        return screenStep32(ix, s);
     PartSeq ps;
     ps.planes = s.planes;
     ps.nw = s.nw;
