@@ -47,7 +47,7 @@ __device__ __forceinline__ auto runOf(const K& k, S& st, u32 i, unsigned act, in
 template <class K, class S> __device__ __forceinline__ void runOf(const K& k, S& st, u32 i, unsigned, long) { k.run(st, i); }
 
 template <class K>
-__global__ void __launch_bounds__(128) clb_kernel(const K k, u32 nMax, const u32* __restrict__ nDev, u32* workCtr, const u32* __restrict__ abortWord) {
+__global__ void __launch_bounds__(128) clb_kernel(const __grid_constant__ K k, u32 nMax, const u32* __restrict__ nDev, u32* workCtr, const u32* __restrict__ abortWord) {
     if (abortWord && (*abortWord & ERR_ABORT_MASK))
         return; // an earlier stage of this attempt overflowed a list: what follows would read unwritten records
     extern __shared__ __align__(16) u8 clb_smem[];
@@ -94,7 +94,7 @@ __global__ void __launch_bounds__(128) clb_kernel(const K k, u32 nMax, const u32
 // lanes keep stepping, so the step loop runs with (almost) full warps even
 // when the tasks differ a lot in their number of steps.
 template <class K>
-__global__ void __launch_bounds__(128) clb_kernel_stepped(const K k, u32 nMax, const u32* __restrict__ nDev, u32* workCtr, const u32* __restrict__ abortWord) {
+__global__ void __launch_bounds__(128) clb_kernel_stepped(const __grid_constant__ K k, u32 nMax, const u32* __restrict__ nDev, u32* workCtr, const u32* __restrict__ abortWord) {
     if (abortWord && (*abortWord & ERR_ABORT_MASK))
         return; // an earlier stage of this attempt overflowed a list: what follows would read unwritten records
     u32 n = nMax;
@@ -154,7 +154,7 @@ template <class K> constexpr bool isStepped(long) { return false; }
 template <class K> constexpr auto groupOfK(int) -> decltype(K::kGroup) { return K::kGroup; }
 template <class K> constexpr int groupOfK(long) { return 32; }
 template <class K, int MINB, int G>
-__global__ void __launch_bounds__(128, MINB) clb_kernel_warp(const K k, u32 nMax, const u32* __restrict__ nDev, u32* workCtr, const u32* __restrict__ abortWord) {
+__global__ void __launch_bounds__(128, MINB) clb_kernel_warp(const __grid_constant__ K k, u32 nMax, const u32* __restrict__ nDev, u32* workCtr, const u32* __restrict__ abortWord) {
     if (abortWord && (*abortWord & ERR_ABORT_MASK))
         return; // an earlier stage of this attempt overflowed a list: what follows would read unwritten records
     u32 n = nMax;
@@ -190,7 +190,7 @@ template <class K> constexpr bool isWarpTask(long) { return false; }
 // together (the functor's collectives use __syncthreads); CTAs claim tasks one at a time.
 static const int HEAVY_GROUP = 256, HEAVY_THREADS_PER_SM = 512;
 template <class K, int THREADS>
-__global__ void __launch_bounds__(THREADS, HEAVY_THREADS_PER_SM / THREADS) clb_kernel_cta(const K k, u32 nMax, const u32* __restrict__ nDev, u32* workCtr, const u32* __restrict__ abortWord) {
+__global__ void __launch_bounds__(THREADS, HEAVY_THREADS_PER_SM / THREADS) clb_kernel_cta(const __grid_constant__ K k, u32 nMax, const u32* __restrict__ nDev, u32* workCtr, const u32* __restrict__ abortWord) {
     if (abortWord && (*abortWord & ERR_ABORT_MASK))
         return; // an earlier stage of this attempt overflowed a list: what follows would read unwritten records
     __shared__ u32 claimed;

@@ -214,11 +214,12 @@ template <typename W, int GS> struct Frontier {
     // the critical path of a level is the pair of rank lookups
     Node* fc[2];
     u32 fcCap;
+    bool prefetch; // ask for the rank records of a surviving child when it is counted (FrontierKernel::prefetch)
 
     CLB_HD Frontier(const IndexView& ix_, const Batch& B_, const DevSearch& s_, const PartInfo& pi_, u32 t_, u32 si,
                     u8* scr_, u32 cap_)
         : ix(ix_), B(B_), s(s_), pi(pi_), t(t_), searchIdx(si), scr(scr_), cap(cap_), top(0), err(0),
-          edit(B_.metric == METRIC_EDIT), nGroups(0), fcCap(0) {
+          edit(B_.metric == METRIC_EDIT), nGroups(0), fcCap(0), prefetch(false) {
         fc[0] = fc[1] = (Node*)0;
         CLB_LANES_G(l, GS) {
             ctr[l].nodes = 0;
@@ -495,6 +496,10 @@ template <typename W, int GS> struct Frontier {
                             if (count) {
                                 S.sv |= 1u << q;
                                 nKids[l]++;
+                                // the rank records this child's own expansion will read, one level from now: asked
+                                // for here, they arrive in the L2 while the level is being stored and re-read
+                                if (prefetch && kind == FK_ALIVE && !(kfl & (FF_CHAIN | FF_USE_SM)))
+                                    prefetchExtend(ix, (int)dir, r);
                                 continue;
                             }
                             Node k;

@@ -132,6 +132,7 @@ template <typename W, int GS> struct FrontierKernel {
     // warp groups on the GPU keep the frontier of the level under expansion in shared memory:
     // two buffers of fcNodes records per warp (fcBytes = the backend's budget per warp)
     u32 fcBytes;
+    u32 prefetch; // L2 prefetch of a surviving child's rank records (Frontier::prefetch)
     CLB_HD u32 fcNodes() const { return GS == 32 ? fcBytes / (2u * (u32)sizeof(FNode<W>)) : 0u; }
     CLB_HD size_t smemBytes(u32 nThreads) const { return (size_t)(nThreads / 32) * 2 * fcNodes() * sizeof(FNode<W>); }
     CLB_HD void bindShared(State& s, u8* smem, u32 tid, u32) const {
@@ -153,6 +154,7 @@ template <typename W, int GS> struct FrontierKernel {
         const PartInfo pi = B.parts.load(task.t, st->P);
         const DevSearch& se = st->sc[pi.scheme].s[task.search];
         Frontier<W, GS> F(ix, B, se, pi, task.t, task.search, s.scr, (u32)slabBytes);
+        F.prefetch = prefetch != 0;
         if (s.fc) {
             F.fc[0] = (FNode<W>*)s.fc;
             F.fc[1] = F.fc[0] + fcNodes();
@@ -228,6 +230,7 @@ struct VerifyKernel {
     u8* wideSlabs;    // Row<u128>[rowsCap] per worker, only when 128-bit matrices can occur
     size_t wideBytes;
     u32 pass;         // 0: all candidates, first centre; 1: the `extra` list, remaining centres
+    u32 band32;       // 32-bit band where it fits (clb_verify.h)
     struct State {
         LocalCtr lc;
         VerifyScratch vs;
@@ -259,6 +262,7 @@ struct VerifyKernel {
         s.vs.rows = wideSlabs ? (void*)(wideSlabs + (size_t)worker * wideBytes) : (void*)0;
         s.vs.rowsCap = rowsCap;
         s.vs.warpMask = 1u;
+        s.vs.band32 = band32;
     }
     // act: the lanes of the warp that run a task in this round
     CLB_HD void run(State& s, u32 i, unsigned act) const {

@@ -124,9 +124,15 @@ template <typename BE> struct Pipeline {
     u32 dedupProbe = 0;      // batches since dedup was last tried (0: try it in the next batch)
     bool dedupOn = true;     // de-duplication was on in the batch in flight
     std::string lastError;
+    bool searchPrefetch = true; // L2 prefetch of the rank records of surviving children (COLUMBA_B200_SEARCH_PREFETCH=0: off)
+    bool verify32 = true;    // the same for the full verification (COLUMBA_B200_VERIFY32=0)
     bool screen32 = true;    // screening pass on a 32-bit band where it fits (COLUMBA_B200_SCREEN32=0: 64-bit window)
 
     Pipeline(BE& b) : be(b) {
+        if (const char* e = getenv("COLUMBA_B200_SEARCH_PREFETCH"))
+            searchPrefetch = atoi(e) != 0;
+        if (const char* e = getenv("COLUMBA_B200_VERIFY32"))
+            verify32 = atoi(e) != 0;
         if (const char* e = getenv("COLUMBA_B200_SCREEN32"))
             screen32 = atoi(e) != 0;
         // test hook: small lists make the overflow / re-run path run on small batches
@@ -371,31 +377,31 @@ template <typename BE> struct Pipeline {
             const u32 nHeavyGroups = tmax<u32>(1u, be.workers(WK_SEARCH_HEAVY) / (be.heavyGroupSize() / 32u * be.laneStride()));
             bSlabSearch.ensure(be, tmax<size_t>(sb * nGroups, hb * nHeavyGroups));
             if (wide) {
-                FrontierKernel<u128, 32> k2{ix, dst, B, (u8*)bSlabSearch.p, sb, 0, be.frontierCacheBytes()};
+                FrontierKernel<u128, 32> k2{ix, dst, B, (u8*)bSlabSearch.p, sb, 0, be.frontierCacheBytes(), searchPrefetch ? 1u : 0u};
                 be.launch(k2, capTasks, &M->nTasks, WK_SEARCH);
-                FrontierKernel<u128, BE::kHeavyGroup> k2h{ix, dst, B, (u8*)bSlabSearch.p, hb, 1, 0};
+                FrontierKernel<u128, BE::kHeavyGroup> k2h{ix, dst, B, (u8*)bSlabSearch.p, hb, 1, 0, searchPrefetch ? 1u : 0u};
                 be.launch(k2h, capTasks, &M->nHeavy, WK_SEARCH_HEAVY);
             } else {
                 if (sg == 8) {
-                    FrontierKernel<u64, 8> k2{ix, dst, B, (u8*)bSlabSearch.p, sb, 0, 0};
+                    FrontierKernel<u64, 8> k2{ix, dst, B, (u8*)bSlabSearch.p, sb, 0, 0, searchPrefetch ? 1u : 0u};
                     be.launch(k2, capTasks, &M->nTasks, WK_SEARCH);
                 } else if (sg == 16) {
-                    FrontierKernel<u64, 16> k2{ix, dst, B, (u8*)bSlabSearch.p, sb, 0, 0};
+                    FrontierKernel<u64, 16> k2{ix, dst, B, (u8*)bSlabSearch.p, sb, 0, 0, searchPrefetch ? 1u : 0u};
                     be.launch(k2, capTasks, &M->nTasks, WK_SEARCH);
                 } else {
-                    FrontierKernel<u64, 32> k2{ix, dst, B, (u8*)bSlabSearch.p, sb, 0, be.frontierCacheBytes()};
+                    FrontierKernel<u64, 32> k2{ix, dst, B, (u8*)bSlabSearch.p, sb, 0, be.frontierCacheBytes(), searchPrefetch ? 1u : 0u};
                     be.launch(k2, capTasks, &M->nTasks, WK_SEARCH);
                 }
                 bool launched = false;
                 if constexpr (BE::kHeavyGroup > 128) {
                     if (be.heavyGroupSize() == 128) {
-                        FrontierKernel<u64, 128> k2s{ix, dst, B, (u8*)bSlabSearch.p, hb, 1, 0};
+                        FrontierKernel<u64, 128> k2s{ix, dst, B, (u8*)bSlabSearch.p, hb, 1, 0, searchPrefetch ? 1u : 0u};
                         be.launch(k2s, capTasks, &M->nHeavy, WK_SEARCH_HEAVY);
                         launched = true;
                     }
                 }
                 if (!launched) {
-                    FrontierKernel<u64, BE::kHeavyGroup> k2h{ix, dst, B, (u8*)bSlabSearch.p, hb, 1, 0};
+                    FrontierKernel<u64, BE::kHeavyGroup> k2h{ix, dst, B, (u8*)bSlabSearch.p, hb, 1, 0, searchPrefetch ? 1u : 0u};
                     be.launch(k2h, capTasks, &M->nHeavy, WK_SEARCH_HEAVY);
                 }
             }
@@ -411,7 +417,7 @@ template <typename BE> struct Pipeline {
             const size_t wb = (size_t)vRows * sizeof(Row<u128>);
             if (wide)
                 bSlabVerifyWide.ensure(be, wb * nw);
-            VerifyKernel k3{ix, B, (u8*)bSlabVerify.p, gb, vRows, ls, wide ? (u8*)bSlabVerifyWide.p : (u8*)0, wb, 0};
+            VerifyKernel k3{ix, B, (u8*)bSlabVerify.p, gb, vRows, ls, wide ? (u8*)bSlabVerifyWide.p : (u8*)0, wb, 0, verify32 ? 1u : 0u};
             if (opt.metric == METRIC_EDIT) {
                 LocateKernel l1{ix, B};
                 be.launch(l1, capCands, &M->nCands, WK_LIGHT);

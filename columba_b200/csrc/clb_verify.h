@@ -124,6 +124,7 @@ struct VerifyScratch {
     u16* ops;     // cigW entries
     u32 rowsCap;
     unsigned warpMask; // lanes of the warp that run a task in this round (1 on the host)
+    u32 band32;        // forward pass and block re-computation on the 32-bit band where it fits (screenStep32)
 };
 
 struct CandSink {
@@ -169,6 +170,18 @@ CLB_HD u64 pickM(u64 m0, u64 m1, u64 m2, u64 m3, u32 y) {
     return (y & 2u) ? b : a;
 }
 CLB_HD u64 bandPack(u64 HP, u64 X, u32 sh) { return (u64)(u32)(HP >> sh) | ((u64)(u32)(X >> sh) << 32); }
+CLB_HD u64 bandPack32(u32 HP, u32 X, u32 sh) { return (u64)(HP >> sh) | ((u64)(X >> sh) << 32); }
+// one row of the 32-bit band that moves with the diagonal (see screenStep32): the previous row (HP, HN) is
+// re-aligned to this row's columns first; returns D0
+CLB_HD u32 bandRow32(u32& HP, u32& HN, u32 M) {
+    const u32 HPa = (HP >> 1) | 0x80000000u, HNa = HN >> 1;
+    const u32 D0 = (((M & HPa) + HPa) ^ HPa) | M | HNa;
+    const u32 VP = HNa | ~(D0 | HPa);
+    const u32 VN = D0 & HPa;
+    HP = (VN << 1) | ~(D0 | (VP << 1));
+    HN = D0 & (VP << 1);
+    return D0;
+}
 
 // 64-bit fast path of verifyWindow: the row state (HP, HN, RAC, score) stays in
 // registers, the four match vectors of the current 32-row block are cut out
@@ -183,7 +196,8 @@ CLB_HD u64 bandPack(u64 HP, u64 X, u32 sh) { return (u64)(u32)(HP >> sh) | ((u64
 template <typename Sink>
 CLB_HD bool verifyWindowFast(const IndexView& ix, const Batch& B, u32 t, const BandStore& bs, u32 start, u32 end,
                              u32 nZeros, u32 maxED, u32 minED, u16* ops, u32 opsCap, LocalCtr& lc, bool& considered,
-                             Sink& sink, unsigned wm, u32 firstCentre, u32 maxCentres, u32& totalCentres, u32 mult) {
+                             Sink& sink, unsigned wm, u32 firstCentre, u32 maxCentres, u32& totalCentres, u32 mult,
+                             bool band32 = false) {
     typedef BPC<u64> K;
     const PartSeq ps = fullSeq(B, t);
     const u32 n = ps.len + 1;
@@ -221,7 +235,69 @@ CLB_HD bool verifyWindowFast(const IndexView& ix, const Batch& B, u32 t, const B
         return score + ((i > col) ? (u32)(neg - pos) : (u32)(pos - neg));
     };
     u32 i = 1;
-    if (run) {
+    // 32-bit band: bit dB = the main diagonal, the band starts at bit mu (screenStep32)
+    const bool b32 = band32 && Wv + Wh + 1 + 2 <= 32;
+    const u32 mu = b32 ? (32 - (Wv + Wh + 1)) / 2 : 0u, dB = Wv + mu;
+    if (run && b32) {
+        u32 hp = (~0u) << (dB + 1), hn = (1u << (dB + 2 - nZeros)) - 1u, rac = 1u << (dB + Wh);
+        const u32 stop = 1u << mu;
+        auto edAtCol32 = [&](u32 r) -> u32 {
+            const u32 b = (r > col) ? dB - (r - col) + 1 : dB + 1;
+            const u32 e = (r > col) ? dB + 1 : dB + (col - r) + 1;
+            const u32 mask = ((1u << (e - b)) - 1u) << b;
+            const int neg = popc32(hn & mask), pos = popc32(hp & mask);
+            return score + ((r > col) ? (u32)(neg - pos) : (u32)(pos - neg));
+        };
+        bs.ring[0] = bandPack32(hp, 0, mu);
+        bs.cp[0] = hp;
+        bs.cp[bs.cpStride] = hn;
+        if (firstRow == 0)
+            eds[0] = (u8)edAtCol32(0);
+        u64 M0 = seqWindow64(ps, 0, -1 - (i32)dB), M1 = seqWindow64(ps, 1, -1 - (i32)dB),
+            M2 = seqWindow64(ps, 2, -1 - (i32)dB), M3 = seqWindow64(ps, 3, -1 - (i32)dB);
+        u64 tcur = textWindow64(ix, start) << 2, tnxt = textWindow64(ix, start + K::BLOCK - 1);
+        bool ok = true;
+        for (i = 1; i <= size; ++i) {
+            const u32 l = i % K::BLOCK;
+            if (l == 0) {
+                tcur = tnxt;
+                tnxt = textWindow64(ix, start + i + K::BLOCK - 1);
+                const i32 w0 = (i32)i - 1 - (i32)dB;
+                M0 = seqWindow64(ps, 0, w0);
+                M1 = seqWindow64(ps, 1, w0);
+                M2 = seqWindow64(ps, 2, w0);
+                M3 = seqWindow64(ps, 3, w0);
+                const u32 b = i / K::BLOCK; // the row before the block, on its own columns
+                bs.cp[(size_t)(2 * b) * bs.cpStride] = hp;
+                bs.cp[(size_t)(2 * b + 1) * bs.cpStride] = hn;
+            }
+            const u32 Y = (u32)(tcur >> (2 * l)) & 3u;
+            const u32 M = (u32)(pickM(M0, M1, M2, M3, Y) >> l);
+            const u32 D0 = bandRow32(hp, hn, M);
+            score += ((D0 >> dB) & 1u) ^ 1u;
+            if (!(D0 & rac)) {
+                u32 val = 1u;
+                while (val > 0) {
+                    if (hp & rac)
+                        val--;
+                    if (hn & rac)
+                        val++;
+                    if (rac == stop) {
+                        ok = false;
+                        break;
+                    }
+                    rac >>= 1;
+                }
+            }
+            if (!ok)
+                break;
+            bs.ring[(size_t)l * bs.ringStride] = bandPack32(hp, M | ~D0, mu);
+            if (i >= firstRow)
+                eds[i - firstRow] = (u8)edAtCol32(i);
+        }
+        if (firstCentre == 0)
+            lc.s[ST_VERIFY_ROWS] += (i <= size) ? i : size;
+    } else if (run) {
         bs.ring[0] = bandPack(HP, 0, sh0);
         bs.cp[0] = HP;
         bs.cp[bs.cpStride] = HN;
@@ -324,7 +400,27 @@ CLB_HD bool verifyWindowFast(const IndexView& ix, const Batch& B, u32 t, const B
             started = true;
         }
         const u32 cb = ti / K::BLOCK;
-        if (cb != ringBlock) {
+        if (cb != ringBlock && b32) {
+            // rows of block cb again, from its checkpoint
+            u32 hp = (u32)bs.cp[(size_t)(2 * cb) * bs.cpStride], hn = (u32)bs.cp[(size_t)(2 * cb + 1) * bs.cpStride];
+            const i32 w0 = (i32)(cb * K::BLOCK) - 1 - (i32)dB;
+            const u64 R0 = seqWindow64(ps, 0, w0), R1 = seqWindow64(ps, 1, w0), R2 = seqWindow64(ps, 2, w0),
+                      R3 = seqWindow64(ps, 3, w0);
+            u32 i0 = cb * K::BLOCK;
+            if (cb == 0) {
+                bs.ring[0] = bandPack32(hp, 0, mu);
+                i0 = 1;
+            }
+            const u32 i1 = tmin(cb * K::BLOCK + K::BLOCK - 1, lastRow);
+            const u64 tw = (cb == 0) ? textWindow64(ix, start) << 2 : textWindow64(ix, start + cb * K::BLOCK - 1);
+            for (u32 q = i0; q <= i1; q++) {
+                const u32 l = q % K::BLOCK;
+                const u32 M = (u32)(pickM(R0, R1, R2, R3, (u32)(tw >> (2 * l)) & 3u) >> l);
+                const u32 D0 = bandRow32(hp, hn, M);
+                bs.ring[(size_t)l * bs.ringStride] = bandPack32(hp, M | ~D0, mu);
+            }
+            ringBlock = cb;
+        } else if (cb != ringBlock) {
             // rows of block cb again, from its checkpoint
             u64 hp = bs.cp[(size_t)(2 * cb) * bs.cpStride], hn = bs.cp[(size_t)(2 * cb + 1) * bs.cpStride];
             const u64 R0 = matchVec<u64>(ps, cb, 0), R1 = matchVec<u64>(ps, cb, 1), R2 = matchVec<u64>(ps, cb, 2),
@@ -459,7 +555,7 @@ CLB_HD void verifyEditTask(const IndexView& ix, const Batch& B, u32 ci, VerifySc
     if (fast) {
         u32 total = 0;
         ok = verifyWindowFast(ix, B, c.t, vs.bs, start, end, nZeros, maxED, minED, vs.ops, B.cigW, lc, considered,
-                              sink, fm, first, pass == 0 ? 1u : 0xFFFFu, total, mult);
+                              sink, fm, first, pass == 0 ? 1u : 0xFFFFu, total, mult, vs.band32 != 0);
         if (pass == 0 && total > 1)
             B.extra.push(ci, B.err, ERR_CAND_OVERFLOW);
     } else { // (mult is 1: no grouping when 128-bit matrices can occur)

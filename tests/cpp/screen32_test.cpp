@@ -4,7 +4,9 @@
 // abort at the same row, keep the right-most active column on the same
 // diagonal after every step, give the same final-column values wherever one of
 // them is <= maxED + 1 (and values above that in the other), and take the same
-// survivor decision with the same counters.  Windows: true positions with
+// survivor decision with the same counters; the survivors then go through the
+// full verification (verifyWindowFast) in both forms, which must report the same
+// alignments with the same CIGAR strings.  Windows: true positions with
 // shifted starts, junk positions, tandem repeats, homopolymers, the end of the
 // text; reads with N; fixed and free start; maxED 0..7.
 // Compiled with g++ (the kernel functors are host-callable).
@@ -33,6 +35,18 @@ static u32 rnd() {
             return 1;                                                                                         \
         }                                                                                                     \
     } while (0)
+
+struct HitLog {
+    std::vector<u32> v;
+    void operator()(const VerifyHit& h, const u16* ops) {
+        v.push_back(h.b);
+        v.push_back(h.e);
+        v.push_back(h.dist);
+        v.push_back(h.ncig);
+        for (u32 i = 0; i < h.ncig && h.ncig != 0xFFFFFFFFu; i++)
+            v.push_back(ops[i]);
+    }
+};
 
 int main(int argc, char** argv) {
     const u32 nReads = argc > 1 ? (u32)atoi(argv[1]) : 6000;
@@ -150,7 +164,7 @@ int main(int argc, char** argv) {
     B.candMult = mult.data();
     std::vector<u32> survA(nC), survB(nC);
     u32 nA = 0, nB = 0, errA = 0, errB = 0;
-    u64 aborted = 0, survivors = 0, used32 = 0, rows = 0;
+    u64 aborted = 0, survivors = 0, used32 = 0, rows = 0, hits = 0;
     for (u32 ci = 0; ci < nC; ci++) {
         const Cand c = cands[ci];
         const u32 start = starts[ci];
@@ -209,20 +223,49 @@ int main(int argc, char** argv) {
         CHECK(la.c[IN_TEXT_STARTED] == lb.c[IN_TEXT_STARTED]);
         CHECK(la.c[ABORTED_IN_TEXT_VERIF] == lb.c[ABORTED_IN_TEXT_VERIF]);
         CHECK(la.s[ST_VERIFY_ROWS] == lb.s[ST_VERIFY_ROWS]);
+        // the full verification (forward pass with band storage, traceback with block re-computation) in both forms
+        if (nA != beforeA && a.done != 2) {
+            const u32 nZeros = c.fixedStart ? 1u : 2 * (u32)c.maxED + 1;
+            const u32 len = seqLen(B, c.t);
+            const u32 nRows = nZeros - 1 + c.maxED + len + 1;
+            const u32 end = tmin(ix.textLength - 1, start + nRows - 1);
+            u64 ring[2][32], cp[2][2 * 16];
+            u16 ops[2][64];
+            HitLog hl[2];
+            LocalCtr lv[2];
+            bool cons[2], okv[2];
+            u32 tot[2];
+            for (u32 f = 0; f < 2; f++) {
+                BandStore bs;
+                bs.ring = ring[f];
+                bs.ringStride = 1;
+                bs.cp = cp[f];
+                bs.cpStride = 1;
+                bs.cpCap = 16;
+                lv[f].clear();
+                okv[f] = verifyWindowFast(ix, B, c.t, bs, start, end, nZeros, c.maxED, c.minED, ops[f], 2 * (u32)c.maxED + 2,
+                                          lv[f], cons[f], hl[f], 1u, 0, 0xFFFFu, tot[f], 1, f == 0);
+            }
+            CHECK(okv[0] == okv[1] && cons[0] == cons[1] && tot[0] == tot[1]);
+            CHECK(hl[0].v == hl[1].v);
+            CHECK(lv[0].c[CIGARS_IN_TEXT_VERIFICATION] == lv[1].c[CIGARS_IN_TEXT_VERIFICATION]);
+            CHECK(lv[0].s[ST_VERIFY_ROWS] == lv[1].s[ST_VERIFY_ROWS]);
+            hits += hl[0].v.size() ? 1 : 0;
+        }
     }
     for (u32 i = 0; i < nA; i++)
         if (survA[i] != survB[i]) {
             std::printf("FAILED survivor lists differ at %u\n", i);
             return 1;
         }
-    if (used32 * 2 < nC || survivors == 0 || aborted == 0) {
+    if (used32 * 2 < nC || survivors == 0 || aborted == 0 || hits * 4 < survivors) {
         std::printf("FAILED the test does not exercise what it should: %llu of %u on the 32-bit band, %llu survivors, %llu aborted\n",
                     (unsigned long long)used32, nC, (unsigned long long)survivors, (unsigned long long)aborted);
         return 1;
     }
-    std::fprintf(stderr, "%u candidates, %llu on the 32-bit band, %llu aborted, %llu survivors, %llu rows\n", nC,
+    std::fprintf(stderr, "%u candidates, %llu on the 32-bit band, %llu aborted, %llu survivors (%llu verified with hits), %llu rows\n", nC,
                  (unsigned long long)used32, (unsigned long long)aborted, (unsigned long long)survivors,
-                 (unsigned long long)rows);
+                 (unsigned long long)hits, (unsigned long long)rows);
     std::printf("OK\n");
     return 0;
 }
