@@ -189,8 +189,8 @@ template <class K> constexpr bool isWarpTask(long) { return false; }
 // Group-task functors with K::kGroup > 32: a task is run by all threads of a CTA of K::kGroup threads
 // together (the functor's collectives use __syncthreads); CTAs claim tasks one at a time.
 static const int HEAVY_GROUP = 256, HEAVY_THREADS_PER_SM = 512;
-template <class K, int THREADS>
-__global__ void __launch_bounds__(THREADS, HEAVY_THREADS_PER_SM / THREADS) clb_kernel_cta(const __grid_constant__ K k, u32 nMax, const u32* __restrict__ nDev, u32* workCtr, const u32* __restrict__ abortWord) {
+template <class K, int THREADS, int PER_SM>
+__global__ void __launch_bounds__(THREADS, PER_SM / THREADS) clb_kernel_cta(const __grid_constant__ K k, u32 nMax, const u32* __restrict__ nDev, u32* workCtr, const u32* __restrict__ abortWord) {
     if (abortWord && (*abortWord & ERR_ABORT_MASK))
         return; // an earlier stage of this attempt overflowed a list: what follows would read unwritten records
     __shared__ u32 claimed;
@@ -496,10 +496,10 @@ struct CudaBackend {
         stream = ownStream;
         if (const char* e = getenv("COLUMBA_B200_SEARCH_OCC"))
             warpOcc = atoi(e) == 4 ? 4 : 8;
-        if (const char* e = getenv("COLUMBA_B200_FRONTIER_SMEM"))
-            fcBytesEnv = atoi(e);
         if (const char* e = getenv("COLUMBA_B200_HEAVY_GROUP"))
             heavyGroup = atoi(e) == 256 ? 256 : 128;
+        if (const char* e = getenv("COLUMBA_B200_HEAVY_PER_SM"))
+            heavyPerSM = atoi(e) == 1024 ? 1024 : HEAVY_THREADS_PER_SM;
         if (const char* e = getenv("COLUMBA_B200_SEARCH_GROUP")) {
             const int v = atoi(e);
             searchGroup = v == 8 ? 8 : (v == 16 ? 16 : 32);
@@ -595,7 +595,7 @@ struct CudaBackend {
     u32 blocksFor(int kind) const {
         switch (kind) {
         case WK_SEARCH: return (u32)numSMs * (warpOcc == 8 ? 8u : 4u); // x128 threads, one task per warp
-        case WK_SEARCH_HEAVY: return (u32)numSMs * (u32)(HEAVY_THREADS_PER_SM / heavyGroup); // CTAs of heavyGroup threads
+        case WK_SEARCH_HEAVY: return (u32)numSMs * (u32)(heavyPerSM / heavyGroup); // CTAs of heavyGroup threads
         case WK_VERIFY: return (u32)numSMs * 8;
         case WK_FILTER: return (u32)numSMs * 4;
         default: return (u32)numSMs * 16;
@@ -604,6 +604,9 @@ struct CudaBackend {
     static const int kHeavyGroup = HEAVY_GROUP; // lanes per heavy search task (default)
     int heavyGroup = 128;                       // CTAs of 128 threads, four per SM (COLUMBA_B200_HEAVY_GROUP=256: 256 x 2)
     u32 heavyGroupSize() const { return (u32)heavyGroup; }
+    // resident threads per SM of the heavy launch: 512 (128 registers per thread) or, with
+    // COLUMBA_B200_HEAVY_PER_SM=1024, 1024 (64 registers): twice the tasks in flight
+    int heavyPerSM = HEAVY_THREADS_PER_SM;
     // lanes per task of the first search launch: a warp, or (COLUMBA_B200_SEARCH_GROUP = 16, 8) half or a quarter
     // of one -- most levels of a light task hold fewer nodes than a warp has lanes, and the kernel waits on
     // dependent HBM round trips: smaller groups put 2x / 4x as many tasks in flight with the same registers
@@ -612,14 +615,10 @@ struct CudaBackend {
     // error word of the batch in flight: kernels return at once when an earlier one raised an overflow bit
     const u32* abortWord = nullptr;
     void setAbortWord(const u32* w) { abortWord = w; }
-    // Resident CTAs per SM of the warp-per-task search launch: 8 (64 registers per thread; the kernel waits on
-    // dependent HBM round trips, more resident warps hide more of them) or, with COLUMBA_B200_SEARCH_OCC=4, 4 (120
-    // registers).  COLUMBA_B200_FRONTIER_SMEM = bytes of shared-memory frontier buffers per warp; 0 by default: on
-    // the 3.1 Gbp workload staging the frontier on chip made the search 10 % slower (profiles/r2k_*: the buffers take
-    // their 192 KB from the L1 that serves the rank records and the read's bit planes, and every child is stored twice)
+    // Resident CTAs per SM of the warp-per-task search launch: 8 (64 registers per thread) or, with
+    // COLUMBA_B200_SEARCH_OCC=4, 4 (120 registers); 8 measured faster (profiles/r2k_*).  Staging the frontier of the
+    // level under expansion in shared memory was built, measured 10 % slower (same profiles) and removed.
     int warpOcc = 8;
-    int fcBytesEnv = -1;
-    u32 frontierCacheBytes() const { return fcBytesEnv >= 0 ? (u32)fcBytesEnv : 0u; }
     u32 workers(int kind) { return blocksFor(kind) * (kind == WK_SEARCH_HEAVY ? (u32)heavyGroup : 128u); }
     u32 laneStride() const { return 32; }
     u32 fallbackWorkers() const { return 0; }
@@ -632,7 +631,10 @@ struct CudaBackend {
             static_assert(G == 256 || G == 128, "CTA size of the group-task launcher");
             if (nextCtr >= N_CTRS)
                 throw BackendError("work counter pool exhausted");
-            clb_kernel_cta<K, G><<<(u32)numSMs * (u32)(HEAVY_THREADS_PER_SM / G), G, 0, stream>>>(k, nMax, nDev, workCtrs + nextCtr++, abortWord);
+            if (heavyPerSM == 1024)
+                clb_kernel_cta<K, G, 1024><<<(u32)numSMs * (u32)(1024 / G), G, 0, stream>>>(k, nMax, nDev, workCtrs + nextCtr++, abortWord);
+            else
+                clb_kernel_cta<K, G, HEAVY_THREADS_PER_SM><<<(u32)numSMs * (u32)(HEAVY_THREADS_PER_SM / G), G, 0, stream>>>(k, nMax, nDev, workCtrs + nextCtr++, abortWord);
             CLB_CUDA(cudaGetLastError());
             launches++;
             return;

@@ -60,11 +60,11 @@ template <typename W> struct RowS {
 // recurrences on a sliding window of WORD columns; rows of a block of BLOCK
 // rows share the window).  Returns false when no cell of the row is within the
 // bound (the right-most active column RAC ran out of the band).
+// M = match vector of the row's character within the window of the row's block
 template <typename W>
-CLB_HD bool rowStep(const MatGeom& g, const PartSeq& ps, const RowS<W>& p, u32 i, u32 Y, RowS<W>& o) {
+CLB_HD bool rowStepM(const MatGeom& g, const RowS<W>& p, u32 i, W M, RowS<W>& o) {
     typedef BPC<W> K;
-    const u32 b = i / K::BLOCK, l = i % K::BLOCK;
-    const W M = matchVec<W>(ps, b, Y);
+    const u32 l = i % K::BLOCK;
     W HP = p.HP, HN = p.HN, RAC = p.RAC << 1u;
     if (l == 0) {
         HP >>= K::BLOCK;
@@ -98,6 +98,10 @@ CLB_HD bool rowStep(const MatGeom& g, const PartSeq& ps, const RowS<W>& p, u32 i
     o.HN = HN;
     o.RAC = RAC;
     return ok;
+}
+template <typename W>
+CLB_HD bool rowStep(const MatGeom& g, const PartSeq& ps, const RowS<W>& p, u32 i, u32 Y, RowS<W>& o) {
+    return rowStepM<W>(g, p, i, matchVec<W>(ps, i / BPC<W>::BLOCK, Y), o);
 }
 // value of cell (i, j) from the row's horizontal deltas
 template <typename W> CLB_HD u32 cellAt(const RowS<W>& r, u32 i, u32 j) {
@@ -208,19 +212,11 @@ template <typename W, int GS> struct Frontier {
     FGroup grp[MAXP];
     u32 nGroups;
     LV<FCounters> ctr;
-    // on-chip copy of the frontier (warp groups on the GPU): the first fcCap nodes of the level that is being
-    // expanded are read from fc[level & 1], the first fcCap children go to fc[(level + 1) & 1] as well as to the
-    // node array in HBM (which the ranking and the cluster walks use later), so that the only HBM round trip on
-    // the critical path of a level is the pair of rank lookups
-    Node* fc[2];
-    u32 fcCap;
-    bool prefetch; // ask for the rank records of a surviving child when it is counted (FrontierKernel::prefetch)
 
     CLB_HD Frontier(const IndexView& ix_, const Batch& B_, const DevSearch& s_, const PartInfo& pi_, u32 t_, u32 si,
                     u8* scr_, u32 cap_)
         : ix(ix_), B(B_), s(s_), pi(pi_), t(t_), searchIdx(si), scr(scr_), cap(cap_), top(0), err(0),
-          edit(B_.metric == METRIC_EDIT), nGroups(0), fcCap(0), prefetch(false) {
-        fc[0] = fc[1] = (Node*)0;
+          edit(B_.metric == METRIC_EDIT), nGroups(0) {
         CLB_LANES_G(l, GS) {
             ctr[l].nodes = 0;
             ctr[l].lookups = 0;
@@ -383,7 +379,21 @@ template <typename W, int GS> struct Frontier {
         u32 b0 = 0, b1 = G.nPI, level = 0;
         lvl[0] = 0;
         lvl[1] = b1;
+        // Every node of a level sits on the same row of its instance's matrix (the roots are level 0), all
+        // instances of the group lay the same part along the columns, and the match vectors of a character are
+        // cut per block of BLOCK rows: the four vectors that the rows of this level's children need are the same
+        // for every node of the level and change once per BLOCK levels.  They are cut out of the read's bit
+        // planes here, once, instead of once per child and pass.
+        W M0 = W(0), M1 = W(0), M2 = W(0), M3 = W(0);
+        u32 mBlock = F_NONE;
         while (b1 > b0 && !err) {
+            if ((edit || level == 0) && (level + 1) / BPC<W>::BLOCK != mBlock) {
+                mBlock = (level + 1) / BPC<W>::BLOCK;
+                M0 = matchVec<W>(ps, mBlock, 0);
+                M1 = matchVec<W>(ps, mBlock, 1);
+                M2 = matchVec<W>(ps, mBlock, 2);
+                M3 = matchVec<W>(ps, mBlock, 3);
+            }
             u32 outBase = b1; // children are appended to the node array
             for (u32 base = b0; base < b1 && !err; base += GS) {
                 LV<u32> nKids, off;
@@ -401,7 +411,7 @@ template <typename W, int GS> struct Frontier {
                             const u32 i = base + (u32)l;
                             if (i >= b1)
                                 continue;
-                            const Node x = (level > 0 && i - b0 < fcCap) ? fc[level & 1u][i - b0] : nodes[i];
+                            const Node x = nodes[i];
                             if (x.kind() != FK_ALIVE)
                                 continue;
                             const FPI* P = pisOf(G) + x.pi;
@@ -452,12 +462,13 @@ template <typename W, int GS> struct Frontier {
                             rs.score = 0;
                             u32 kind, ked = F_ED_NONE, kfl = 0;
                             if (chain || edit) {
-                                if (!chain && row >= P.g.m) {
+                                if ((!chain && row >= P.g.m) || row != level + 1) {
                                     if (count)
                                         atomOr(B.err, ERR_INTERNAL);
                                     continue;
                                 }
-                                const bool valid = rowStep<W>(P.g, ps, S.prs, row, cc, rs);
+                                const W Mlo = (cc & 1u) ? M1 : M0, Mhi = (cc & 1u) ? M3 : M2;
+                                const bool valid = rowStepM<W>(P.g, S.prs, row, (cc & 2u) ? Mhi : Mlo, rs);
                                 if (count)
                                     ctr[l].rows++;
                                 kind = classify(P.g, rs, valid, row, chain ? 0xFFFFFFFFu : r.width(), chain, idx, ked);
@@ -496,10 +507,6 @@ template <typename W, int GS> struct Frontier {
                             if (count) {
                                 S.sv |= 1u << q;
                                 nKids[l]++;
-                                // the rank records this child's own expansion will read, one level from now: asked
-                                // for here, they arrive in the L2 while the level is being stored and re-read
-                                if (prefetch && kind == FK_ALIVE && !(kfl & (FF_CHAIN | FF_USE_SM)))
-                                    prefetchExtend(ix, (int)dir, r);
                                 continue;
                             }
                             Node k;
@@ -516,8 +523,6 @@ template <typename W, int GS> struct Frontier {
                             k.setMeta(cc & 3u, kind, kfl, ked);
                             // the node array of the group is the last allocation: it grows in place
                             nodes[at] = k;
-                            if (at - b1 < fcCap)
-                                fc[(level + 1u) & 1u][at - b1] = k;
                             at++;
                         }
                     }
@@ -532,6 +537,163 @@ template <typename W, int GS> struct Frontier {
                 }
                 if (err)
                     break;
+                outBase += total;
+                grpSyncG<GS>();
+            }
+            if (err)
+                break;
+            level++;
+            if (level + 1 >= lvlCap) {
+                err |= ERR_INTERNAL;
+                break;
+            }
+            b0 = b1;
+            b1 = outBase;
+            lvl[level + 1] = b1;
+        }
+        G.nNodes = b1;
+        G.nLevels = level + 1; // levels 0 .. level, lvl[level+1] = number of nodes
+    }
+
+    // The same expansion for groups of at most a warp, with one lane per (node, child) pair: lane l of a chunk
+    // takes the child q = l % 4 (in the reference's order T, G, C, A) of the node base + l / 4.  The light tasks
+    // that warps run have narrow levels (ncu: 9.5 of 32 lanes had a node, 5.9 a child to compute, and half of
+    // the kernel's issue slots were in use): with a lane per pair a level of up to GS / 4 nodes computes all its
+    // children's matrix rows in ONE pass over the loop body instead of four, every lane holds exactly one
+    // child, so the record stays in registers between the prefix sum and the store -- no second pass that
+    // builds the rows again -- and the prefix sum over the lanes is the depth-first order as before.  The four
+    // lanes of a node read the same two rank records (one L1 request) and keep the child of their character.
+    CLB_HD void expandGroupPairs(FGroup& G, const PartSeq& ps) {
+        const u32 idx = G.idx, dir = s.dir[idx], uni = s.isUniBack(idx) ? 1u : 0u, maxED = s.U[idx];
+        const u32 part = s.order[idx];
+        constexpr u32 NS = (u32)GS / 4u; // nodes per chunk
+        Node* nodes = nodesOf(G);
+        u32* lvl = lvlOf(G);
+        const u32 lvlCap = maxRows() + 2;
+        u32 b0 = 0, b1 = G.nPI, level = 0;
+        lvl[0] = 0;
+        lvl[1] = b1;
+        W M0 = W(0), M1 = W(0), M2 = W(0), M3 = W(0); // match vectors of the level's row (see expandGroup)
+        u32 mBlock = F_NONE;
+        while (b1 > b0 && !err) {
+            if ((edit || level == 0) && (level + 1) / BPC<W>::BLOCK != mBlock) {
+                mBlock = (level + 1) / BPC<W>::BLOCK;
+                M0 = matchVec<W>(ps, mBlock, 0);
+                M1 = matchVec<W>(ps, mBlock, 1);
+                M2 = matchVec<W>(ps, mBlock, 2);
+                M3 = matchVec<W>(ps, mBlock, 3);
+            }
+            u32 outBase = b1;
+            for (u32 base = b0; base < b1 && !err; base += NS) {
+                LV<u32> has, off;
+                LV<Node> kid;
+                CLB_LANES_G(l, GS) {
+                    has[l] = 0;
+                    const u32 i = base + ((u32)l >> 2), q = (u32)l & 3u;
+                    if (i >= b1)
+                        continue;
+                    const Node x = nodes[i];
+                    if (x.kind() != FK_ALIVE)
+                        continue;
+                    const FPI& P = pisOf(G)[x.pi];
+                    const u32 row = (u32)x.row + 1;
+                    const bool chain = (x.flags() & FF_CHAIN) != 0;
+                    RangePair r;
+                    u32 cc;
+                    if (chain) {
+                        // the next node is the next descendant handed over by the previous phase
+                        if (q != 0)
+                            continue;
+                        const FDesc d = ((const FDesc*)(scr + P.descOff))[x.row];
+                        r = d.r;
+                        cc = d.c;
+                    } else {
+                        // extendFMPos: all four children with two rank lookups, this lane keeps its own
+                        RangePair ch[4];
+                        const RangePair parentRange = (x.flags() & FF_USE_SM) ? P.sm.r : x.r;
+                        extendAll(ix, (int)dir, uni != 0, parentRange, ch);
+                        if (q == 0)
+                            ctr[l].lookups += 2;
+                        cc = 3u - q;
+                        r = pick4(ch, cc);
+                        if (r.empty())
+                            continue;
+                        ctr[l].nodes++;
+                    }
+                    RowS<W> rs;
+                    rs.HP = rs.HN = rs.RAC = W(0);
+                    rs.score = 0;
+                    u32 kind, ked = F_ED_NONE, kfl = 0;
+                    if (chain || edit) {
+                        if ((!chain && row >= P.g.m) || row != level + 1) {
+                            atomOr(B.err, ERR_INTERNAL);
+                            continue;
+                        }
+                        RowS<W> prs;
+                        prs.HP = x.HP;
+                        prs.HN = x.HN;
+                        prs.RAC = x.RAC;
+                        prs.score = x.score;
+                        const W Mlo = (cc & 1u) ? M1 : M0, Mhi = (cc & 1u) ? M3 : M2;
+                        const bool valid = rowStepM<W>(P.g, prs, row, (cc & 2u) ? Mhi : Mlo, rs);
+                        ctr[l].rows++;
+                        kind = classify(P.g, rs, valid, row, chain ? 0xFFFFFFFFu : r.width(), chain, idx, ked);
+                        if (kind == 0xFFu)
+                            continue;
+                        if (chain) {
+                            kfl = FF_FROM_CHAIN;
+                            if (kind == FK_ALIVE) {
+                                if (row < P.nDesc) {
+                                    kfl |= FF_CHAIN;
+                                } else if (P.nDesc == P.g.m - 1) {
+                                    kind = FK_DEAD; // the last descendant sits on the last row
+                                } else if (s.dsw[idx]) {
+                                    kfl |= FF_USE_SM; // after a switch the children come from the start range
+                                }
+                            }
+                        }
+                    } else { // recApproxMatchHamming, src/indexinterface.cpp:1211-1304
+                        if (r.width() <= ix.switchPoint) {
+                            kind = FK_IT;
+                            rs.score = x.score;
+                        } else {
+                            const u32 v = x.score + ((cc != partChar(part, dir, row - 1)) ? 1u : 0u);
+                            rs.score = v;
+                            if (v > maxED)
+                                continue;
+                            if (row == ps.len) {
+                                if (v < s.L[idx])
+                                    continue;
+                                kind = FK_HAM_END;
+                            } else {
+                                kind = FK_ALIVE;
+                            }
+                        }
+                    }
+                    Node& k = kid[l];
+                    k.r = r;
+                    k.HP = rs.HP;
+                    k.HN = rs.HN;
+                    k.RAC = rs.RAC;
+                    k.score = rs.score;
+                    k.parent = i;
+                    k.cnt = chain ? (kind == FK_GD ? 1u : 0u) : (kind != FK_ALIVE ? 1u : 0u);
+                    k.base = 0;
+                    k.pi = x.pi;
+                    k.row = (u16)row;
+                    k.setMeta(cc & 3u, kind, kfl, ked);
+                    has[l] = 1;
+                }
+                const u32 total = grpExScanG<GS>(has, off);
+                if (!total)
+                    continue;
+                (void)alloc((size_t)total * sizeof(Node)); // the node array of the group is the last allocation
+                if (err)
+                    break;
+                CLB_LANES_G(l, GS) {
+                    if (has[l])
+                        nodes[outBase + off[l]] = kid[l];
+                }
                 outBase += total;
                 grpSyncG<GS>();
             }
@@ -1310,7 +1472,10 @@ template <typename W, int GS> struct Frontier {
             FGroup& G = grp[nGroups - 1];
             const PartSeq ps = partSeq(s.order[G.idx], s.dir[G.idx]);
             initGroup(G, ps);
-            expandGroup(G, ps);
+            if (GS <= 32)
+                expandGroupPairs(G, ps);
+            else
+                expandGroup(G, ps);
             if (err)
                 return false;
             rankLeaves(G);

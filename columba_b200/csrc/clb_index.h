@@ -139,20 +139,6 @@ CLB_HD void extendAll(const IndexView& ix, int dir, bool uniBack, const RangePai
         }
     }
 }
-// L2 prefetch of the one or two rank records that extendAll(ix, dir, ., p, .) will read
-CLB_HD void prefetchExtend(const IndexView& ix, int dir, const RangePair& p) {
-#if defined(__CUDA_ARCH__)
-    const BwtRec* rec = (dir == DIR_BWD) ? ix.fwd.rec : ix.rev.rec;
-    const Range t = (dir == DIR_BWD) ? p.sa : p.rev;
-    asm volatile("prefetch.global.L2 [%0];" ::"l"(rec + (t.b >> 6)));
-    if ((t.b >> 6) != (t.e >> 6))
-        asm volatile("prefetch.global.L2 [%0];" ::"l"(rec + (t.e >> 6)));
-#else
-    (void)ix;
-    (void)dir;
-    (void)p;
-#endif
-}
 // single character (code 0..3) -- indexinterface.cpp:1034-1049 (addChar).
 // Written without branches on dir / uniBack / c: the lanes of a warp extend
 // different parts in different directions in the same instruction stream.

@@ -127,19 +127,8 @@ template <typename W, int GS> struct FrontierKernel {
         LV<u64> started, immediate;
         u64 tasks;
         u8* scr;
-        u8* fc; // on-chip frontier buffers of this warp (null: none)
     };
-    // warp groups on the GPU keep the frontier of the level under expansion in shared memory:
-    // two buffers of fcNodes records per warp (fcBytes = the backend's budget per warp)
-    u32 fcBytes;
-    u32 prefetch; // L2 prefetch of a surviving child's rank records (Frontier::prefetch)
-    CLB_HD u32 fcNodes() const { return GS == 32 ? fcBytes / (2u * (u32)sizeof(FNode<W>)) : 0u; }
-    CLB_HD size_t smemBytes(u32 nThreads) const { return (size_t)(nThreads / 32) * 2 * fcNodes() * sizeof(FNode<W>); }
-    CLB_HD void bindShared(State& s, u8* smem, u32 tid, u32) const {
-        s.fc = fcNodes() ? smem + (size_t)(tid / 32) * 2 * fcNodes() * sizeof(FNode<W>) : (u8*)0;
-    }
     CLB_HD void begin(State& s, u32 warp) const {
-        s.fc = (u8*)0;
         CLB_LANES_G(l, GS) {
             s.ctr[l].nodes = s.ctr[l].lookups = s.ctr[l].rows = s.ctr[l].fmOccs = 0;
             s.started[l] = 0;
@@ -154,12 +143,6 @@ template <typename W, int GS> struct FrontierKernel {
         const PartInfo pi = B.parts.load(task.t, st->P);
         const DevSearch& se = st->sc[pi.scheme].s[task.search];
         Frontier<W, GS> F(ix, B, se, pi, task.t, task.search, s.scr, (u32)slabBytes);
-        F.prefetch = prefetch != 0;
-        if (s.fc) {
-            F.fc[0] = (FNode<W>*)s.fc;
-            F.fc[1] = F.fc[0] + fcNodes();
-            F.fcCap = fcNodes();
-        }
         LV<u64> started, immediate;
         CLB_LANES_G(l, GS) {
             started[l] = 0;

@@ -132,8 +132,9 @@ template <int GS> __device__ __forceinline__ u32 grpBcastG(const LV<u32>& x, int
     return v;
 }
 #else
+enum { GRP_MAX = 128 }; // largest group the host emulation runs (a CTA of 128 lanes)
 template <typename T> struct LV {
-    T v[GRP];
+    T v[GRP_MAX];
     T& operator[](int l) { return v[l]; }
     const T& operator[](int l) const { return v[l]; }
 };
@@ -167,13 +168,12 @@ inline u32 grpMax(const LV<u32>& x) {
     return s;
 }
 inline u32 grpBcast(const LV<u32>& x, int src) { return x.v[src]; }
-// the CPU harness emulates a group of min(GS, 32) lanes (groups above a warp are emulated by 32 lanes that
-// stride by GS: their chunks then hold GS - 32 empty places, which changes nothing but the work per chunk)
-#define CLB_LANES_G(l, GS) for (int l = 0; l < ((GS) < GRP ? (GS) : GRP); l++)
-template <int GS> inline void grpSyncG() {}
+// the CPU harness emulates a group of GS <= GRP_MAX lanes
+#define CLB_LANES_G(l, GS) for (int l = 0; l < (GS); l++)
+template <int GS> inline void grpSyncG() { static_assert(GS <= GRP_MAX, "group size of the host emulation"); }
 template <int GS> inline u32 grpExScanG(const LV<u32>& x, LV<u32>& out) {
     u32 run = 0;
-    for (int l = 0; l < (GS < GRP ? GS : GRP); l++) {
+    for (int l = 0; l < GS; l++) {
         const u32 v = x.v[l];
         out.v[l] = run;
         run += v;

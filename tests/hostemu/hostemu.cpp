@@ -54,15 +54,14 @@ struct HostEmuBackend {
         k.end(st);
         launches++;
     }
-    static const int kHeavyGroup = 32; // lanes per heavy search task (the emulation always runs groups of 32)
-    u32 heavyGroupSize() const { return 32; }
+    static const int kHeavyGroup = 128; // lanes per heavy search task, as on the GPU
+    u32 heavyGroupSize() const { return 128; }
     // lanes per task of the first search launch (8, 16 or 32), as in the CUDA backend
     u32 searchGroupSize() const {
         const char* e = getenv("COLUMBA_B200_SEARCH_GROUP");
         const int v = e ? atoi(e) : 0;
         return v == 8 ? 8u : (v == 16 ? 16u : 32u);
     }
-    u32 frontierCacheBytes() const { return 0; } // no shared memory here
     const u32* abortWord = nullptr;
     void setAbortWord(const u32* w) { abortWord = w; }
     static u32 sortResult(u32) { return 0; }

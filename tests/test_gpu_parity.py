@@ -43,6 +43,27 @@ def test_gpu_matches_reference_golden(case, gpu_indexes):
     m.close()
 
 
+@pytest.mark.parametrize("case", [c for c in sorted(CASES) if c.startswith("g2_")])
+@pytest.mark.parametrize("group", ["32", "16"])
+def test_gpu_heavy_search_launch_and_small_groups(case, group, gpu_indexes, monkeypatch):
+    """Small search scratch: a third of the tasks of the repeat-rich set go to the heavy launch (one CTA per task);
+    the first launch also with half-warp groups."""
+    monkeypatch.setenv("COLUMBA_B200_SEARCH_SLAB", "4096")
+    monkeypatch.setenv("COLUMBA_B200_SEARCH_GROUP", group)
+    p = CASES[case]
+    ix = gpu_indexes(p.get("kmer", 10), p.get("in_text", 4), p)
+    m = cb.Mapper(ix, gu.scheme_arg(p), p.get("metric", "edit"), p.get("partition", "dynamic"))
+    names, seqs = gu.read_fastq_gz(gu.reads_file(p))
+    reads, off = cb.Mapper.pack(seqs)
+    res = m.map_batch(reads, off, p["k"])
+    exp, ctr = gu.expected(case)
+    assert res.stats["HEAVY_TASKS"] > 0
+    assert res.tuples(names, ix.seq_names) == exp
+    for k, v in gu.CTR_MAP.items():
+        assert res.counters[v] == ctr[k], k
+    m.close()
+
+
 def test_gpu_rank_extend_locate_match_oracle(gpu_indexes, golden_index):
     ix = gpu_indexes(10, 4)
     m = cb.Mapper(ix)
