@@ -41,6 +41,20 @@ CLB_HD int popc32(u32 x) {
     return __builtin_popcount(x);
 #endif
 }
+CLB_HD int msb32(u32 x) { // index of the highest set bit, x != 0
+#if defined(__CUDA_ARCH__)
+    return 31 - __clz((int)x);
+#else
+    return 31 - __builtin_clz(x);
+#endif
+}
+CLB_HD int msb64(u64 x) { // x != 0
+#if defined(__CUDA_ARCH__)
+    return 63 - __clzll((long long)x);
+#else
+    return 63 - __builtin_clzll(x);
+#endif
+}
 CLB_HD int ctz64(u64 x) { // x != 0
 #if defined(__CUDA_ARCH__)
     return __ffsll((long long)x) - 1;

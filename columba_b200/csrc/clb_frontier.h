@@ -79,21 +79,8 @@ CLB_HD bool rowStepM(const MatGeom& g, const RowS<W>& p, u32 i, W M, RowS<W>& o)
     const u32 diagBit = l + K::DIAG_R0;
     o.score = p.score + (((D0 >> diagBit) & W(1)) ? 0u : 1u);
     bool ok = true;
-    if (!(D0 & RAC)) {
-        const W stop = W(1) << (diagBit - g.Wv);
-        int val = 1;
-        while (val > 0) {
-            if (HP & RAC)
-                val--;
-            if (HN & RAC)
-                val++;
-            if (RAC == stop) {
-                ok = false;
-                break;
-            }
-            RAC >>= 1u;
-        }
-    }
+    if (!(D0 & RAC))
+        ok = racWalk(HP, HN, RAC, W(1) << (diagBit - g.Wv));
     o.HP = HP;
     o.HN = HN;
     o.RAC = RAC;

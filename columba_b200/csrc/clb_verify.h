@@ -275,20 +275,8 @@ CLB_HD bool verifyWindowFast(const IndexView& ix, const Batch& B, u32 t, const B
             const u32 M = (u32)(pickM(M0, M1, M2, M3, Y) >> l);
             const u32 D0 = bandRow32(hp, hn, M);
             score += ((D0 >> dB) & 1u) ^ 1u;
-            if (!(D0 & rac)) {
-                u32 val = 1u;
-                while (val > 0) {
-                    if (hp & rac)
-                        val--;
-                    if (hn & rac)
-                        val++;
-                    if (rac == stop) {
-                        ok = false;
-                        break;
-                    }
-                    rac >>= 1;
-                }
-            }
+            if (!(D0 & rac))
+                ok = racWalk(hp, hn, rac, stop);
             if (!ok)
                 break;
             bs.ring[(size_t)l * bs.ringStride] = bandPack32(hp, M | ~D0, mu);
@@ -648,20 +636,8 @@ CLB_HD bool screenStep32(const IndexView& ix, ScreenState& s) {
         HP = (VN << 1) | ~(D0 | (VP << 1));
         HN = D0 & (VP << 1);
         s.score += ((D0 >> dB) & 1u) ^ 1u;
-        if (!(D0 & RAC)) {
-            u32 val = 1u;
-            while (val > 0) {
-                if (HP & RAC)
-                    val--;
-                if (HN & RAC)
-                    val++;
-                if (RAC == stop) {
-                    s.ok = 0;
-                    break;
-                }
-                RAC >>= 1;
-            }
-        }
+        if (!(D0 & RAC) && !racWalk(HP, HN, RAC, stop))
+            s.ok = 0;
         if (!s.ok)
             break;
         if (i >= s.firstRow)

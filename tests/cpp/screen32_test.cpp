@@ -48,7 +48,42 @@ struct HitLog {
     }
 };
 
+// the walk of the right-most active column as the reference does it
+template <typename W> static bool walkLoop(W HP, W HN, W& RAC, W stop) {
+    u32 val = 1u;
+    while (val > 0) {
+        if (HP & RAC)
+            val--;
+        if (HN & RAC)
+            val++;
+        if (RAC == stop)
+            return false;
+        RAC >>= 1;
+    }
+    return true;
+}
+
 int main(int argc, char** argv) {
+    // racWalk (closed form + fallback) against the loop: random delta words, every stop <= RAC
+    for (u32 it = 0; it < 2000000; it++) {
+        const u64 a = ((u64)rnd() << 40) ^ ((u64)rnd() << 20) ^ rnd(), b = ((u64)rnd() << 40) ^ ((u64)rnd() << 20) ^ rnd();
+        const u64 dens = (it & 1) ? (((u64)rnd() << 40) ^ ((u64)rnd() << 20) ^ rnd()) : ~0ull;
+        const u64 HP = a & ~b & dens, HN = b & ~a & dens & (((u64)rnd() << 32) | rnd());
+        const u32 r = rnd() % 64, st = rnd() % (r + 1);
+        u64 R1 = 1ull << r, R2 = R1;
+        const bool o1 = racWalk(HP, HN, R1, 1ull << st), o2 = walkLoop<u64>(HP, HN, R2, 1ull << st);
+        if (o1 != o2 || (o1 && R1 != R2)) {
+            std::printf("FAILED racWalk 64 at %u\n", it);
+            return 1;
+        }
+        const u32 r3 = r % 32, st3 = st % (r3 + 1);
+        u32 Q1 = 1u << r3, Q2 = Q1;
+        const bool p1 = racWalk((u32)HP, (u32)HN, Q1, 1u << st3), p2 = walkLoop<u32>((u32)HP, (u32)HN, Q2, 1u << st3);
+        if (p1 != p2 || (p1 && Q1 != Q2)) {
+            std::printf("FAILED racWalk 32 at %u\n", it);
+            return 1;
+        }
+    }
     const u32 nReads = argc > 1 ? (u32)atoi(argv[1]) : 6000;
     // ---- text: random, with tandem repeats, homopolymers and copies
     const u32 N = 300000;
