@@ -497,9 +497,9 @@ struct CudaBackend {
         if (const char* e = getenv("COLUMBA_B200_SEARCH_OCC"))
             warpOcc = atoi(e) == 4 ? 4 : 8;
         if (const char* e = getenv("COLUMBA_B200_HEAVY_GROUP"))
-            heavyGroup = atoi(e) == 256 ? 256 : 128;
+            heavyGroup = atoi(e) == 128 ? 128 : 256;
         if (const char* e = getenv("COLUMBA_B200_HEAVY_PER_SM"))
-            heavyPerSM = atoi(e) == 1024 ? 1024 : HEAVY_THREADS_PER_SM;
+            heavyPerSM = atoi(e) == 512 ? HEAVY_THREADS_PER_SM : 1024;
         if (const char* e = getenv("COLUMBA_B200_SEARCH_GROUP")) {
             const int v = atoi(e);
             searchGroup = v == 8 ? 8 : (v == 16 ? 16 : 32);
@@ -602,11 +602,12 @@ struct CudaBackend {
         }
     }
     static const int kHeavyGroup = HEAVY_GROUP; // lanes per heavy search task (default)
-    int heavyGroup = 128;                       // CTAs of 128 threads, four per SM (COLUMBA_B200_HEAVY_GROUP=256: 256 x 2)
+    int heavyGroup = 256;                       // CTAs of 256 threads, four per SM (COLUMBA_B200_HEAVY_GROUP=128: 128 x 8)
     u32 heavyGroupSize() const { return (u32)heavyGroup; }
-    // resident threads per SM of the heavy launch: 512 (128 registers per thread) or, with
-    // COLUMBA_B200_HEAVY_PER_SM=1024, 1024 (64 registers): twice the tasks in flight
-    int heavyPerSM = HEAVY_THREADS_PER_SM;
+    // resident threads per SM of the heavy launch: 1024 (64 registers per thread) or, with
+    // COLUMBA_B200_HEAVY_PER_SM=512, 512 (128 registers).  Measured on the 3.1 Gbp workload (search stage per
+    // 1 M reads): 512 threads as 4 x 128: 163.4 ms, 1024 as 8 x 128: 156.7 ms, 1024 as 4 x 256: 154.8 ms
+    int heavyPerSM = 1024;
     // lanes per task of the first search launch: a warp, or (COLUMBA_B200_SEARCH_GROUP = 16, 8) half or a quarter
     // of one -- most levels of a light task hold fewer nodes than a warp has lanes, and the kernel waits on
     // dependent HBM round trips: smaller groups put 2x / 4x as many tasks in flight with the same registers

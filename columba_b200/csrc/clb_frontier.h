@@ -161,6 +161,8 @@ struct FAct {
     u32 spawn;  // phase instance of the next group that this leaf hands over to, or F_NONE
     u32 off;    // emission index of the leaf's first emission / prefix sum scratch
     u64 mask;   // end phase: cluster indices that this leaf reports
+    u32 pi;     // the leaf's phase instance and kind: the numbering passes work on the action list alone and
+    u32 kind;   // do not chase the node records (random 64-byte reads in a scratch far larger than the L2)
 };
 
 struct FGroup {
@@ -198,12 +200,13 @@ template <typename W, int GS> struct Frontier {
     bool edit;
     FGroup grp[MAXP];
     u32 nGroups;
+    u32 heavyWidth; // first launch: start ranges wider than this go to the heavy launch at once (0: never)
     LV<FCounters> ctr;
 
     CLB_HD Frontier(const IndexView& ix_, const Batch& B_, const DevSearch& s_, const PartInfo& pi_, u32 t_, u32 si,
                     u8* scr_, u32 cap_)
         : ix(ix_), B(B_), s(s_), pi(pi_), t(t_), searchIdx(si), scr(scr_), cap(cap_), top(0), err(0),
-          edit(B_.metric == METRIC_EDIT), nGroups(0) {
+          edit(B_.metric == METRIC_EDIT), nGroups(0), heavyWidth(0) {
         CLB_LANES_G(l, GS) {
             ctr[l].nodes = 0;
             ctr[l].lookups = 0;
@@ -767,10 +770,12 @@ template <typename W, int GS> struct Frontier {
                     if (n.kind() != FK_ALIVE && n.kind() != FK_DEAD && n.cnt == 1) {
                         FAct a;
                         a.node = i;
-                        a.nEv = 0;
+                        a.nEv = n.kind() == FK_IT ? n.r.sa.width() : 0u; // one candidate per row of the range
                         a.spawn = F_NONE;
                         a.off = 0;
                         a.mask = 0;
+                        a.pi = n.pi;
+                        a.kind = n.kind();
                         acts[n.base] = a;
                     }
                 }
@@ -985,19 +990,17 @@ template <typename W, int GS> struct Frontier {
                 if (a >= nA)
                     continue;
                 FAct& A = acts[a];
-                const Node& n = nodes[A.node];
-                const FPI& P = pis[n.pi];
-                if (n.kind() == FK_IT) {
-                    A.nEv = n.r.sa.width();
+                if (A.kind == FK_IT) // nEv was set with the action
                     continue;
-                }
-                if (n.kind() == FK_HAM_END) {
+                if (A.kind == FK_HAM_END) {
                     if (isEnd)
                         A.nEv = 1;
                     else
                         sp[l] = 1;
                     continue;
                 }
+                const Node& n = nodes[A.node];
+                const FPI& P = pis[n.pi];
                 Cluster C;
                 walkCluster(G, P, A.node, C);
                 const u32 maxED = s.U[idx], lowerBound = s.L[idx];
@@ -1183,7 +1186,7 @@ template <typename W, int GS> struct Frontier {
                     if (a < G.nActs) {
                         const u32 w = acts[a].spawn != F_NONE ? npis[acts[a].spawn].total : acts[a].nEv;
                         if (w)
-                            atomAdd<u32>(&pis[nodes[acts[a].node].pi].total, w);
+                            atomAdd<u32>(&pis[acts[a].pi].total, w);
                     }
                 }
             }
@@ -1226,7 +1229,7 @@ template <typename W, int GS> struct Frontier {
                 CLB_LANES_G(l, GS) {
                     const u32 a = base + (u32)l;
                     if (a < G.nActs) {
-                        const FPI& P = pis[nodes[acts[a].node].pi];
+                        const FPI& P = pis[acts[a].pi];
                         const u32 o = P.base + (acts[a].off - P.sBegin);
                         acts[a].off = o;
                         if (acts[a].spawn != F_NONE)
@@ -1250,7 +1253,7 @@ template <typename W, int GS> struct Frontier {
                     nc[l] = 0;
                     nf[l] = 0;
                     if (a < G.nActs && acts[a].nEv) {
-                        if (nodes[acts[a].node].kind() == FK_IT)
+                        if (acts[a].kind == FK_IT)
                             nc[l] = acts[a].nEv;
                         else
                             nf[l] = acts[a].nEv;
@@ -1403,6 +1406,12 @@ template <typename W, int GS> struct Frontier {
         }
         if (S.go == 0)
             return true;
+        // A task that starts from a wide range outgrows the first launch's scratch with near certainty: it is handed
+        // to the heavy launch here instead of after 16 k nodes of work that the heavy launch then repeats.
+        if (S.go == 1 && S.idx > 0 && heavyWidth && S.sm.r.width() > heavyWidth) {
+            err |= ERR_STACK_OVERFLOW;
+            return false;
+        }
         if (S.go == 2) { // verifyExactPartialMatchInText, src/fmindex/fmindex.cpp:245-265
             CLB_LANES_G(l, GS) {
                 if (l != 0)

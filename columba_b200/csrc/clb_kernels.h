@@ -122,6 +122,7 @@ template <typename W, int GS> struct FrontierKernel {
     u8* slabs;
     size_t slabBytes; // per warp
     u32 heavy;
+    u32 heavyWidth;   // first launch: tasks that start from a wider range are queued for the heavy launch at once
     struct State {
         LV<FCounters> ctr;
         LV<u64> started, immediate;
@@ -143,6 +144,7 @@ template <typename W, int GS> struct FrontierKernel {
         const PartInfo pi = B.parts.load(task.t, st->P);
         const DevSearch& se = st->sc[pi.scheme].s[task.search];
         Frontier<W, GS> F(ix, B, se, pi, task.t, task.search, s.scr, (u32)slabBytes);
+        F.heavyWidth = heavy ? 0u : heavyWidth;
         LV<u64> started, immediate;
         CLB_LANES_G(l, GS) {
             started[l] = 0;

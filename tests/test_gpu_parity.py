@@ -50,6 +50,8 @@ def test_gpu_heavy_search_launch_and_small_groups(case, group, gpu_indexes, monk
     the first launch also with half-warp groups."""
     monkeypatch.setenv("COLUMBA_B200_SEARCH_SLAB", "4096")
     monkeypatch.setenv("COLUMBA_B200_SEARCH_GROUP", group)
+    if group == "16":  # tasks that start from a wide range go to the heavy launch without a first attempt
+        monkeypatch.setenv("COLUMBA_B200_HEAVY_WIDTH", "64")
     p = CASES[case]
     ix = gpu_indexes(p.get("kmer", 10), p.get("in_text", 4), p)
     m = cb.Mapper(ix, gu.scheme_arg(p), p.get("metric", "edit"), p.get("partition", "dynamic"))

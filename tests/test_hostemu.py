@@ -58,6 +58,8 @@ def test_heavy_search_launch_and_small_groups(case, group, emu_indexes, monkeypa
     children counted then built) -- same occurrences and counters; the first launch with quarter-warp groups."""
     monkeypatch.setenv("COLUMBA_B200_SEARCH_SLAB", "4096")
     monkeypatch.setenv("COLUMBA_B200_SEARCH_GROUP", group)
+    if group == "8":  # tasks that start from a wide range go to the heavy launch without a first attempt
+        monkeypatch.setenv("COLUMBA_B200_HEAVY_WIDTH", "64")
     p = CASES[case]
     ix = emu_indexes(p.get("kmer", 10), p.get("in_text", 4), p)
     m = cb.Mapper(ix, gu.scheme_arg(p), p.get("metric", "edit"), p.get("partition", "dynamic"))
