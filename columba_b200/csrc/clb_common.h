@@ -41,6 +41,13 @@ CLB_HD int popc32(u32 x) {
     return __builtin_popcount(x);
 #endif
 }
+CLB_HD void prefetchL2(const void* p) {
+#if defined(__CUDA_ARCH__)
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+#else
+    (void)p;
+#endif
+}
 CLB_HD int msb32(u32 x) { // index of the highest set bit, x != 0
 #if defined(__CUDA_ARCH__)
     return 31 - __clz((int)x);

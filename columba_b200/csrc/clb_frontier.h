@@ -200,13 +200,14 @@ template <typename W, int GS> struct Frontier {
     bool edit;
     FGroup grp[MAXP];
     u32 nGroups;
+    bool rankPrefetch; // the ranking passes ask for the next level's records one level ahead
     u32 heavyWidth; // first launch: start ranges wider than this go to the heavy launch at once (0: never)
     LV<FCounters> ctr;
 
     CLB_HD Frontier(const IndexView& ix_, const Batch& B_, const DevSearch& s_, const PartInfo& pi_, u32 t_, u32 si,
                     u8* scr_, u32 cap_)
         : ix(ix_), B(B_), s(s_), pi(pi_), t(t_), searchIdx(si), scr(scr_), cap(cap_), top(0), err(0),
-          edit(B_.metric == METRIC_EDIT), nGroups(0), heavyWidth(0) {
+          edit(B_.metric == METRIC_EDIT), nGroups(0), rankPrefetch(false), heavyWidth(0) {
         CLB_LANES_G(l, GS) {
             ctr[l].nodes = 0;
             ctr[l].lookups = 0;
@@ -713,6 +714,10 @@ template <typename W, int GS> struct Frontier {
                 CLB_LANES_G(l, GS) {
                     const u32 i = base + (u32)l;
                     if (i < b1) {
+                        // the level above is read next, after the sync: ask for its records now (the scratch of
+                        // a heavy task is far larger than the L2, the passes over the levels wait on HBM)
+                        if (rankPrefetch && L > 1 && lvl[L - 1] + (i - b0) < b0)
+                            prefetchL2(&nodes[lvl[L - 1] + (i - b0)].parent);
                         const u32 c = nodes[i].cnt;
                         if (c)
                             atomAdd<u32>(&nodes[nodes[i].parent].cnt, c);
@@ -752,6 +757,8 @@ template <typename W, int GS> struct Frontier {
                 CLB_LANES_G(l, GS) {
                     const u32 i = base + (u32)l;
                     if (i < b1) {
+                        if (rankPrefetch && L + 1 < G.nLevels && b1 + (i - b0) < lvl[L + 2])
+                            prefetchL2(&nodes[b1 + (i - b0)].parent);
                         const u32 p = nodes[i].parent;
                         u32 b = nodes[p].base;
                         for (u32 q = 1; q <= 3 && i >= b0 + q && nodes[i - q].parent == p; q++)

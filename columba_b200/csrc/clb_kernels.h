@@ -123,6 +123,7 @@ template <typename W, int GS> struct FrontierKernel {
     size_t slabBytes; // per warp
     u32 heavy;
     u32 heavyWidth;   // first launch: tasks that start from a wider range are queued for the heavy launch at once
+    u32 rankPrefetch; // ranking passes prefetch one level ahead (Frontier::rankPrefetch)
     struct State {
         LV<FCounters> ctr;
         LV<u64> started, immediate;
@@ -145,6 +146,7 @@ template <typename W, int GS> struct FrontierKernel {
         const DevSearch& se = st->sc[pi.scheme].s[task.search];
         Frontier<W, GS> F(ix, B, se, pi, task.t, task.search, s.scr, (u32)slabBytes);
         F.heavyWidth = heavy ? 0u : heavyWidth;
+        F.rankPrefetch = rankPrefetch != 0;
         LV<u64> started, immediate;
         CLB_LANES_G(l, GS) {
             started[l] = 0;

@@ -124,6 +124,7 @@ template <typename BE> struct Pipeline {
     u32 dedupProbe = 0;      // batches since dedup was last tried (0: try it in the next batch)
     bool dedupOn = true;     // de-duplication was on in the batch in flight
     std::string lastError;
+    u32 rankPrefetch = 0;    // COLUMBA_B200_RANK_PREFETCH=1: the ranking passes of the search prefetch one level ahead
     u32 heavyWidth = 0;      // search tasks that start from a wider SA range skip the first launch (COLUMBA_B200_HEAVY_WIDTH)
     bool verify32 = true;    // the same for the full verification (COLUMBA_B200_VERIFY32=0)
     bool screen32 = true;    // screening pass on a 32-bit band where it fits (COLUMBA_B200_SCREEN32=0: 64-bit window)
@@ -132,6 +133,8 @@ template <typename BE> struct Pipeline {
         // test hook: small search scratch hands most tasks of a small batch to the heavy launch
         if (const char* e = getenv("COLUMBA_B200_SEARCH_SLAB"))
             searchSlabBytes = tmax<size_t>(4096, (size_t)atol(e));
+        if (const char* e = getenv("COLUMBA_B200_RANK_PREFETCH"))
+            rankPrefetch = atoi(e) != 0 ? 1u : 0u;
         if (const char* e = getenv("COLUMBA_B200_HEAVY_WIDTH"))
             heavyWidth = (u32)atol(e);
         if (const char* e = getenv("COLUMBA_B200_VERIFY32"))
@@ -380,31 +383,31 @@ template <typename BE> struct Pipeline {
             const u32 nHeavyGroups = tmax<u32>(1u, be.workers(WK_SEARCH_HEAVY) / (be.heavyGroupSize() / 32u * be.laneStride()));
             bSlabSearch.ensure(be, tmax<size_t>(sb * nGroups, hb * nHeavyGroups));
             if (wide) {
-                FrontierKernel<u128, 32> k2{ix, dst, B, (u8*)bSlabSearch.p, sb, 0, heavyWidth};
+                FrontierKernel<u128, 32> k2{ix, dst, B, (u8*)bSlabSearch.p, sb, 0, heavyWidth, rankPrefetch};
                 be.launch(k2, capTasks, &M->nTasks, WK_SEARCH);
-                FrontierKernel<u128, BE::kHeavyGroup> k2h{ix, dst, B, (u8*)bSlabSearch.p, hb, 1, heavyWidth};
+                FrontierKernel<u128, BE::kHeavyGroup> k2h{ix, dst, B, (u8*)bSlabSearch.p, hb, 1, heavyWidth, rankPrefetch};
                 be.launch(k2h, capTasks, &M->nHeavy, WK_SEARCH_HEAVY);
             } else {
                 if (sg == 8) {
-                    FrontierKernel<u64, 8> k2{ix, dst, B, (u8*)bSlabSearch.p, sb, 0, heavyWidth};
+                    FrontierKernel<u64, 8> k2{ix, dst, B, (u8*)bSlabSearch.p, sb, 0, heavyWidth, rankPrefetch};
                     be.launch(k2, capTasks, &M->nTasks, WK_SEARCH);
                 } else if (sg == 16) {
-                    FrontierKernel<u64, 16> k2{ix, dst, B, (u8*)bSlabSearch.p, sb, 0, heavyWidth};
+                    FrontierKernel<u64, 16> k2{ix, dst, B, (u8*)bSlabSearch.p, sb, 0, heavyWidth, rankPrefetch};
                     be.launch(k2, capTasks, &M->nTasks, WK_SEARCH);
                 } else {
-                    FrontierKernel<u64, 32> k2{ix, dst, B, (u8*)bSlabSearch.p, sb, 0, heavyWidth};
+                    FrontierKernel<u64, 32> k2{ix, dst, B, (u8*)bSlabSearch.p, sb, 0, heavyWidth, rankPrefetch};
                     be.launch(k2, capTasks, &M->nTasks, WK_SEARCH);
                 }
                 bool launched = false;
                 if constexpr (BE::kHeavyGroup > 128) {
                     if (be.heavyGroupSize() == 128) {
-                        FrontierKernel<u64, 128> k2s{ix, dst, B, (u8*)bSlabSearch.p, hb, 1, heavyWidth};
+                        FrontierKernel<u64, 128> k2s{ix, dst, B, (u8*)bSlabSearch.p, hb, 1, heavyWidth, rankPrefetch};
                         be.launch(k2s, capTasks, &M->nHeavy, WK_SEARCH_HEAVY);
                         launched = true;
                     }
                 }
                 if (!launched) {
-                    FrontierKernel<u64, BE::kHeavyGroup> k2h{ix, dst, B, (u8*)bSlabSearch.p, hb, 1, heavyWidth};
+                    FrontierKernel<u64, BE::kHeavyGroup> k2h{ix, dst, B, (u8*)bSlabSearch.p, hb, 1, heavyWidth, rankPrefetch};
                     be.launch(k2h, capTasks, &M->nHeavy, WK_SEARCH_HEAVY);
                 }
             }

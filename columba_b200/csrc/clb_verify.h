@@ -605,20 +605,46 @@ CLB_HD u32 screenEdAtCol32(const ScreenState& s, u32 HP, u32 HN, u32 i) {
     const int neg = popc32(HN & mask), pos = popc32(HP & mask);
     return s.score + ((i > col) ? (u32)(neg - pos) : (u32)(pos - neg));
 }
+// The rows of one step are gone through in segments that neither cross a block boundary (where the text window
+// and the four match-vector windows are fetched) nor the first row of the final-column zone (from where on the
+// distance in the final column is kept per row): the loop over a segment then has no such checks -- per row
+// the text character, the match vector, the recurrence, the score and the test of the right-most active column.
+template <bool EDS>
+CLB_HD bool screenRows32(ScreenState& s, u32& HP, u32& HN, u32& RAC, u32& i, u32 segEnd, u32 dB, u32 stop) {
+    u32 score = s.score;
+    const u64 tcur = s.tcur, M0 = s.M0, M1 = s.M1, M2 = s.M2, M3 = s.M3;
+    bool ok = true;
+    for (; i <= segEnd; ++i) {
+        const u32 l = i % BPC<u64>::BLOCK;
+        const u32 Y = (u32)(tcur >> (2 * l)) & 3u;
+        const u32 M = (u32)(pickM(M0, M1, M2, M3, Y) >> l);
+        const u32 D0 = bandRow32(HP, HN, M);
+        score += ((D0 >> dB) & 1u) ^ 1u;
+        if (!(D0 & RAC) && !racWalk(HP, HN, RAC, stop)) {
+            ok = false;
+            break;
+        }
+        if (EDS) {
+            s.score = score;
+            s.eds[i - s.firstRow] = (u8)screenEdAtCol32(s, HP, HN, i);
+        }
+    }
+    s.score = score;
+    return ok;
+}
 CLB_HD bool screenStep32(const IndexView& ix, ScreenState& s) {
     typedef BPC<u64> K;
-    PartSeq ps;
-    ps.planes = s.planes;
-    ps.nw = s.nw;
-    ps.base = 0;
-    ps.len = s.len;
     u32 i = s.i;
     const u32 last = tmin(s.size, i + SCREEN_ROWS - 1);
     u32 HP = (u32)s.HP, HN = (u32)s.HN, RAC = (u32)s.RAC;
     const u32 dB = s.dB, stop = 1u << (dB - s.Wv);
-    for (; i <= last; ++i) {
-        const u32 l = i % K::BLOCK;
-        if (l == 0) {
+    while (i <= last) {
+        if (i % K::BLOCK == 0) {
+            PartSeq ps;
+            ps.planes = s.planes;
+            ps.nw = s.nw;
+            ps.base = 0;
+            ps.len = s.len;
             s.tcur = s.tnxt;
             s.tnxt = textWindow64(ix, s.start + i + K::BLOCK - 1);
             const i32 w0 = (i32)i - 1 - (i32)dB;
@@ -627,21 +653,18 @@ CLB_HD bool screenStep32(const IndexView& ix, ScreenState& s) {
             s.M2 = seqWindow64(ps, 2, w0);
             s.M3 = seqWindow64(ps, 3, w0);
         }
-        const u32 Y = (u32)(s.tcur >> (2 * l)) & 3u;
-        const u32 M = (u32)(pickM(s.M0, s.M1, s.M2, s.M3, Y) >> l);
-        const u32 HPa = (HP >> 1) | 0x80000000u, HNa = HN >> 1; // the previous row on this row's columns
-        const u32 D0 = (((M & HPa) + HPa) ^ HPa) | M | HNa;
-        const u32 VP = HNa | ~(D0 | HPa);
-        const u32 VN = D0 & HPa;
-        HP = (VN << 1) | ~(D0 | (VP << 1));
-        HN = D0 & (VP << 1);
-        s.score += ((D0 >> dB) & 1u) ^ 1u;
-        if (!(D0 & RAC) && !racWalk(HP, HN, RAC, stop))
+        u32 segEnd = tmin(last, i | (K::BLOCK - 1));
+        bool ok;
+        if (i >= s.firstRow) {
+            ok = screenRows32<true>(s, HP, HN, RAC, i, segEnd, dB, stop);
+        } else {
+            segEnd = tmin(segEnd, s.firstRow - 1);
+            ok = screenRows32<false>(s, HP, HN, RAC, i, segEnd, dB, stop);
+        }
+        if (!ok) {
             s.ok = 0;
-        if (!s.ok)
             break;
-        if (i >= s.firstRow)
-            s.eds[i - s.firstRow] = (u8)screenEdAtCol32(s, HP, HN, i);
+        }
     }
     s.HP = HP;
     s.HN = HN;
