@@ -599,15 +599,12 @@ template <typename W, int GS> struct Frontier {
                         r = d.r;
                         cc = d.c;
                     } else {
-                        // extendFMPos: all four children with two rank lookups, this lane keeps its own
-                        RangePair ch[4];
-                        const RangePair parentRange = (x.flags() & FF_USE_SM) ? P.sm.r : x.r;
-                        extendAll(ix, (int)dir, uni != 0, parentRange, ch);
+                        // extendFMPos: the two rank lookups serve all four children, this lane computes its own
+                        r = (x.flags() & FF_USE_SM) ? P.sm.r : x.r;
                         if (q == 0)
                             ctr[l].lookups += 2;
                         cc = 3u - q;
-                        r = pick4(ch, cc);
-                        if (r.empty())
+                        if (!extendOne(ix, (int)dir, uni != 0, cc, r))
                             continue;
                         ctr[l].nodes++;
                     }
