@@ -529,10 +529,12 @@ template <typename W, int GS> struct Frontier {
                 if (err)
                     break;
                 outBase += total;
-                grpSyncG<GS>();
             }
             if (err)
                 break;
+            // the children become visible to the lanes that expand them: once per level (the chunks of a level
+            // touch disjoint records; a barrier per chunk was a third of the CTA launch's barriers)
+            grpSyncG<GS>();
             level++;
             if (level + 1 >= lvlCap) {
                 err |= ERR_INTERNAL;
@@ -683,10 +685,10 @@ template <typename W, int GS> struct Frontier {
                         nodes[outBase + off[l]] = kid[l];
                 }
                 outBase += total;
-                grpSyncG<GS>();
             }
             if (err)
                 break;
+            grpSyncG<GS>(); // the children become visible to the lanes that expand them: once per level
             level++;
             if (level + 1 >= lvlCap) {
                 err |= ERR_INTERNAL;
