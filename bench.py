@@ -575,11 +575,14 @@ def main():
             if os.path.exists(sam):
                 os.unlink(sam)
             if p.returncode == 0 and mt:
+                mf = re.search(r"formatting threads per mapping thread (\d+)", p.stderr)
                 line["e2e_sam"] = {"value": n / float(mt.group(2)), "unit": "reads/s", "seconds": float(mt.group(2)),
                                    "reads": n, "sam_bytes": sam_bytes, "host_threads": int(mt.group(1)),
+                                   "format_threads_per_host_thread": int(mf.group(1)) if mf else 1,
                                    "includes": "FASTQ parsing, H2D, kernels, D2H, SAM formatting and writing to /dev/shm by "
                                                "the batch driver columba_b200/bin/clb_map (one context per host thread, "
-                                               "batches of 262144 reads, no warm-up); index load excluded, as in the "
+                                               "batches of 262144 reads, a batch's records formatted and written by "
+                                               "several threads, no warm-up); index load excluded, as in the "
                                                "reference's 'mapping threads finished mapping in' timer"}
             else:
                 line["e2e_sam"] = {"value": None, "error": (p.stderr or "")[-200:]}

@@ -21,10 +21,10 @@ def fastq():
     return fq
 
 
-def run(exe, base, k, threads, batch, tmp_path):
+def run(exe, base, k, threads, batch, tmp_path, fmt=3):
     sam = str(tmp_path / "out.sam")
     p = subprocess.run([exe, "-r", base, "-f", fastq(), "-o", sam, "-e", str(k), "-t", str(threads), "-b", str(batch),
-                        "-D", cb.SCHEMES_DIR], capture_output=True, text=True)
+                        "-F", str(fmt), "-D", cb.SCHEMES_DIR], capture_output=True, text=True)
     assert p.returncode == 0, p.stderr[-500:]
     assert "mapping threads finished mapping in" in p.stderr
     return [l for l in open(sam) if not l.startswith("@")]
@@ -37,8 +37,8 @@ def test_batch_driver_kernel_logic(case, golden_index, hostemu_lib, tmp_path):
     if not os.path.exists(exe) or os.path.getmtime(exe) < max(os.path.getmtime(SRC), os.path.getmtime(hostemu_lib)):
         subprocess.check_call(["g++", "-std=c++14", "-O2", SRC, "-L", libdir, "-lclb_hostemu", "-Wl,-rpath," + libdir,
                                "-lpthread", "-o", exe])
-    for threads, batch in ((1, 1 << 20), (2, 64), (3, 7)):
-        assert run(exe, golden_index, CASES[case], threads, batch, tmp_path) == expected_sam(case)
+    for threads, batch, fmt in ((1, 1 << 20, 5), (2, 64, 1), (3, 7, 3), (2, 200, 2)):
+        assert run(exe, golden_index, CASES[case], threads, batch, tmp_path, fmt) == expected_sam(case)
 
 
 @pytest.mark.gpu
