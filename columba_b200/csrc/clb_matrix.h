@@ -207,20 +207,8 @@ CLB_HD bool bpComputeRow(const MatGeom& g, Row<W>* bv, const PartSeq& ps, u32 i,
     const u32 diagBit = l + K::DIAG_R0;
     bv[i].score = bv[i - 1].score + ((D0 & (W(1) << diagBit)) ? 0u : 1u);
     bool ok = true;
-    if (!(D0 & RAC)) {
-        u32 val = 1u;
-        while (val > 0) {
-            if (HP & RAC)
-                val--;
-            if (HN & RAC)
-                val++;
-            if (RAC == (W(1) << (diagBit - g.Wv))) {
-                ok = false;
-                break;
-            }
-            RAC >>= 1u;
-        }
-    }
+    if (!(D0 & RAC))
+        ok = racWalk(HP, HN, RAC, W(1) << (diagBit - g.Wv));
     bv[i].HP = HP;
     bv[i].HN = HN;
     bv[i].D0 = D0;
@@ -240,17 +228,6 @@ template <typename W> CLB_HD u32 bpAt(const Row<W>* bv, u32 i, u32 j) {
     score += (i > j) ? (u32)(neg - pos) : (u32)(pos - neg);
     return score;
 }
-// bitparallelmatrix.h:651-665
-template <typename W> CLB_HD bool bpOnlyVerticalGapsLeft(const MatGeom& g, const Row<W>* bv, u32 i) {
-    typedef BPC<W> K;
-    if (i + K::LEFT < g.n)
-        return false;
-    const u32 b = i / K::BLOCK, r = i % K::BLOCK;
-    u32 bb = K::DIAG_R0 - g.Wv + r + 1;
-    u32 be = K::DIAG_R0 + g.n - b * K::BLOCK;
-    return (((~bv[i].HN >> bb) << bb) << (K::WORD - be)) == W(0);
-}
-
 // CIGAR ops are emitted back to front as (len << 2) | op with op 0=M 1=I 2=D;
 // the caller reverses them.  Returns the number of runs (0xFFFFFFFF on
 // overflow of cap).
