@@ -54,9 +54,19 @@ struct Batch {
     void parse() {
         const size_t n = size();
         nameLen.resize(n);
-        off.assign(1, 0);
-        off.reserve(n + 1);
-        seqs.clear();
+        off.resize(n + 1);
+        off[0] = 0;
+        seqs.resize(raw.size()); // upper bound; cut to size below
+        char* w = &seqs[0];
+        static const struct Clean { // upper case, everything but ACGT becomes N
+            char t[256];
+            Clean() {
+                for (int c = 0; c < 256; c++)
+                    t[c] = 'N';
+                for (const char* p = "ACGTacgt"; *p; p++)
+                    t[(unsigned char)*p] = (char)(*p & ~32);
+            }
+        } clean;
         for (size_t i = 0; i < n; i++) {
             // name: up to the first blank of the header line (Read::cleanUpRecord, src/reads.h:43-58)
             const uint32_t hb = lineOff[4 * i] + 1;
@@ -69,15 +79,11 @@ struct Batch {
             uint32_t se = lineOff[4 * i + 2];
             while (se > sb && (raw[se - 1] == '\n' || raw[se - 1] == '\r'))
                 se--;
-            for (uint32_t p = sb; p < se; p++) { // uppercase, everything but ACGT becomes N
-                char c = raw[p];
-                c = (char)(c >= 'a' && c <= 'z' ? c - 32 : c);
-                if (c != 'A' && c != 'C' && c != 'G' && c != 'T')
-                    c = 'N';
-                seqs.push_back(c);
-            }
-            off.push_back((uint32_t)seqs.size());
+            for (uint32_t p = sb; p < se; p++)
+                *w++ = clean.t[(unsigned char)raw[p]];
+            off[i + 1] = (uint32_t)(w - &seqs[0]);
         }
+        seqs.resize((size_t)(w - &seqs[0]));
     }
 };
 
