@@ -280,19 +280,8 @@ struct ScreenKernel {
     struct State {
         LocalCtr lc;
         ScreenState s;
-        u64 mloc[4]; // the match-vector windows where there is no shared memory (host emulation)
     };
-    // the CUDA launcher gives every thread four 64-bit slots of shared memory, interleaved over the CTA
-    static CLB_HD size_t smemBytes(u32 nThreads) { return (size_t)4 * nThreads * sizeof(u64); }
-    CLB_HD void bindShared(State& st, u8* smem, u32 tid, u32 nThreads) const {
-        st.s.mw = (u64*)smem + tid;
-        st.s.mws = nThreads;
-    }
-    CLB_HD void begin(State& st, u32) const {
-        st.lc.clear();
-        st.s.mw = st.mloc;
-        st.s.mws = 1;
-    }
+    CLB_HD void begin(State& st, u32) const { st.lc.clear(); }
     CLB_HD void run(State& st, u32 i) const {
         start(st, i);
         while (!step(st)) {

@@ -573,8 +573,6 @@ struct ScreenState {
     u32 Wv, firstRow, col, sofc, nw, len;
     u8 maxED, minED, run, considered, ok, done;
     u8 b32, dB; // 32-bit band (see screenStep32): in use, bit of the main diagonal
-    u64* mw;    // 32-bit band: the four match-vector windows of the block, window c at mw[c * mws] (shared memory
-    u32 mws;    // on the GPU: the row's window is then ONE indexed load instead of a select out of four registers)
     u8 eds[3 * BPC<u64>::MAX_ED + 4];
 };
 enum { SCREEN_ROWS = 8 };
@@ -614,14 +612,12 @@ CLB_HD u32 screenEdAtCol32(const ScreenState& s, u32 HP, u32 HN, u32 i) {
 template <bool EDS>
 CLB_HD bool screenRows32(ScreenState& s, u32& HP, u32& HN, u32& RAC, u32& i, u32 segEnd, u32 dB, u32 stop) {
     u32 score = s.score;
-    const u64 tcur = s.tcur;
-    const u64* mw = s.mw;
-    const u32 mws = s.mws;
+    const u64 tcur = s.tcur, M0 = s.M0, M1 = s.M1, M2 = s.M2, M3 = s.M3;
     bool ok = true;
     for (; i <= segEnd; ++i) {
         const u32 l = i % BPC<u64>::BLOCK;
         const u32 Y = (u32)(tcur >> (2 * l)) & 3u;
-        const u32 M = (u32)(mw[Y * mws] >> l);
+        const u32 M = (u32)(pickM(M0, M1, M2, M3, Y) >> l);
         const u32 D0 = bandRow32(HP, HN, M);
         score += ((D0 >> dB) & 1u) ^ 1u;
         if (!(D0 & RAC) && !racWalk(HP, HN, RAC, stop)) {
@@ -652,10 +648,10 @@ CLB_HD bool screenStep32(const IndexView& ix, ScreenState& s) {
             s.tcur = s.tnxt;
             s.tnxt = textWindow64(ix, s.start + i + K::BLOCK - 1);
             const i32 w0 = (i32)i - 1 - (i32)dB;
-            s.mw[0] = seqWindow64(ps, 0, w0);
-            s.mw[s.mws] = seqWindow64(ps, 1, w0);
-            s.mw[2 * s.mws] = seqWindow64(ps, 2, w0);
-            s.mw[3 * s.mws] = seqWindow64(ps, 3, w0);
+            s.M0 = seqWindow64(ps, 0, w0);
+            s.M1 = seqWindow64(ps, 1, w0);
+            s.M2 = seqWindow64(ps, 2, w0);
+            s.M3 = seqWindow64(ps, 3, w0);
         }
         u32 segEnd = tmin(last, i | (K::BLOCK - 1));
         bool ok;
@@ -733,10 +729,10 @@ CLB_HD void screenStart(const IndexView& ix, const Batch& B, u32 ci, ScreenState
         if (s.firstRow == 0)
             s.eds[0] = (u8)screenEdAtCol32(s, (u32)s.HP, (u32)s.HN, 0);
         const i32 w0 = -1 - (i32)s.dB;
-        s.mw[0] = seqWindow64(ps, 0, w0);
-        s.mw[s.mws] = seqWindow64(ps, 1, w0);
-        s.mw[2 * s.mws] = seqWindow64(ps, 2, w0);
-        s.mw[3 * s.mws] = seqWindow64(ps, 3, w0);
+        s.M0 = seqWindow64(ps, 0, w0);
+        s.M1 = seqWindow64(ps, 1, w0);
+        s.M2 = seqWindow64(ps, 2, w0);
+        s.M3 = seqWindow64(ps, 3, w0);
         s.tcur = textWindow64(ix, s.start) << 2;
         s.tnxt = textWindow64(ix, s.start + K::BLOCK - 1);
         if (s.size == 0)

@@ -206,10 +206,6 @@ int main(int argc, char** argv) {
         ScreenState a, b;
         std::memset(&a, 0, sizeof(a));
         std::memset(&b, 0, sizeof(b));
-        u64 mwa[4], mwb[4];
-        a.mw = mwa;
-        b.mw = mwb;
-        a.mws = b.mws = 1;
         screenStart(ix, B, ci, a, true);
         screenStart(ix, B, ci, b, false);
         CHECK(b.b32 == 0);
