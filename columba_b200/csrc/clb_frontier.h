@@ -1183,7 +1183,6 @@ template <typename W, int GS> struct Frontier {
         for (u32 q = nGroups; q-- > 0;) {
             FGroup& G = grp[q];
             FAct* acts = actsOf(G);
-            Node* nodes = nodesOf(G);
             FPI* pis = pisOf(G);
             FPI* npis = (q + 1 < nGroups) ? pisOf(grp[q + 1]) : (FPI*)0;
             for (u32 base = 0; base < G.nActs; base += GS) {
@@ -1202,7 +1201,6 @@ template <typename W, int GS> struct Frontier {
         for (u32 q = 0; q < nGroups; q++) {
             FGroup& G = grp[q];
             FAct* acts = actsOf(G);
-            Node* nodes = nodesOf(G);
             FPI* pis = pisOf(G);
             FPI* npis = (q + 1 < nGroups) ? pisOf(grp[q + 1]) : (FPI*)0;
             u32 run = 0;
